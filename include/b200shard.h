@@ -1,0 +1,153 @@
+/*
+ * b200shard.h — C ABI of libb200shard.so: the shard-execution hot path of
+ * seanbonjean/llm-sharding (NodeWorker.pass_through_shard) as hand-written sm_100a CUDA.
+ *
+ * The reference has no FFI on this path: the boundary it sits behind is a Python class,
+ * LlamaShardPart (utils/shard_loader.py:8-78), driven by NodeWorker
+ * (utils/node_worker.py:127-185 load_shards, :226-272 pass_through_shard, :319-355
+ * clear_KV_cache) and by Communicator (utils/node_worker.py:13-67) for the hop.  Each entry
+ * point below names the reference interface it replaces.  INTEGRATION.md shows the ctypes
+ * binding a maintainer of the reference would add.
+ *
+ * Conventions: every function returns 0 on success or a negative B200_E* code (no C++
+ * exception crosses the ABI); b200_last_error() gives the message for the calling thread.
+ * Pointers named d_* are DEVICE pointers owned by the caller; h_* are host pointers.
+ * `stream` is a cudaStream_t passed as void*.  All activations crossing the ABI are bf16
+ * ("model dtype" of the reference's messages, utils/node_worker.py:252,267-271); token ids
+ * are int64 like torch.long (utils/node_worker.py:208,264).
+ */
+#ifndef B200SHARD_H
+#define B200SHARD_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define B200_API __attribute__((visibility("default")))
+#else
+#define B200_API
+#endif
+
+#define B200_OK 0
+#define B200_EINVAL (-1)   /* -> ValueError  ("[ERROR] ..." texts of the reference)      */
+#define B200_ESTATE (-2)   /* -> RuntimeError (protocol / placement violations)           */
+#define B200_ECUDA (-3)    /* -> RuntimeError (CUDA runtime / driver failure)             */
+#define B200_ENOMEM (-4)   /* -> torch.cuda.OutOfMemoryError analogue (KV pages, HBM)     */
+#define B200_ETIMEOUT (-5) /* hop wait exceeded its bound                                 */
+
+/* element type of weight tensors handed to b200_shard_set_* (the .pth storage dtype,
+ * utils/model_sharder.py:24,72-88); the library converts to bf16 while repacking */
+#define B200_DT_BF16 0
+#define B200_DT_F32 1
+#define B200_DT_F16 2
+
+typedef struct b200_shard b200_shard_t; /* replaces LlamaShardPart (+ NodeWorker's lm_head / embed_tokens) */
+typedef struct b200_kv b200_kv_t;       /* replaces transformers DynamicCache held in NodeWorker.past_key_value */
+typedef struct b200_hop b200_hop_t;     /* replaces Communicator's data sockets on one NVSwitch box */
+
+typedef struct {
+    int32_t hidden_size;       /* LlamaConfig fields read at utils/shard_loader.py:35, utils/node_worker.py:88 */
+    int32_t intermediate_size;
+    int32_t n_heads;
+    int32_t n_kv_heads;
+    int32_t head_dim;          /* must be 128 */
+    int32_t vocab_size;
+    float rms_eps;
+    float rope_theta;
+    int32_t n_layers;          /* end - start of this shard (utils/node_worker.py:127-137) */
+    int32_t has_final_norm;    /* end == layer_num (utils/node_worker.py:155-157, utils/shard_loader.py:49-55) */
+    int32_t has_lm_head;       /* end == layer_num (utils/node_worker.py:158-164) */
+    int32_t has_embedding;     /* can_receive_user_request (utils/node_worker.py:105-107,119-124) */
+    int32_t max_tokens;        /* largest B*S of one forward call; sizes the workspace */
+    int32_t max_batch;         /* largest B of one forward call */
+} b200_shard_config_t;
+
+/* ---- shard lifecycle: LlamaShardPart.__init__ / NodeWorker.load_shards ---------------- */
+B200_API int b200_shard_create(const b200_shard_config_t* cfg, int device, b200_shard_t** out);
+/* One block_{i}.pth (utils/shard_loader.py:42-45): the 9 tensors in state_dict key order
+ * q,k,v,o,gate,up,down [out,in] row-major, input_layernorm, post_attention_layernorm.
+ * The library repacks into its own fused-QKV / paired gate-up layout and owns that copy;
+ * the caller's tensors may be freed when the call returns (it synchronises `stream`). */
+B200_API int b200_shard_set_layer(b200_shard_t* s, int rel_layer, const void* d_q, const void* d_k, const void* d_v,
+                         const void* d_o, const void* d_gate, const void* d_up, const void* d_down,
+                         const void* d_input_norm, const void* d_post_norm, int dtype, void* stream);
+/* final_norm.pth / lm_head.pth / embedding.pth (utils/shard_loader.py:49-55, utils/node_worker.py:160-163,121-124) */
+B200_API int b200_shard_set_final_norm(b200_shard_t* s, const void* d_weight, int dtype, void* stream);
+B200_API int b200_shard_set_lm_head(b200_shard_t* s, const void* d_weight, int dtype, void* stream);
+B200_API int b200_shard_set_embedding(b200_shard_t* s, const void* d_weight, int dtype, void* stream);
+/* `del self.shard` + empty_cache (utils/node_worker.py:139-147) */
+B200_API int b200_shard_destroy(b200_shard_t* s);
+
+/* ---- KV lifecycle: DynamicCache() / clear_KV_cache / get_seq_length -------------------- */
+/* One slot = one sequence (row of a batch).  Pages of `page_size` tokens (multiple of 64)
+ * are handed to slots on demand from a pool of `n_pages` shared by all layers of the shard. */
+B200_API int b200_kv_create(const b200_shard_t* s, int max_slots, int page_size, int n_pages, b200_kv_t** out);
+B200_API int b200_kv_reset(b200_kv_t* kv, int slot /* -1: every slot */, void* stream); /* clear_KV_cache, utils/node_worker.py:319-355 */
+B200_API int b200_kv_seq_len(const b200_kv_t* kv, int slot); /* past_key_value.get_seq_length(), utils/forwarding_utils.py:15-16 */
+B200_API int b200_kv_destroy(b200_kv_t* kv);
+
+/* ---- the hot path: LlamaShardPart.forward (utils/shard_loader.py:57-78) ---------------- */
+/* d_hidden_in / d_hidden_out: bf16 [B,S,H].  h_slots[b] is the KV slot of row b; every row
+ * must have the same cached length (the reference has no per-row lengths).
+ * Positions are kv_seq_len(slot) .. +S-1 (build_position_ids, utils/forwarding_utils.py:24),
+ * cos/sin are recomputed on device from them (LlamaRotaryEmbedding, called at
+ * utils/node_worker.py:241) so they need not travel with the message.
+ * causal = 0 reproduces the reference (no mask is passed: utils/node_worker.py:253-258);
+ * causal = 1 is real-Llama masking.  K,V of the S new tokens are appended to the slots.
+ * The final RMSNorm is applied when the shard has one (utils/shard_loader.py:76-77). */
+B200_API int b200_shard_forward(b200_shard_t* s, b200_kv_t* kv, const int32_t* h_slots, const void* d_hidden_in,
+                       int B, int S, int causal, void* d_hidden_out, void* stream);
+/* Tail: lm_head + argmax of the last position (utils/node_worker.py:260-265), computed for
+ * row S-1 only.  d_hidden is the forward output (after the final norm).  d_token_out int64 [B];
+ * d_margin_out (optional, may be NULL) float [B] = top-1 minus top-2 logit. */
+B200_API int b200_shard_lm_head_argmax(b200_shard_t* s, const void* d_hidden, int B, int S, int64_t* d_token_out,
+                              float* d_margin_out, void* stream);
+/* Fused forward + tail for tail shards: same as the two calls above but the fp32 residual
+ * never round-trips through bf16.  d_hidden_out may be NULL. */
+B200_API int b200_shard_forward_argmax(b200_shard_t* s, b200_kv_t* kv, const int32_t* h_slots, const void* d_hidden_in,
+                              int B, int S, int causal, void* d_hidden_out, int64_t* d_token_out,
+                              float* d_margin_out, void* stream);
+/* Entry node: embed_tokens(ids) (utils/node_worker.py:215,302). d_ids int64 [n] -> bf16 [n,H] */
+B200_API int b200_shard_embed(b200_shard_t* s, const int64_t* d_ids, int n, void* d_hidden_out, void* stream);
+
+/* ---- the hop: Communicator.transfer_data / receive_data (utils/node_worker.py:44-67) --- */
+/* One receive mailbox per process, in device memory, exported over CUDA IPC.  A sender maps
+ * the peer's mailbox, stores the payload into it with 128-bit NVLink stores from a kernel and
+ * then releases a sequence flag; the receiver's kernel acquires the flag and copies out. */
+#define B200_HOP_HANDLE_BYTES 80
+B200_API int b200_hop_create(int device, int n_ring_slots, int64_t slot_bytes, b200_hop_t** out);
+B200_API int b200_hop_export(b200_hop_t* h, void* h_handle_out /* B200_HOP_HANDLE_BYTES */);
+B200_API int b200_hop_connect(b200_hop_t* h, const void* h_peer_handle, int peer_device, int same_process);
+/* d_payload -> peer mailbox ring slot (seq % n_ring_slots); `seq` must increase by 1 per message. */
+B200_API int b200_hop_send(b200_hop_t* h, const void* d_payload, int64_t bytes, uint64_t seq, void* stream);
+/* wait (on the GPU) for message `seq` in the local mailbox, copy it to d_out; max_wait_us bounds the spin */
+B200_API int b200_hop_recv(b200_hop_t* h, void* d_out, int64_t bytes, uint64_t seq, int64_t max_wait_us, void* stream);
+B200_API int b200_hop_error(b200_hop_t* h); /* nonzero once a recv kernel timed out */
+B200_API int b200_hop_destroy(b200_hop_t* h);
+
+/* ---- introspection -------------------------------------------------------------------- */
+B200_API const char* b200_last_error(void);
+B200_API int b200_version(void);
+/* counters since creation: [0] kernel launches, [1] algorithmic HBM bytes (weights + KV read
+ * + KV write), [2] algorithmic flops, [3] forward calls */
+B200_API int b200_shard_counters(const b200_shard_t* s, uint64_t h_out[4]);
+B200_API int b200_shard_reset_counters(b200_shard_t* s);
+/* 1: capture single-token (S == 1) forwards into CUDA graphs keyed by (B, slots, pointers) */
+B200_API int b200_shard_set_graphs(b200_shard_t* s, int enabled);
+
+/* ---- single-kernel entry points (unit parity tests and micro-benchmarks) -------------- */
+/* LlamaRMSNorm.forward (transformers modeling_llama.py:62-67): fp32 in -> bf16 out, [rows, n] */
+B200_API int b200_rmsnorm(const float* d_x, const void* d_weight_bf16, float eps, int rows, int n, void* d_out_bf16,
+                 void* stream);
+/* out[M,N] (fp32) = A[M,K] (bf16) * W[N,K]^T (bf16): the tcgen05/TMA GEMM used for prefill */
+B200_API int b200_gemm_bf16(const void* d_a, const void* d_w, int M, int N, int K, float* d_out, void* stream);
+/* out[M,N] (fp32) = X[M,K] (fp32) * W[N,K]^T (bf16), M <= 4: the weight-streaming decode kernel */
+B200_API int b200_gemv_bf16(const float* d_x, const void* d_w, int M, int N, int K, float* d_out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200SHARD_H */

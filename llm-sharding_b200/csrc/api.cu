@@ -1,0 +1,702 @@
+// C ABI of libb200shard.so (include/b200shard.h): shard / KV lifecycle and the orchestration of
+// one LlamaShardPart.forward (utils/shard_loader.py:57-78) as a fixed sequence of sm_100a kernels.
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <map>
+#include <string>
+#include <vector>
+
+#include "../../include/b200shard.h"
+#include "internal.h"
+
+using namespace b200;
+
+static thread_local std::string g_err;
+static int fail(int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return code;
+}
+#define CU_TRY(expr)                                                                                      \
+    do {                                                                                                  \
+        cudaError_t e_ = (expr);                                                                          \
+        if (e_ != cudaSuccess)                                                                            \
+            return fail(e_ == cudaErrorMemoryAllocation ? B200_ENOMEM : B200_ECUDA, "[ERROR] CUDA: %s at %s:%d (%s)", \
+                        cudaGetErrorString(e_), __FILE__, __LINE__, #expr);                               \
+    } while (0)
+
+struct LayerW {
+    __nv_bfloat16 *wqkv = nullptr, *wo = nullptr, *wgu = nullptr, *wdown = nullptr, *norm1 = nullptr, *norm2 = nullptr;
+    void* slab = nullptr;
+    bool set = false;
+};
+
+struct GraphKey {
+    int B, causal, with_argmax;
+    const void *in, *out, *tok, *margin;
+    const b200_kv* kv;
+    int32_t slots[kMaxBatch];
+    bool operator<(const GraphKey& o) const { return memcmp(this, &o, sizeof(GraphKey)) < 0; }
+};
+
+struct b200_shard {
+    b200_shard_config_t cfg;
+    int device = 0, num_sms = 148;
+    int nq = 0, nkvd = 0, qkv_rows = 0;
+    std::vector<LayerW> layers;
+    __nv_bfloat16 *final_norm = nullptr, *lm_head = nullptr, *embedding = nullptr;
+    // workspace
+    float* x = nullptr;                 // fp32 residual stream [max_tokens, H]
+    __nv_bfloat16 *xn = nullptr, *qkv = nullptr, *qrot = nullptr, *attn_b = nullptr, *act_b = nullptr;
+    float *q_f = nullptr, *attn_f = nullptr, *act_f = nullptr;  // GEMV path (<= 4 rows), fp32
+    float *lastrow = nullptr, *logits = nullptr, *attn_part = nullptr;
+    __nv_bfloat16* lastrow_b = nullptr;
+    TokMeta tm{};
+    InvFreq inv{};
+    uint64_t n_launch = 0, n_bytes = 0, n_flops = 0, n_calls = 0;
+    bool graphs = false;
+    std::map<GraphKey, cudaGraphExec_t> graph_cache;
+    std::vector<void*> allocs;
+};
+
+struct b200_kv {
+    const b200_shard* shard = nullptr;
+    KvDev dev{};
+    __nv_bfloat16 *k_pool = nullptr, *v_pool = nullptr;
+    int64_t layer_stride = 0;  // elements per layer in a pool
+    std::vector<int> h_len, h_pages;
+    int h_free = 0;
+    std::vector<void*> allocs;
+};
+
+
+template <typename T>
+static int dev_alloc(std::vector<void*>& keep, T** out, size_t n_elems) {
+    void* p = nullptr;
+    size_t bytes = n_elems * sizeof(T);
+    if (bytes == 0) bytes = 16;
+    cudaError_t e = cudaMalloc(&p, bytes);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(B200_ENOMEM, "[ERROR] CUDA out of memory allocating %zu bytes: %s", bytes, cudaGetErrorString(e));
+    }
+    keep.push_back(p);
+    *out = reinterpret_cast<T*>(p);
+    return 0;
+}
+#define TRY(expr) do { int r_ = (expr); if (r_ != 0) return r_; } while (0)
+
+extern "C" B200_API const char* b200_last_error(void) { return g_err.c_str(); }
+extern "C" B200_API int b200_version(void) { return 100; }
+
+extern "C" B200_API int b200_shard_create(const b200_shard_config_t* c, int device, b200_shard_t** out) {
+    if (c == nullptr || out == nullptr) return fail(B200_EINVAL, "[ERROR] null argument");
+    if (c->head_dim != 128) return fail(B200_EINVAL, "[ERROR] head_dim must be 128 (got %d)", c->head_dim);
+    if (c->n_layers <= 0) return fail(B200_EINVAL, "[ERROR] start or end is invalid");
+    if (c->n_heads <= 0 || c->n_kv_heads <= 0 || c->n_heads % c->n_kv_heads != 0)
+        return fail(B200_EINVAL, "[ERROR] n_heads must be a positive multiple of n_kv_heads");
+    if (c->hidden_size % 8 != 0 || c->intermediate_size % 64 != 0 || c->vocab_size % 8 != 0)
+        return fail(B200_EINVAL, "[ERROR] hidden_size %% 8, intermediate_size %% 64 and vocab_size %% 8 must be 0");
+    if (c->max_batch < 1 || c->max_batch > kMaxBatch || c->max_tokens < c->max_batch)
+        return fail(B200_EINVAL, "[ERROR] need 1 <= max_batch <= %d and max_tokens >= max_batch", kMaxBatch);
+    CU_TRY(cudaSetDevice(device));
+    b200_shard* s = new b200_shard();
+    s->cfg = *c;
+    s->device = device;
+    cudaDeviceProp prop;
+    CU_TRY(cudaGetDeviceProperties(&prop, device));
+    s->num_sms = prop.multiProcessorCount;
+    s->nq = c->n_heads * 128;
+    s->nkvd = c->n_kv_heads * 128;
+    s->qkv_rows = s->nq + 2 * s->nkvd;
+    s->layers.resize(c->n_layers);
+    for (int j = 0; j < 64; ++j)  // compute_default_rope_parameters, modeling_llama.py:116-118 (fp32 like torch)
+        s->inv.v[j] = 1.0f / powf(c->rope_theta, (float)(2 * j) / 128.0f);
+    const size_t MT = (size_t)c->max_tokens, H = c->hidden_size, I = c->intermediate_size;
+    const size_t V = c->vocab_size;
+    int r = 0;
+    auto& A = s->allocs;
+    r |= dev_alloc(A, &s->x, MT * H);
+    r |= dev_alloc(A, &s->xn, MT * H);
+    r |= dev_alloc(A, &s->qkv, MT * s->qkv_rows);
+    r |= dev_alloc(A, &s->qrot, MT * s->nq);
+    r |= dev_alloc(A, &s->attn_b, MT * s->nq);
+    r |= dev_alloc(A, &s->act_b, MT * I);
+    r |= dev_alloc(A, &s->q_f, (size_t)kMaxGemvRows * s->nq);
+    r |= dev_alloc(A, &s->attn_f, (size_t)kMaxGemvRows * s->nq);
+    r |= dev_alloc(A, &s->act_f, (size_t)kMaxGemvRows * I);
+    r |= dev_alloc(A, &s->attn_part, (size_t)kMaxGemvRows * c->n_heads * kMaxSplits * 130);
+    r |= dev_alloc(A, &s->lastrow, (size_t)c->max_batch * H);
+    r |= dev_alloc(A, &s->lastrow_b, (size_t)c->max_batch * H);
+    r |= dev_alloc(A, &s->logits, (size_t)c->max_batch * V);
+    r |= dev_alloc(A, &s->tm.call_base, (size_t)c->max_batch);
+    r |= dev_alloc(A, &s->tm.pos, MT);
+    r |= dev_alloc(A, &s->tm.t_end, MT);
+    r |= dev_alloc(A, &s->tm.kv_off, MT);
+    r |= dev_alloc(A, &s->tm.cos, MT * 64);
+    r |= dev_alloc(A, &s->tm.sin, MT * 64);
+    if (r != 0) { b200_shard_destroy(s); return B200_ENOMEM; }
+    *out = s;
+    return 0;
+}
+
+extern "C" B200_API int b200_shard_destroy(b200_shard_t* s) {
+    if (s == nullptr) return 0;
+    cudaSetDevice(s->device);
+    cudaDeviceSynchronize();
+    for (auto& kv : s->graph_cache) cudaGraphExecDestroy(kv.second);
+    for (void* p : s->allocs) cudaFree(p);
+    for (auto& l : s->layers) if (l.slab) cudaFree(l.slab);
+    delete s;
+    return 0;
+}
+
+static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+extern "C" B200_API int b200_shard_set_layer(b200_shard_t* s, int rel, const void* q, const void* k, const void* v, const void* o,
+                                    const void* gate, const void* up, const void* down, const void* n1, const void* n2,
+                                    int dtype, void* stream) {
+    if (s == nullptr) return fail(B200_EINVAL, "[ERROR] null shard");
+    if (rel < 0 || rel >= s->cfg.n_layers)
+        return fail(B200_EINVAL, "[ERROR] String list: shard_weights length must be equal to (end - start)");
+    if (dtype < 0 || dtype > 2) return fail(B200_EINVAL, "[ERROR] unsupported weight dtype %d", dtype);
+    CU_TRY(cudaSetDevice(s->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    LayerW& L = s->layers[rel];
+    const size_t H = s->cfg.hidden_size, I = s->cfg.intermediate_size;
+    const size_t n_qkv = (size_t)s->qkv_rows * H, n_o = H * s->nq, n_gu = 2 * I * H, n_dn = H * I;
+    if (L.slab == nullptr) {
+        size_t off = 0, o_qkv = off; off = align_up(off + n_qkv * 2, 1024);
+        size_t o_o = off; off = align_up(off + n_o * 2, 1024);
+        size_t o_gu = off; off = align_up(off + n_gu * 2, 1024);
+        size_t o_dn = off; off = align_up(off + n_dn * 2, 1024);
+        size_t o_n1 = off; off = align_up(off + H * 2, 1024);
+        size_t o_n2 = off; off = align_up(off + H * 2, 1024);
+        cudaError_t e = cudaMalloc(&L.slab, off);
+        if (e != cudaSuccess) { cudaGetLastError(); return fail(B200_ENOMEM, "[ERROR] CUDA out of memory for layer weights (%zu bytes)", off); }
+        char* b = reinterpret_cast<char*>(L.slab);
+        L.wqkv = reinterpret_cast<__nv_bfloat16*>(b + o_qkv);
+        L.wo = reinterpret_cast<__nv_bfloat16*>(b + o_o);
+        L.wgu = reinterpret_cast<__nv_bfloat16*>(b + o_gu);
+        L.wdown = reinterpret_cast<__nv_bfloat16*>(b + o_dn);
+        L.norm1 = reinterpret_cast<__nv_bfloat16*>(b + o_n1);
+        L.norm2 = reinterpret_cast<__nv_bfloat16*>(b + o_n2);
+    }
+    launch_convert_to_bf16(q, dtype, L.wqkv, (int64_t)s->nq * H, st);
+    launch_convert_to_bf16(k, dtype, L.wqkv + (size_t)s->nq * H, (int64_t)s->nkvd * H, st);
+    launch_convert_to_bf16(v, dtype, L.wqkv + (size_t)(s->nq + s->nkvd) * H, (int64_t)s->nkvd * H, st);
+    launch_convert_to_bf16(o, dtype, L.wo, (int64_t)n_o, st);
+    launch_pack_gate_up(gate, dtype, L.wgu, (int)I, (int)H, 0, st);
+    launch_pack_gate_up(up, dtype, L.wgu, (int)I, (int)H, 1, st);
+    launch_convert_to_bf16(down, dtype, L.wdown, (int64_t)n_dn, st);
+    launch_convert_to_bf16(n1, dtype, L.norm1, (int64_t)H, st);
+    launch_convert_to_bf16(n2, dtype, L.norm2, (int64_t)H, st);
+    CU_TRY(cudaGetLastError());
+    CU_TRY(cudaStreamSynchronize(st));
+    L.set = true;
+    return 0;
+}
+
+static int set_single(b200_shard_t* s, __nv_bfloat16** dst, const void* w, size_t n, int dtype, void* stream, int present,
+                      const char* what) {
+    if (s == nullptr || w == nullptr) return fail(B200_EINVAL, "[ERROR] null argument");
+    if (!present) return fail(B200_ESTATE, "[ERROR] this shard was created without %s", what);
+    CU_TRY(cudaSetDevice(s->device));
+    if (*dst == nullptr) TRY(dev_alloc(s->allocs, dst, n));
+    launch_convert_to_bf16(w, dtype, *dst, (int64_t)n, (cudaStream_t)stream);
+    CU_TRY(cudaGetLastError());
+    CU_TRY(cudaStreamSynchronize((cudaStream_t)stream));
+    return 0;
+}
+extern "C" B200_API int b200_shard_set_final_norm(b200_shard_t* s, const void* w, int dtype, void* stream) {
+    return set_single(s, &s->final_norm, w, s ? s->cfg.hidden_size : 0, dtype, stream, s ? s->cfg.has_final_norm : 0, "a final norm");
+}
+extern "C" B200_API int b200_shard_set_lm_head(b200_shard_t* s, const void* w, int dtype, void* stream) {
+    return set_single(s, &s->lm_head, w, s ? (size_t)s->cfg.vocab_size * s->cfg.hidden_size : 0, dtype, stream,
+                      s ? s->cfg.has_lm_head : 0, "an lm_head");
+}
+extern "C" B200_API int b200_shard_set_embedding(b200_shard_t* s, const void* w, int dtype, void* stream) {
+    return set_single(s, &s->embedding, w, s ? (size_t)s->cfg.vocab_size * s->cfg.hidden_size : 0, dtype, stream,
+                      s ? s->cfg.has_embedding : 0, "an embedding layer");
+}
+
+// ------------------------------------------------------------------------------------- KV
+extern "C" B200_API int b200_kv_create(const b200_shard_t* s, int max_slots, int page_size, int n_pages, b200_kv_t** out) {
+    if (s == nullptr || out == nullptr) return fail(B200_EINVAL, "[ERROR] null argument");
+    if (max_slots < 1 || page_size < 64 || page_size % 64 != 0 || n_pages < 1)
+        return fail(B200_EINVAL, "[ERROR] need max_slots >= 1, page_size a multiple of 64, n_pages >= 1");
+    CU_TRY(cudaSetDevice(s->device));
+    b200_kv* kv = new b200_kv();
+    kv->shard = s;
+    KvDev& d = kv->dev;
+    d.max_slots = max_slots;
+    d.page_size = page_size;
+    d.n_pages = n_pages;
+    d.max_pages_per_slot = n_pages;  // a single slot may take the whole pool, up to the attention kernels' reach
+    if ((int64_t)d.max_pages_per_slot * page_size > (int64_t)kMaxSplits * kMaxChunkKeys)
+        d.max_pages_per_slot = (int)((int64_t)kMaxSplits * kMaxChunkKeys / page_size);
+    kv->layer_stride = (int64_t)n_pages * s->cfg.n_kv_heads * page_size * 128;
+    int r = 0;
+    r |= dev_alloc(kv->allocs, &d.seq_lens, (size_t)max_slots);
+    r |= dev_alloc(kv->allocs, &d.block_table, (size_t)max_slots * d.max_pages_per_slot);
+    r |= dev_alloc(kv->allocs, &d.pages_held, (size_t)max_slots);
+    r |= dev_alloc(kv->allocs, &d.free_stack, (size_t)n_pages);
+    r |= dev_alloc(kv->allocs, &d.free_top, 1);
+    r |= dev_alloc(kv->allocs, &d.error, 1);
+    r |= dev_alloc(kv->allocs, &kv->k_pool, (size_t)kv->layer_stride * s->cfg.n_layers);
+    r |= dev_alloc(kv->allocs, &kv->v_pool, (size_t)kv->layer_stride * s->cfg.n_layers);
+    if (r != 0) { b200_kv_destroy(kv); return B200_ENOMEM; }
+    // pages past a sequence's end are read (and masked) by the attention kernels: start from zeros
+    CU_TRY(cudaMemset(kv->k_pool, 0, (size_t)kv->layer_stride * s->cfg.n_layers * 2));
+    CU_TRY(cudaMemset(kv->v_pool, 0, (size_t)kv->layer_stride * s->cfg.n_layers * 2));
+    launch_kv_init(d, 0);
+    CU_TRY(cudaGetLastError());
+    CU_TRY(cudaDeviceSynchronize());
+    kv->h_len.assign(max_slots, 0);
+    kv->h_pages.assign(max_slots, 0);
+    kv->h_free = n_pages;
+    *out = kv;
+    return 0;
+}
+extern "C" B200_API int b200_kv_destroy(b200_kv_t* kv) {
+    if (kv == nullptr) return 0;
+    cudaSetDevice(kv->shard->device);
+    cudaDeviceSynchronize();
+    for (void* p : kv->allocs) cudaFree(p);
+    delete kv;
+    return 0;
+}
+extern "C" B200_API int b200_kv_reset(b200_kv_t* kv, int slot, void* stream) {
+    if (kv == nullptr) return fail(B200_EINVAL, "[ERROR] null kv");
+    if (slot < -1 || slot >= kv->dev.max_slots) return fail(B200_EINVAL, "[ERROR] kv slot %d out of range", slot);
+    CU_TRY(cudaSetDevice(kv->shard->device));
+    launch_kv_reset(kv->dev, slot, (cudaStream_t)stream);
+    CU_TRY(cudaGetLastError());
+    const int lo = slot < 0 ? 0 : slot, hi = slot < 0 ? kv->dev.max_slots : slot + 1;
+    for (int i = lo; i < hi; ++i) {
+        kv->h_free += kv->h_pages[i];
+        kv->h_pages[i] = 0;
+        kv->h_len[i] = 0;
+    }
+    return 0;
+}
+extern "C" B200_API int b200_kv_seq_len(const b200_kv_t* kv, int slot) {
+    if (kv == nullptr || slot < 0 || slot >= kv->dev.max_slots) return fail(B200_EINVAL, "[ERROR] kv slot out of range");
+    return kv->h_len[slot];
+}
+
+// ------------------------------------------------------------------------------------- forward
+static int gemv_row_limit(const b200_shard* s) {
+    const size_t kmax = (size_t)(s->cfg.intermediate_size > s->cfg.hidden_size ? s->cfg.intermediate_size : s->cfg.hidden_size);
+    const size_t kpad = ((kmax / 8 + 31) / 32) * 256;
+    int lim = (int)((220 * 1024) / (kpad * 4));
+    if (lim > kMaxGemvRows) lim = kMaxGemvRows;
+    return lim;
+}
+
+static int check_call(b200_shard_t* s, b200_kv_t* kv, const int32_t* h_slots, const void* in, int B, int S, SlotList* sl) {
+    if (s == nullptr || kv == nullptr || h_slots == nullptr || in == nullptr) return fail(B200_EINVAL, "[ERROR] null argument");
+    if (kv->shard != s) return fail(B200_ESTATE, "[ERROR] this KV cache belongs to another shard");
+    if (B < 1 || B > s->cfg.max_batch || S < 1 || (int64_t)B * S > s->cfg.max_tokens)
+        return fail(B200_EINVAL, "[ERROR] batch %d x seq_len %d exceeds the shard's limits (max_batch %d, max_tokens %d)", B, S,
+                    s->cfg.max_batch, s->cfg.max_tokens);
+    for (auto& l : s->layers)
+        if (!l.set) return fail(B200_ESTATE, "[ERROR] a layer of this shard has no weights loaded");
+    int need_total = 0;
+    for (int b = 0; b < B; ++b) {
+        const int slot = h_slots[b];
+        if (slot < 0 || slot >= kv->dev.max_slots) return fail(B200_EINVAL, "[ERROR] kv slot %d out of range", slot);
+        for (int c = 0; c < b; ++c)
+            if (h_slots[c] == slot) return fail(B200_EINVAL, "[ERROR] kv slot %d used by two rows of one batch", slot);
+        if (kv->h_len[slot] != kv->h_len[h_slots[0]])
+            return fail(B200_EINVAL, "[ERROR] rows of one batch must have equal cached lengths");
+        const int need = (kv->h_len[slot] + S + kv->dev.page_size - 1) / kv->dev.page_size;
+        if (need > kv->dev.max_pages_per_slot) return fail(B200_ENOMEM, "[ERROR] KV slot capacity exceeded");
+        need_total += need > kv->h_pages[slot] ? need - kv->h_pages[slot] : 0;
+        sl->v[b] = slot;
+    }
+    if (need_total > kv->h_free) return fail(B200_ENOMEM, "[ERROR] KV page pool exhausted (%d pages needed, %d free)", need_total, kv->h_free);
+    return 0;
+}
+
+// enqueue every kernel of one forward (+ optional tail); no host synchronisation
+static int enqueue_forward(b200_shard_t* s, b200_kv_t* kv, const SlotList& sl, const void* in, int B, int S, int causal,
+                           void* out, int64_t* tok, float* margin, bool with_tail, cudaStream_t st) {
+    const b200_shard_config_t& c = s->cfg;
+    const int M = B * S, H = c.hidden_size, I = c.intermediate_size;
+    const int64_t head_stride = (int64_t)kv->dev.page_size * 128;
+    launch_kv_alloc(kv->dev, sl, B, S, s->tm.call_base, st);
+    launch_prep(kv->dev, sl, B, S, causal, s->inv, c.n_kv_heads, s->tm, st);
+    launch_load_residual(reinterpret_cast<const __nv_bfloat16*>(in), s->x, (int64_t)M * H, st);
+    s->n_launch += 3;
+    const bool gemv_path = M <= gemv_row_limit(s);
+    for (int l = 0; l < c.n_layers; ++l) {
+        const LayerW& L = s->layers[l];
+        __nv_bfloat16* kp = kv->k_pool + (int64_t)l * kv->layer_stride;
+        __nv_bfloat16* vp = kv->v_pool + (int64_t)l * kv->layer_stride;
+        if (gemv_path) {
+            GemvParams g{};
+            g.W = L.wqkv; g.x = s->x; g.norm_w = L.norm1; g.eps = c.rms_eps; g.N = s->qkv_rows; g.K = H;
+            g.q_out = s->q_f; g.k_pool = kp; g.v_pool = vp; g.kv_off = s->tm.kv_off; g.cos = s->tm.cos; g.sin = s->tm.sin;
+            g.n_heads = c.n_heads; g.n_kv = c.n_kv_heads; g.head_stride = head_stride;
+            launch_gemv(g, M, EPI_QKV, true, s->num_sms, st);
+            AttnDecodeParams a{};
+            a.q = s->q_f; a.k_pool = kp; a.v_pool = vp; a.block_table = kv->dev.block_table; a.t_end = s->tm.t_end;
+            a.slots = sl; a.S = S; a.n_heads = c.n_heads; a.n_kv = c.n_kv_heads; a.page_size = kv->dev.page_size;
+            a.max_pages_per_slot = kv->dev.max_pages_per_slot;
+            int ns = (2 * s->num_sms + M * c.n_heads - 1) / (M * c.n_heads);
+            const int ns_cap = (kv->dev.max_pages_per_slot * kv->dev.page_size + kMaxChunkKeys - 1) / kMaxChunkKeys;
+            if (ns < ns_cap) ns = ns_cap;
+            a.n_splits = ns < 1 ? 1 : (ns > kMaxSplits ? kMaxSplits : ns);
+            a.part = s->attn_part; a.out = s->attn_f;
+            launch_attn_decode(a, M, st);
+            GemvParams o{};
+            o.W = L.wo; o.x = s->attn_f; o.N = H; o.K = s->nq; o.out = s->x;
+            launch_gemv(o, M, EPI_RESID, false, s->num_sms, st);
+            GemvParams gu{};
+            gu.W = L.wgu; gu.x = s->x; gu.norm_w = L.norm2; gu.eps = c.rms_eps; gu.N = 2 * I; gu.K = H; gu.out = s->act_f;
+            launch_gemv(gu, M, EPI_SWIGLU, true, s->num_sms, st);
+            GemvParams d{};
+            d.W = L.wdown; d.x = s->act_f; d.N = H; d.K = I; d.out = s->x;
+            launch_gemv(d, M, EPI_RESID, false, s->num_sms, st);
+            s->n_launch += 6;
+        } else {
+            launch_rmsnorm_bf16(s->x, L.norm1, c.rms_eps, M, H, s->xn, st);
+            GemmParams g{s->xn, L.wqkv, M, s->qkv_rows, H, s->qkv, GEMM_STORE_BF16};
+            if (launch_gemm(g, st) != 0) return fail(B200_ECUDA, "[ERROR] %s", gemm_error());
+            RopeAppendParams ra{};
+            ra.qkv = s->qkv; ra.q_out = s->qrot; ra.k_pool = kp; ra.v_pool = vp; ra.kv_off = s->tm.kv_off;
+            ra.cos = s->tm.cos; ra.sin = s->tm.sin; ra.n_heads = c.n_heads; ra.n_kv = c.n_kv_heads; ra.head_stride = head_stride;
+            launch_rope_append(ra, M, st);
+            AttnPrefillParams ap{};
+            ap.q = s->qrot; ap.k_pool = kp; ap.v_pool = vp; ap.block_table = kv->dev.block_table; ap.call_base = s->tm.call_base;
+            ap.slots = sl; ap.B = B; ap.S = S; ap.causal = causal; ap.n_heads = c.n_heads; ap.n_kv = c.n_kv_heads;
+            ap.page_size = kv->dev.page_size; ap.max_pages_per_slot = kv->dev.max_pages_per_slot; ap.out = s->attn_b;
+            launch_attn_prefill(ap, st);
+            GemmParams o{s->attn_b, L.wo, M, H, s->nq, s->x, GEMM_RESID_F32};
+            if (launch_gemm(o, st) != 0) return fail(B200_ECUDA, "[ERROR] %s", gemm_error());
+            launch_rmsnorm_bf16(s->x, L.norm2, c.rms_eps, M, H, s->xn, st);
+            GemmParams gu{s->xn, L.wgu, M, 2 * I, H, s->act_b, GEMM_SWIGLU_BF16};
+            if (launch_gemm(gu, st) != 0) return fail(B200_ECUDA, "[ERROR] %s", gemm_error());
+            GemmParams d{s->act_b, L.wdown, M, H, I, s->x, GEMM_RESID_F32};
+            if (launch_gemm(d, st) != 0) return fail(B200_ECUDA, "[ERROR] %s", gemm_error());
+            s->n_launch += 8;
+        }
+    }
+    if (out != nullptr) {  // final RMSNorm when this is the tail shard (utils/shard_loader.py:76-77), else a plain cast
+        launch_rmsnorm_bf16(s->x, c.has_final_norm ? s->final_norm : nullptr, c.rms_eps, M, H,
+                            reinterpret_cast<__nv_bfloat16*>(out), st);
+        s->n_launch += 1;
+    }
+    if (with_tail) {
+        launch_lastrow_norm_f32(s->x, c.has_final_norm ? s->final_norm : nullptr, c.rms_eps, B, S, H, s->lastrow, st);
+        s->n_launch += 1;
+    }
+    (void)tok; (void)margin;
+    return 0;
+}
+
+static int enqueue_tail(b200_shard_t* s, int B, int64_t* tok, float* margin, cudaStream_t st) {
+    const b200_shard_config_t& c = s->cfg;
+    if (B <= gemv_row_limit(s)) {
+        GemvParams g{};
+        g.W = s->lm_head; g.x = s->lastrow; g.N = c.vocab_size; g.K = c.hidden_size; g.out = s->logits;
+        launch_gemv(g, B, EPI_STORE, false, s->num_sms, st);
+    } else {
+        launch_rmsnorm_bf16(s->lastrow, nullptr, 0.f, B, c.hidden_size, s->lastrow_b, st);
+        GemmParams g{s->lastrow_b, s->lm_head, B, c.vocab_size, c.hidden_size, s->logits, GEMM_STORE_F32};
+        if (launch_gemm(g, st) != 0) return fail(B200_ECUDA, "[ERROR] %s", gemm_error());
+        s->n_launch += 1;
+    }
+    launch_argmax(s->logits, B, c.vocab_size, tok, margin, st);
+    s->n_launch += 2;
+    return 0;
+}
+
+static void account(b200_shard_t* s, b200_kv_t* kv, const SlotList& sl, int B, int S, int causal, bool tail) {
+    const b200_shard_config_t& c = s->cfg;
+    const uint64_t H = c.hidden_size, I = c.intermediate_size;
+    const uint64_t params = (uint64_t)s->qkv_rows * H + H * s->nq + 3 * I * H;
+    uint64_t bytes = (uint64_t)c.n_layers * (params * 2 + 2 * H * 2);
+    uint64_t flops = (uint64_t)c.n_layers * 2 * params * (uint64_t)B * S;
+    for (int b = 0; b < B; ++b) {
+        const uint64_t T = (uint64_t)kv->h_len[sl.v[b]] + S;
+        bytes += (uint64_t)c.n_layers * 2 * T * s->nkvd * 2;         // K,V read once per call
+        bytes += (uint64_t)c.n_layers * 2 * (uint64_t)S * s->nkvd * 2;  // K,V append
+        const uint64_t pairs = causal ? ((uint64_t)S * (2 * T - S + 1)) / 2 : (uint64_t)S * T;
+        flops += (uint64_t)c.n_layers * 4 * pairs * s->nq;
+    }
+    if (tail) {
+        bytes += (uint64_t)c.vocab_size * H * 2 + H * 2;
+        flops += 2ull * c.vocab_size * H * B;
+    }
+    s->n_bytes += bytes;
+    s->n_flops += flops;
+    s->n_calls += 1;
+}
+
+static int forward_impl(b200_shard_t* s, b200_kv_t* kv, const int32_t* h_slots, const void* in, int B, int S, int causal,
+                        void* out, int64_t* tok, float* margin, bool with_tail, void* stream) {
+    SlotList sl{};
+    TRY(check_call(s, kv, h_slots, in, B, S, &sl));
+    if (with_tail) {
+        if (!s->cfg.has_lm_head || s->lm_head == nullptr) return fail(B200_ESTATE, "[ERROR] this shard does not hold the lm_head");
+        if (tok == nullptr) return fail(B200_EINVAL, "[ERROR] null token output");
+    }
+    if (s->cfg.has_final_norm && s->final_norm == nullptr) return fail(B200_ESTATE, "[ERROR] final norm weight not loaded");
+    CU_TRY(cudaSetDevice(s->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    account(s, kv, sl, B, S, causal, with_tail);
+    bool done = false;
+    if (s->graphs && S == 1) {
+        GraphKey key;
+        memset(&key, 0, sizeof(key));
+        key.B = B; key.causal = causal; key.with_argmax = with_tail ? 1 : 0;
+        key.in = in; key.out = out; key.tok = tok; key.margin = margin; key.kv = kv;
+        for (int b = 0; b < B; ++b) key.slots[b] = sl.v[b];
+        auto it = s->graph_cache.find(key);
+        if (it == s->graph_cache.end()) {
+            // capture on a side stream so that the caller's stream state is untouched
+            cudaStream_t cs;
+            CU_TRY(cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking));
+            const uint64_t launches_before = s->n_launch;
+            CU_TRY(cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal));
+            int r = enqueue_forward(s, kv, sl, in, B, S, causal, out, tok, margin, with_tail, cs);
+            if (r == 0 && with_tail) r = enqueue_tail(s, B, tok, margin, cs);
+            cudaGraph_t graph = nullptr;
+            cudaError_t ce = cudaStreamEndCapture(cs, &graph);
+            s->n_launch = launches_before;
+            if (r != 0 || ce != cudaSuccess || graph == nullptr) {
+                cudaGetLastError();
+                cudaStreamDestroy(cs);
+                if (r != 0) return r;
+                return fail(B200_ECUDA, "[ERROR] CUDA graph capture failed: %s", cudaGetErrorString(ce));
+            }
+            cudaGraphExec_t exec = nullptr;
+            ce = cudaGraphInstantiate(&exec, graph, 0);
+            cudaGraphDestroy(graph);
+            cudaStreamDestroy(cs);
+            if (ce != cudaSuccess) return fail(B200_ECUDA, "[ERROR] cudaGraphInstantiate failed: %s", cudaGetErrorString(ce));
+            it = s->graph_cache.emplace(key, exec).first;
+        }
+        CU_TRY(cudaGraphLaunch(it->second, st));
+        s->n_launch += 3 + (uint64_t)s->cfg.n_layers * 6 + (out ? 1 : 0) + (with_tail ? 3 : 0);
+        done = true;
+    }
+    if (!done) {
+        TRY(enqueue_forward(s, kv, sl, in, B, S, causal, out, tok, margin, with_tail, st));
+        if (with_tail) TRY(enqueue_tail(s, B, tok, margin, st));
+        CU_TRY(cudaGetLastError());
+    }
+    for (int b = 0; b < B; ++b) {  // host mirror of what kv_alloc_kernel does on the device
+        const int slot = sl.v[b];
+        const int need = (kv->h_len[slot] + S + kv->dev.page_size - 1) / kv->dev.page_size;
+        if (need > kv->h_pages[slot]) { kv->h_free -= need - kv->h_pages[slot]; kv->h_pages[slot] = need; }
+        kv->h_len[slot] += S;
+    }
+    return 0;
+}
+
+extern "C" B200_API int b200_shard_forward(b200_shard_t* s, b200_kv_t* kv, const int32_t* h_slots, const void* in, int B, int S,
+                                  int causal, void* out, void* stream) {
+    if (out == nullptr) return fail(B200_EINVAL, "[ERROR] null output");
+    return forward_impl(s, kv, h_slots, in, B, S, causal, out, nullptr, nullptr, false, stream);
+}
+extern "C" B200_API int b200_shard_forward_argmax(b200_shard_t* s, b200_kv_t* kv, const int32_t* h_slots, const void* in, int B, int S,
+                                         int causal, void* out, int64_t* tok, float* margin, void* stream) {
+    return forward_impl(s, kv, h_slots, in, B, S, causal, out, tok, margin, true, stream);
+}
+extern "C" B200_API int b200_shard_lm_head_argmax(b200_shard_t* s, const void* hidden, int B, int S, int64_t* tok, float* margin,
+                                         void* stream) {
+    if (s == nullptr || hidden == nullptr || tok == nullptr) return fail(B200_EINVAL, "[ERROR] null argument");
+    if (!s->cfg.has_lm_head || s->lm_head == nullptr) return fail(B200_ESTATE, "[ERROR] this shard does not hold the lm_head");
+    if (B < 1 || B > s->cfg.max_batch || S < 1) return fail(B200_EINVAL, "[ERROR] bad batch / seq_len");
+    CU_TRY(cudaSetDevice(s->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    launch_lastrow_bf16_to_f32(reinterpret_cast<const __nv_bfloat16*>(hidden), B, S, s->cfg.hidden_size, s->lastrow, st);
+    s->n_launch += 1;
+    TRY(enqueue_tail(s, B, tok, margin, st));
+    CU_TRY(cudaGetLastError());
+    s->n_bytes += (uint64_t)s->cfg.vocab_size * s->cfg.hidden_size * 2;
+    return 0;
+}
+extern "C" B200_API int b200_shard_embed(b200_shard_t* s, const int64_t* ids, int n, void* out, void* stream) {
+    if (s == nullptr || ids == nullptr || out == nullptr) return fail(B200_EINVAL, "[ERROR] null argument");
+    if (!s->cfg.has_embedding || s->embedding == nullptr)
+        return fail(B200_ESTATE, "[ERROR] this node does not have embedding layer while receiving user request.");
+    CU_TRY(cudaSetDevice(s->device));
+    launch_embed(s->embedding, ids, n, s->cfg.hidden_size, s->cfg.vocab_size, reinterpret_cast<__nv_bfloat16*>(out), (cudaStream_t)stream);
+    CU_TRY(cudaGetLastError());
+    s->n_launch += 1;
+    return 0;
+}
+
+extern "C" B200_API int b200_shard_counters(const b200_shard_t* s, uint64_t h_out[4]) {
+    if (s == nullptr || h_out == nullptr) return fail(B200_EINVAL, "[ERROR] null argument");
+    h_out[0] = s->n_launch; h_out[1] = s->n_bytes; h_out[2] = s->n_flops; h_out[3] = s->n_calls;
+    return 0;
+}
+extern "C" B200_API int b200_shard_reset_counters(b200_shard_t* s) {
+    if (s == nullptr) return fail(B200_EINVAL, "[ERROR] null shard");
+    s->n_launch = s->n_bytes = s->n_flops = s->n_calls = 0;
+    return 0;
+}
+extern "C" B200_API int b200_shard_set_graphs(b200_shard_t* s, int enabled) {
+    if (s == nullptr) return fail(B200_EINVAL, "[ERROR] null shard");
+    s->graphs = enabled != 0;
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------- hop
+struct b200_hop {
+    int device = 0, n_slots = 0;
+    int64_t slot_bytes = 0;
+    char* local = nullptr;       // [n_slots][slot_bytes] then flags[n_slots] (uint64)
+    char* peer = nullptr;        // mapped mailbox of the next node
+    bool peer_ipc = false;
+    unsigned int* counter = nullptr;
+    int* err = nullptr;
+    int n_slots_peer = 0;
+    int64_t slot_bytes_peer = 0;
+};
+struct HopHandle {  // exactly B200_HOP_HANDLE_BYTES
+    cudaIpcMemHandle_t ipc;  // 64 bytes, valid across processes
+    char* raw;               // valid inside the exporting process
+    uint64_t has_ipc;
+};
+static_assert(sizeof(HopHandle) == B200_HOP_HANDLE_BYTES, "handle size");
+
+extern "C" B200_API int b200_hop_create(int device, int n_ring_slots, int64_t slot_bytes, b200_hop_t** out) {
+    if (out == nullptr || n_ring_slots < 1 || slot_bytes < 16) return fail(B200_EINVAL, "[ERROR] bad hop arguments");
+    CU_TRY(cudaSetDevice(device));
+    b200_hop* h = new b200_hop();
+    h->device = device;
+    h->n_slots = n_ring_slots;
+    h->slot_bytes = (slot_bytes + 255) / 256 * 256;
+    const size_t total = (size_t)h->n_slots * h->slot_bytes + (size_t)h->n_slots * 8 + 256;
+    cudaError_t e = cudaMalloc(&h->local, total);
+    if (e != cudaSuccess) { cudaGetLastError(); delete h; return fail(B200_ENOMEM, "[ERROR] CUDA out of memory for the hop mailbox"); }
+    cudaMemset(h->local, 0, total);
+    cudaMalloc(&h->counter, 256);
+    cudaMemset(h->counter, 0, 256);
+    h->err = reinterpret_cast<int*>(reinterpret_cast<char*>(h->counter) + 128);
+    CU_TRY(cudaDeviceSynchronize());
+    *out = h;
+    return 0;
+}
+extern "C" B200_API int b200_hop_export(b200_hop_t* h, void* handle_out) {
+    if (h == nullptr || handle_out == nullptr) return fail(B200_EINVAL, "[ERROR] null argument");
+    CU_TRY(cudaSetDevice(h->device));
+    HopHandle hh;
+    memset(&hh, 0, sizeof(hh));
+    cudaError_t e = cudaIpcGetMemHandle(&hh.ipc, h->local);
+    hh.has_ipc = (e == cudaSuccess) ? 1 : 0;
+    if (e != cudaSuccess) cudaGetLastError();  // still usable inside one process through `raw`
+    hh.raw = h->local;
+    memcpy(handle_out, &hh, sizeof(hh));
+    return 0;
+}
+extern "C" B200_API int b200_hop_connect(b200_hop_t* h, const void* peer_handle, int peer_device, int same_process) {
+    if (h == nullptr || peer_handle == nullptr) return fail(B200_EINVAL, "[ERROR] null argument");
+    CU_TRY(cudaSetDevice(h->device));
+    if (h->peer != nullptr && h->peer_ipc) { cudaIpcCloseMemHandle(h->peer); h->peer = nullptr; }
+    if (same_process) {
+        HopHandle hh;
+        memcpy(&hh, peer_handle, sizeof(hh));
+        char* raw = hh.raw;
+        if (peer_device != h->device) {
+            int can = 0;
+            CU_TRY(cudaDeviceCanAccessPeer(&can, h->device, peer_device));
+            if (!can) return fail(B200_ECUDA, "[ERROR] GPU %d cannot map GPU %d's memory", h->device, peer_device);
+            cudaError_t e = cudaDeviceEnablePeerAccess(peer_device, 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) CU_TRY(e);
+            cudaGetLastError();
+        }
+        h->peer = raw;
+        h->peer_ipc = false;
+    } else {
+        HopHandle hh;
+        memcpy(&hh, peer_handle, sizeof(hh));
+        if (!hh.has_ipc) return fail(B200_ECUDA, "[ERROR] the peer could not export a CUDA IPC handle");
+        void* p = nullptr;
+        CU_TRY(cudaIpcOpenMemHandle(&p, hh.ipc, cudaIpcMemLazyEnablePeerAccess));
+        h->peer = reinterpret_cast<char*>(p);
+        h->peer_ipc = true;
+    }
+    return 0;
+}
+extern "C" B200_API int b200_hop_send(b200_hop_t* h, const void* payload, int64_t bytes, uint64_t seq, void* stream) {
+    if (h == nullptr || h->peer == nullptr) return fail(B200_ESTATE, "[ERROR] hop has no connected peer");
+    if (bytes < 0 || bytes > h->slot_bytes) return fail(B200_EINVAL, "[ERROR] hop payload of %lld bytes exceeds the slot (%lld)", (long long)bytes, (long long)h->slot_bytes);
+    CU_TRY(cudaSetDevice(h->device));
+    const int slot = (int)(seq % (uint64_t)h->n_slots);
+    char* pslot = h->peer + (size_t)slot * h->slot_bytes;
+    uint64_t* pflag = reinterpret_cast<uint64_t*>(h->peer + (size_t)h->n_slots * h->slot_bytes) + slot;
+    launch_hop_send(payload, bytes, pslot, pflag, seq, h->counter, (cudaStream_t)stream);
+    CU_TRY(cudaGetLastError());
+    return 0;
+}
+extern "C" B200_API int b200_hop_recv(b200_hop_t* h, void* out, int64_t bytes, uint64_t seq, int64_t max_wait_us, void* stream) {
+    if (h == nullptr || out == nullptr) return fail(B200_EINVAL, "[ERROR] null argument");
+    if (bytes < 0 || bytes > h->slot_bytes) return fail(B200_EINVAL, "[ERROR] hop payload exceeds the slot");
+    CU_TRY(cudaSetDevice(h->device));
+    const int slot = (int)(seq % (uint64_t)h->n_slots);
+    const char* lslot = h->local + (size_t)slot * h->slot_bytes;
+    const uint64_t* lflag = reinterpret_cast<const uint64_t*>(h->local + (size_t)h->n_slots * h->slot_bytes) + slot;
+    launch_hop_recv(out, bytes, lslot, lflag, seq, max_wait_us * 2000 /* ~2 GHz */, h->err, (cudaStream_t)stream);
+    CU_TRY(cudaGetLastError());
+    return 0;
+}
+extern "C" B200_API int b200_hop_error(b200_hop_t* h) {
+    if (h == nullptr) return 0;
+    int v = 0;
+    cudaSetDevice(h->device);
+    cudaMemcpy(&v, h->err, sizeof(int), cudaMemcpyDeviceToHost);
+    return v;
+}
+extern "C" B200_API int b200_hop_destroy(b200_hop_t* h) {
+    if (h == nullptr) return 0;
+    cudaSetDevice(h->device);
+    cudaDeviceSynchronize();
+    if (h->peer != nullptr && h->peer_ipc) cudaIpcCloseMemHandle(h->peer);
+    cudaFree(h->local);
+    cudaFree(h->counter);
+    delete h;
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------- single kernels
+extern "C" B200_API int b200_rmsnorm(const float* x, const void* w, float eps, int rows, int n, void* out, void* stream) {
+    if (x == nullptr || out == nullptr || rows < 1 || n < 8 || n % 8 != 0) return fail(B200_EINVAL, "[ERROR] bad rmsnorm arguments");
+    launch_rmsnorm_bf16(x, reinterpret_cast<const __nv_bfloat16*>(w), eps, rows, n, reinterpret_cast<__nv_bfloat16*>(out), (cudaStream_t)stream);
+    CU_TRY(cudaGetLastError());
+    return 0;
+}
+extern "C" B200_API int b200_gemm_bf16(const void* a, const void* w, int M, int N, int K, float* out, void* stream) {
+    if (a == nullptr || w == nullptr || out == nullptr) return fail(B200_EINVAL, "[ERROR] null argument");
+    GemmParams g{reinterpret_cast<const __nv_bfloat16*>(a), reinterpret_cast<const __nv_bfloat16*>(w), M, N, K, out, GEMM_STORE_F32};
+    if (launch_gemm(g, (cudaStream_t)stream) != 0) return fail(B200_EINVAL, "[ERROR] %s", gemm_error());
+    CU_TRY(cudaGetLastError());
+    return 0;
+}
+extern "C" B200_API int b200_gemv_bf16(const float* x, const void* w, int M, int N, int K, float* out, void* stream) {
+    if (x == nullptr || w == nullptr || out == nullptr) return fail(B200_EINVAL, "[ERROR] null argument");
+    if (M < 1 || M > kMaxGemvRows || K % 8 != 0 || (size_t)M * (((size_t)K / 8 + 31) / 32) * 1024 > 220 * 1024)
+        return fail(B200_EINVAL, "[ERROR] gemv: need 1 <= M <= %d, K %% 8 == 0 and M*K*4 bytes of shared memory", kMaxGemvRows);
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    GemvParams g{};
+    g.W = reinterpret_cast<const __nv_bfloat16*>(w); g.x = x; g.N = N; g.K = K; g.out = out;
+    launch_gemv(g, M, EPI_STORE, false, sms, (cudaStream_t)stream);
+    CU_TRY(cudaGetLastError());
+    return 0;
+}

@@ -1,0 +1,284 @@
+// Dense projection GEMMs of the shard path for more than a handful of token rows (prefill and
+// batched decode): C[M,N] = A[M,K] * W[N,K]^T, bf16 operands, fp32 accumulation in tensor memory.
+// Replaces the cuBLAS GEMMs under q/k/v/o_proj (transformers modeling_llama.py:262-264,287-288)
+// and gate/up/down_proj (:182-184) that the reference reaches from utils/shard_loader.py:66-74.
+//
+// sm_100a design: one CTA per 128x128 output tile; warp 0 = TMA producer (cp.async.bulk.tensor,
+// 128B-swizzled 128x64 tiles of A and W through a 6-stage mbarrier ring), warp 1 = single-thread
+// tcgen05.mma issuer (UMMA 128x128x16, accumulator = 128 TMEM columns), warps 2..5 = epilogue
+// (tcgen05.ld 32x32b, one accumulator row per thread) with the fused epilogues:
+//   STORE_BF16 (QKV), RESID_F32 (o_proj / down_proj + residual add, modeling_llama.py:325,331),
+//   SWIGLU_BF16 (silu(gate)*up on the paired gate/up weight layout, :183), STORE_F32 (lm_head).
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "common.cuh"
+#include "internal.h"
+
+namespace b200 {
+
+constexpr int kBlkM = 128, kBlkN = 128, kBlkK = 64, kStages = 6;
+constexpr int kGemmThreads = 192;
+constexpr uint32_t kStageBytesA = kBlkM * kBlkK * 2, kStageBytesB = kBlkN * kBlkK * 2;
+constexpr uint32_t kStageBytes = kStageBytesA + kStageBytesB;
+constexpr uint32_t kTmemCols = 128;
+constexpr size_t kGemmSmem = 1024 /*align slack*/ + (size_t)kStages * kStageBytes + 256 /*barriers*/;
+
+__device__ __forceinline__ uint32_t s_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+// bounded spin: a protocol bug must surface as a launch failure, never as a hung GPU
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t done = 0;
+    for (uint32_t spin = 0; !done; ++spin) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+        if (!done && spin > (1u << 26)) __trap();
+    }
+}
+__device__ __forceinline__ void tma_load_2d(const CUtensorMap* map, uint32_t bar, uint32_t dst, int x, int y) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(dst), "l"(map), "r"(bar), "r"(x), "r"(y) : "memory");
+}
+// K-major operand tile, 128-byte swizzle, rows of 64 bf16 (=128 B); 8-row groups are 1024 B apart
+__device__ __forceinline__ uint64_t umma_desc(uint32_t smem_addr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);   // start address
+    d |= (uint64_t)1 << 16;                       // leading byte offset (unused for swizzled K-major)
+    d |= (uint64_t)(1024 >> 4) << 32;             // stride byte offset
+    d |= (uint64_t)1 << 46;                       // descriptor version (sm_100)
+    d |= (uint64_t)2 << 61;                       // SWIZZLE_128B
+    return d;
+}
+// kind::f16 instruction descriptor: D=f32, A=B=bf16, both K-major, N=128, M=128
+constexpr uint32_t kIdesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(kBlkN >> 3) << 17) | ((uint32_t)(kBlkM >> 4) << 24);
+
+__device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accum) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(accum) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+          "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+          "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+template <int EPI>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
+                    const GemmParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t raw = s_u32(smem_raw);
+    const uint32_t base = (raw + 1023u) & ~1023u;  // SWIZZLE_128B tiles need 1024-byte alignment
+    uint8_t* gen_base = smem_raw + (base - raw);
+    const uint32_t bars = base + kStages * kStageBytes;
+    const uint32_t full0 = bars, empty0 = bars + 8 * kStages, tmem_full = bars + 16 * kStages;
+    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(gen_base + kStages * kStageBytes + 16 * kStages + 8);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int n_blk = blockIdx.x, m_blk = blockIdx.y;
+    const int num_k = (p.K + kBlkK - 1) / kBlkK;
+
+    if (warp == 0 && lane == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_a) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_b) : "memory");
+        for (int i = 0; i < kStages; ++i) { mbar_init(full0 + 8 * i, 1); mbar_init(empty0 + 8 * i, 1); }
+        mbar_init(tmem_full, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(s_u32((const void*)tmem_slot)), "n"(kTmemCols) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {  // ===== TMA producer
+            for (int kb = 0; kb < num_k; ++kb) {
+                const int st = kb % kStages;
+                const uint32_t ph = (uint32_t)(kb / kStages) & 1u;
+                mbar_wait(empty0 + 8 * st, ph ^ 1u);
+                mbar_expect_tx(full0 + 8 * st, kStageBytes);
+                const uint32_t sa = base + st * kStageBytes, sb = sa + kStageBytesA;
+                tma_load_2d(&tma_a, full0 + 8 * st, sa, kb * kBlkK, m_blk * kBlkM);
+                tma_load_2d(&tma_b, full0 + 8 * st, sb, kb * kBlkK, n_blk * kBlkN);
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {  // ===== MMA issuer (one thread drives the tensor core for the CTA)
+            for (int kb = 0; kb < num_k; ++kb) {
+                const int st = kb % kStages;
+                const uint32_t ph = (uint32_t)(kb / kStages) & 1u;
+                mbar_wait(full0 + 8 * st, ph);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint32_t sa = base + st * kStageBytes, sb = sa + kStageBytesA;
+#pragma unroll
+                for (int k = 0; k < kBlkK / 16; ++k)
+                    umma_f16(tmem_base, umma_desc(sa + k * 32), umma_desc(sb + k * 32), kIdesc, (kb > 0 || k > 0) ? 1u : 0u);
+                umma_commit(empty0 + 8 * st);  // frees the smem slot when these MMAs retire
+            }
+            umma_commit(tmem_full);            // accumulator complete
+        }
+    } else {  // ===== epilogue: warp w may only touch TMEM lanes 32*(w%4) .. +31
+        mbar_wait(tmem_full, 0);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const int quad = warp & 3;
+        const int row = m_blk * kBlkM + quad * 32 + lane;
+        const uint32_t trow = tmem_base + ((uint32_t)(quad * 32) << 16);
+        const bool row_ok = row < p.M;
+        if (EPI == GEMM_SWIGLU_BF16) {
+            __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(p.out);
+            const int No = p.N / 2;
+#pragma unroll 1
+            for (int c = 0; c < 2; ++c) {
+                uint32_t g[32], u[32];
+                tmem_ld32(trow + c * 32, g);
+                tmem_ld32(trow + 64 + c * 32, u);
+                const int col0 = n_blk * 64 + c * 32;
+                if (row_ok) {
+#pragma unroll
+                    for (int v = 0; v < 4; ++v) {
+                        if (col0 + v * 8 < No) {
+                            uint32_t w[4];
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) {
+                                const float g0 = __uint_as_float(g[v * 8 + 2 * e]), g1 = __uint_as_float(g[v * 8 + 2 * e + 1]);
+                                const float u0 = __uint_as_float(u[v * 8 + 2 * e]), u1 = __uint_as_float(u[v * 8 + 2 * e + 1]);
+                                w[e] = pack_bf16(silu(g0) * u0, silu(g1) * u1);
+                            }
+                            *reinterpret_cast<uint4*>(out + (size_t)row * No + col0 + v * 8) = make_uint4(w[0], w[1], w[2], w[3]);
+                        }
+                    }
+                }
+            }
+        } else {
+#pragma unroll 1
+            for (int c = 0; c < kBlkN / 32; ++c) {
+                uint32_t r[32];
+                tmem_ld32(trow + c * 32, r);
+                const int col0 = n_blk * kBlkN + c * 32;
+                if (row_ok) {
+                    if (EPI == GEMM_STORE_BF16) {
+                        __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(p.out) + (size_t)row * p.N + col0;
+#pragma unroll
+                        for (int v = 0; v < 4; ++v)
+                            if (col0 + v * 8 < p.N)
+                                *reinterpret_cast<uint4*>(out + v * 8) = make_uint4(
+                                    pack_bf16(__uint_as_float(r[v * 8 + 0]), __uint_as_float(r[v * 8 + 1])),
+                                    pack_bf16(__uint_as_float(r[v * 8 + 2]), __uint_as_float(r[v * 8 + 3])),
+                                    pack_bf16(__uint_as_float(r[v * 8 + 4]), __uint_as_float(r[v * 8 + 5])),
+                                    pack_bf16(__uint_as_float(r[v * 8 + 6]), __uint_as_float(r[v * 8 + 7])));
+                    } else {
+                        float* out = reinterpret_cast<float*>(p.out) + (size_t)row * p.N + col0;
+#pragma unroll
+                        for (int v = 0; v < 8; ++v)
+                            if (col0 + v * 4 < p.N) {
+                                float4 acc = make_float4(__uint_as_float(r[v * 4 + 0]), __uint_as_float(r[v * 4 + 1]),
+                                                         __uint_as_float(r[v * 4 + 2]), __uint_as_float(r[v * 4 + 3]));
+                                if (EPI == GEMM_RESID_F32) {
+                                    const float4 o = *reinterpret_cast<const float4*>(out + v * 4);
+                                    acc.x += o.x; acc.y += o.y; acc.z += o.z; acc.w += o.w;
+                                }
+                                *reinterpret_cast<float4*>(out + v * 4) = acc;
+                            }
+                    }
+                }
+            }
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    }
+    __syncthreads();
+    if (warp == 1) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(kTmemCols) : "memory");
+    }
+}
+
+// ---- host side: tensor maps through the driver entry point (no link-time libcuda dependency)
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn g_encode = nullptr;
+static thread_local char g_gemm_err[256] = "";
+const char* gemm_error() { return g_gemm_err; }
+
+static int make_map(CUtensorMap* map, const void* ptr, int rows, int K, int box_rows) {
+    if (g_encode == nullptr) {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q);
+        if (e != cudaSuccess || fn == nullptr) {
+            snprintf(g_gemm_err, sizeof(g_gemm_err), "cuTensorMapEncodeTiled entry point unavailable: %s", cudaGetErrorString(e));
+            return -1;
+        }
+        g_encode = reinterpret_cast<EncodeTiledFn>(fn);
+    }
+    const cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)rows};
+    const cuuint64_t strides[1] = {(cuuint64_t)K * 2};
+    const cuuint32_t box[2] = {(cuuint32_t)kBlkK, (cuuint32_t)box_rows};
+    const cuuint32_t estr[2] = {1, 1};
+    CUresult r = g_encode(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        snprintf(g_gemm_err, sizeof(g_gemm_err), "cuTensorMapEncodeTiled failed (%d) rows=%d K=%d ptr=%p", (int)r, rows, K, ptr);
+        return -1;
+    }
+    return 0;
+}
+
+int launch_gemm(const GemmParams& p, cudaStream_t st) {
+    if (p.K % 8 != 0 || p.N % 8 != 0 || p.M <= 0) {
+        snprintf(g_gemm_err, sizeof(g_gemm_err), "gemm: need K%%8==0, N%%8==0, M>0 (M=%d N=%d K=%d)", p.M, p.N, p.K);
+        return -1;
+    }
+    if (p.epi == GEMM_SWIGLU_BF16 && p.N % 128 != 0) {
+        snprintf(g_gemm_err, sizeof(g_gemm_err), "gemm swiglu: packed N must be a multiple of 128 (N=%d)", p.N);
+        return -1;
+    }
+    CUtensorMap ma, mb;
+    if (make_map(&ma, p.A, p.M, p.K, kBlkM) != 0) return -1;
+    if (make_map(&mb, p.W, p.N, p.K, kBlkN) != 0) return -1;
+    dim3 grid((p.N + kBlkN - 1) / kBlkN, (p.M + kBlkM - 1) / kBlkM);
+#define B200_GEMM_LAUNCH(E)                                                                                 \
+    {                                                                                                       \
+        auto kfn = gemm_tcgen05_kernel<E>;                                                                  \
+        cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGemmSmem);             \
+        kfn<<<grid, kGemmThreads, kGemmSmem, st>>>(ma, mb, p);                                              \
+    }
+    switch (p.epi) {
+        case GEMM_STORE_BF16: B200_GEMM_LAUNCH(GEMM_STORE_BF16) break;
+        case GEMM_RESID_F32: B200_GEMM_LAUNCH(GEMM_RESID_F32) break;
+        case GEMM_SWIGLU_BF16: B200_GEMM_LAUNCH(GEMM_SWIGLU_BF16) break;
+        default: B200_GEMM_LAUNCH(GEMM_STORE_F32) break;
+    }
+#undef B200_GEMM_LAUNCH
+    return 0;
+}
+
+}  // namespace b200

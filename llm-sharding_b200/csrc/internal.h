@@ -1,0 +1,140 @@
+// Host-side launcher prototypes shared between api.cu and the kernel translation units.
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+
+namespace b200 {
+
+constexpr int kMaxBatch = 64;
+constexpr int kMaxGemvRows = 4;   // token rows served by the weight-streaming SIMT kernels
+constexpr int kMaxSplits = 16;    // split-K factor bound of decode attention
+constexpr int kMaxChunkKeys = 8192;  // keys one decode-attention CTA may hold scores for
+struct SlotList { int32_t v[kMaxBatch]; };
+struct InvFreq { float v[64]; };  // RoPE inverse frequencies, head_dim/2 entries
+
+// ---- KV bookkeeping living in device memory (graph-replayable: nothing host-baked) -----
+struct KvDev {
+    int32_t* seq_lens;     // [max_slots] committed length per slot
+    int32_t* block_table;  // [max_slots][max_pages_per_slot] page ids (-1 = none)
+    int32_t* pages_held;   // [max_slots]
+    int32_t* free_stack;   // [n_pages]
+    int32_t* free_top;     // [1] number of free pages
+    int32_t* error;        // [1] sticky: 1 = pool exhausted, 2 = slot overflow
+    int32_t max_slots, max_pages_per_slot, n_pages, page_size;
+};
+
+// per-call token metadata (device arrays sized max_tokens / max_batch)
+struct TokMeta {
+    int32_t* call_base;  // [B] cached length of row b before this call
+    int32_t* pos;        // [M] absolute position of token m
+    int32_t* t_end;      // [M] number of keys token m attends to
+    int64_t* kv_off;     // [M] element offset of (token, kv head 0) inside one layer's K (or V) pool
+    float* cos;          // [M][64]
+    float* sin;          // [M][64]
+};
+
+enum GemvEpi { EPI_STORE = 0, EPI_RESID = 1, EPI_QKV = 2, EPI_SWIGLU = 3 };
+
+struct GemvParams {
+    const __nv_bfloat16* W;  // [N,K] row-major
+    const float* x;          // [M,K] fp32
+    const __nv_bfloat16* norm_w;  // [K] (NORM prologue) or nullptr
+    float eps;
+    int N, K;
+    float* out;              // STORE: [M,N]; RESID: [M,N] += ; SWIGLU: [M,N/2]
+    // QKV epilogue
+    float* q_out;            // [M, n_heads*128]
+    __nv_bfloat16* k_pool;   // this layer's K pool base
+    __nv_bfloat16* v_pool;
+    const int64_t* kv_off;
+    const float* cos;
+    const float* sin;
+    int n_heads, n_kv;
+    int64_t head_stride;     // page_size*128 elements between kv heads inside a page
+};
+void launch_gemv(const GemvParams& p, int M, int epi, bool norm, int num_sms, cudaStream_t st);
+
+void launch_kv_alloc(const KvDev& kv, const SlotList& slots, int B, int S, int32_t* call_base, cudaStream_t st);
+void launch_kv_reset(const KvDev& kv, int slot, cudaStream_t st);
+void launch_kv_init(const KvDev& kv, cudaStream_t st);
+void launch_prep(const KvDev& kv, const SlotList& slots, int B, int S, int causal, const InvFreq& inv, int n_kv,
+                 const TokMeta& tm, cudaStream_t st);
+
+void launch_load_residual(const __nv_bfloat16* in, float* x, int64_t n, cudaStream_t st);
+// x fp32 [rows,n] -> bf16; norm_w == nullptr: plain convert
+void launch_rmsnorm_bf16(const float* x, const __nv_bfloat16* norm_w, float eps, int rows, int n,
+                         __nv_bfloat16* out, cudaStream_t st);
+// last-row gather + optional norm, fp32 out [B,n] (input rows b*S+S-1)
+void launch_lastrow_norm_f32(const float* x, const __nv_bfloat16* norm_w, float eps, int B, int S, int n,
+                             float* out, cudaStream_t st);
+void launch_lastrow_bf16_to_f32(const __nv_bfloat16* h, int B, int S, int n, float* out, cudaStream_t st);
+void launch_argmax(const float* logits, int B, int V, int64_t* tok, float* margin, cudaStream_t st);
+void launch_embed(const __nv_bfloat16* table, const int64_t* ids, int n, int H, int V, __nv_bfloat16* out,
+                  cudaStream_t st);
+void launch_convert_to_bf16(const void* src, int dtype, __nv_bfloat16* dst, int64_t n, cudaStream_t st);
+// dst rows [dst_row0 + (r/64)*128 + half*64 + r%64] <- src row r (gate: half 0, up: half 1)
+void launch_pack_gate_up(const void* src, int dtype, __nv_bfloat16* dst, int rows, int cols, int half,
+                         cudaStream_t st);
+
+struct AttnDecodeParams {
+    const float* q;            // [M, n_heads*128] fp32 (rope applied)
+    const __nv_bfloat16* k_pool;
+    const __nv_bfloat16* v_pool;
+    const int32_t* block_table;  // [max_slots][max_pages_per_slot]
+    const int32_t* t_end;      // [M]
+    SlotList slots;            // row b -> slot
+    int S;                     // tokens per row (m = b*S + s)
+    int n_heads, n_kv, page_size, max_pages_per_slot, n_splits;
+    float* part;               // scratch [M][n_heads][n_splits][130]
+    float* out;                // [M, n_heads*128] fp32
+};
+void launch_attn_decode(const AttnDecodeParams& p, int M, cudaStream_t st);
+
+struct RopeAppendParams {
+    const __nv_bfloat16* qkv;  // [M, (n_heads+2*n_kv)*128]
+    __nv_bfloat16* q_out;      // [M, n_heads*128]
+    __nv_bfloat16* k_pool;
+    __nv_bfloat16* v_pool;
+    const int64_t* kv_off;
+    const float* cos;
+    const float* sin;
+    int n_heads, n_kv;
+    int64_t head_stride;
+};
+void launch_rope_append(const RopeAppendParams& p, int M, cudaStream_t st);
+
+struct AttnPrefillParams {
+    const __nv_bfloat16* q;    // [B*S, n_heads*128] bf16 (rope applied)
+    const __nv_bfloat16* k_pool;
+    const __nv_bfloat16* v_pool;
+    const int32_t* block_table;
+    const int32_t* call_base;  // [B]
+    SlotList slots;
+    int B, S, causal;
+    int n_heads, n_kv, page_size, max_pages_per_slot;
+    __nv_bfloat16* out;        // [B*S, n_heads*128]
+};
+void launch_attn_prefill(const AttnPrefillParams& p, cudaStream_t st);
+
+// tcgen05 GEMM: C[M,N] = A[M,K] * W[N,K]^T with fused epilogues
+enum GemmEpi { GEMM_STORE_BF16 = 0, GEMM_RESID_F32 = 1, GEMM_SWIGLU_BF16 = 2, GEMM_STORE_F32 = 3 };
+struct GemmParams {
+    const __nv_bfloat16* A;  // [M,K]
+    const __nv_bfloat16* W;  // [N,K]
+    int M, N, K;
+    void* out;               // STORE_BF16: bf16 [M,N]; RESID_F32: fp32 [M,N] +=; SWIGLU: bf16 [M,N/2]; STORE_F32
+    int epi;
+};
+// returns cudaError-like int (0 ok); message via get_gemm_error()
+int launch_gemm(const GemmParams& p, cudaStream_t st);
+const char* gemm_error();
+
+// hop
+// payload == nullptr: the payload was already written in place; only publish the flag
+void launch_hop_send(const void* payload, int64_t bytes, void* peer_slot, uint64_t* peer_flag, uint64_t seq,
+                     unsigned int* counter, cudaStream_t st);
+void launch_hop_recv(void* out, int64_t bytes, const void* local_slot, const uint64_t* local_flag, uint64_t seq,
+                     int64_t max_wait_cycles, int* err, cudaStream_t st);
+
+}  // namespace b200

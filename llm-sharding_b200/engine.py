@@ -1,0 +1,201 @@
+"""Thin object wrappers over the C ABI: ``Shard`` (weights + workspace of one layer range) and
+``PagedKVCache`` (what ``NodeWorker.past_key_value`` holds instead of a ``DynamicCache``,
+utils/node_worker.py:98,184).  Device memory handed in/out is plain torch tensors; torch is the
+allocator and the stream provider, the kernels are the library's."""
+from __future__ import annotations
+
+import ctypes as C
+import json
+import os
+
+import torch
+
+from . import _lib
+
+LAYER_KEYS = (  # LlamaDecoderLayer.state_dict() keys as saved in block_{i}.pth (utils/model_sharder.py:77-79)
+    "self_attn.q_proj.weight", "self_attn.k_proj.weight", "self_attn.v_proj.weight", "self_attn.o_proj.weight",
+    "mlp.gate_proj.weight", "mlp.up_proj.weight", "mlp.down_proj.weight",
+    "input_layernorm.weight", "post_attention_layernorm.weight",
+)
+
+
+def read_model_config(shards_path: str) -> dict:
+    """The fields of config.json the path needs (what LlamaConfig.from_pretrained(shards_path)
+    supplies at utils/shard_loader.py:35 and utils/node_worker.py:88)."""
+    with open(os.path.join(shards_path, "config.json")) as f:
+        c = json.load(f)
+    n_heads = c["num_attention_heads"]
+    rope = c.get("rope_parameters") or {}
+    scaling = c.get("rope_scaling") or ({} if rope.get("rope_type", "default") == "default" else rope)
+    if scaling and scaling.get("rope_type", scaling.get("type", "default")) != "default":
+        raise ValueError("[ERROR] only the default RoPE parametrisation is built (no llama3 / yarn scaling yet)")
+    return {
+        "hidden_size": c["hidden_size"], "intermediate_size": c["intermediate_size"],
+        "num_hidden_layers": c["num_hidden_layers"], "num_attention_heads": n_heads,
+        "num_key_value_heads": c.get("num_key_value_heads") or n_heads,
+        "head_dim": c.get("head_dim") or c["hidden_size"] // n_heads,
+        "vocab_size": c["vocab_size"], "rms_norm_eps": c.get("rms_norm_eps", 1e-6),
+        "rope_theta": float(rope.get("rope_theta", c.get("rope_theta", 10000.0))),
+        "max_position_embeddings": c.get("max_position_embeddings", 4096),
+    }
+
+
+class Shard:
+    def __init__(self, model_cfg: dict, n_layers: int, device: torch.device, *, has_final_norm=False, has_lm_head=False,
+                 has_embedding=False, max_tokens=4096, max_batch=1):
+        _lib.require_cuda()
+        self.lib = _lib.load()
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise RuntimeError("[ERROR] the B200 shard path runs on CUDA devices only (no CPU fallback)")
+        self.dev_index = self.device.index if self.device.index is not None else torch.cuda.current_device()
+        self.model_cfg = dict(model_cfg)
+        self.n_layers = n_layers
+        self.hidden_size = model_cfg["hidden_size"]
+        self.vocab_size = model_cfg["vocab_size"]
+        self.has_final_norm, self.has_lm_head, self.has_embedding = has_final_norm, has_lm_head, has_embedding
+        self.max_tokens, self.max_batch = max_tokens, max_batch
+        cfg = _lib.ShardConfig(
+            model_cfg["hidden_size"], model_cfg["intermediate_size"], model_cfg["num_attention_heads"],
+            model_cfg["num_key_value_heads"], model_cfg["head_dim"], model_cfg["vocab_size"],
+            model_cfg["rms_norm_eps"], model_cfg["rope_theta"], n_layers,
+            int(has_final_norm), int(has_lm_head), int(has_embedding), max_tokens, max_batch)
+        h = C.c_void_p()
+        _lib.check(self.lib.b200_shard_create(C.byref(cfg), self.dev_index, C.byref(h)))
+        self.handle = h
+
+    # ---- weights
+    def _stream(self):
+        return _lib.stream_ptr(self.device)
+
+    def set_layer(self, rel_idx: int, state: dict) -> None:
+        ts = []
+        dts = set()
+        for k in LAYER_KEYS:
+            if k not in state:
+                raise RuntimeError(f"[ERROR] Missing key(s) in state_dict: \"{k}\"")
+            t = state[k].to(self.device).contiguous()
+            dts.add(t.dtype)
+            ts.append(t)
+        if len(dts) != 1 or next(iter(dts)) not in _lib.TORCH_TO_DT:
+            raise ValueError(f"[ERROR] unsupported / mixed weight dtypes {dts}")
+        _lib.check(self.lib.b200_shard_set_layer(self.handle, rel_idx, *[t.data_ptr() for t in ts],
+                                                 _lib.TORCH_TO_DT[ts[0].dtype], self._stream()))
+
+    def _set_single(self, fn, w: torch.Tensor) -> None:
+        t = w.to(self.device).contiguous()
+        if t.dtype not in _lib.TORCH_TO_DT:
+            raise ValueError(f"[ERROR] unsupported weight dtype {t.dtype}")
+        _lib.check(fn(self.handle, t.data_ptr(), _lib.TORCH_TO_DT[t.dtype], self._stream()))
+
+    def set_final_norm(self, w): self._set_single(self.lib.b200_shard_set_final_norm, w)
+    def set_lm_head(self, w): self._set_single(self.lib.b200_shard_set_lm_head, w)
+    def set_embedding(self, w): self._set_single(self.lib.b200_shard_set_embedding, w)
+
+    # ---- compute
+    def new_kv(self, max_slots: int = 1, page_size: int = 64, n_pages: int | None = None, max_seq_len: int = 4096):
+        return PagedKVCache(self, max_slots, page_size, n_pages, max_seq_len)
+
+    def _slots(self, slots, B):
+        if slots is None:
+            slots = list(range(B))
+        if len(slots) != B:
+            raise ValueError("[ERROR] one KV slot per batch row is required")
+        return (C.c_int32 * B)(*slots)
+
+    def forward(self, hidden: torch.Tensor, kv: "PagedKVCache", slots=None, causal: bool = False,
+                out: torch.Tensor | None = None) -> torch.Tensor:
+        """LlamaShardPart.forward: bf16 [B,S,H] -> bf16 [B,S,H]."""
+        hidden = self._check_hidden(hidden)
+        B, S, _ = hidden.shape
+        if out is None:
+            out = torch.empty_like(hidden)
+        _lib.check(self.lib.b200_shard_forward(self.handle, kv.handle, self._slots(slots, B), hidden.data_ptr(), B, S,
+                                               int(causal), out.data_ptr(), self._stream()))
+        return out
+
+    def forward_argmax(self, hidden: torch.Tensor, kv: "PagedKVCache", slots=None, causal: bool = False,
+                       want_hidden: bool = False, want_margin: bool = False):
+        hidden = self._check_hidden(hidden)
+        B, S, _ = hidden.shape
+        out = torch.empty_like(hidden) if want_hidden else None
+        tok = torch.empty(B, dtype=torch.int64, device=self.device)
+        margin = torch.empty(B, dtype=torch.float32, device=self.device) if want_margin else None
+        _lib.check(self.lib.b200_shard_forward_argmax(self.handle, kv.handle, self._slots(slots, B), hidden.data_ptr(), B, S,
+                                                      int(causal), _lib.ptr(out), tok.data_ptr(), _lib.ptr(margin),
+                                                      self._stream()))
+        return tok, out, margin
+
+    def lm_head_argmax(self, hidden: torch.Tensor, want_margin: bool = False):
+        hidden = self._check_hidden(hidden)
+        B, S, _ = hidden.shape
+        tok = torch.empty(B, dtype=torch.int64, device=self.device)
+        margin = torch.empty(B, dtype=torch.float32, device=self.device) if want_margin else None
+        _lib.check(self.lib.b200_shard_lm_head_argmax(self.handle, hidden.data_ptr(), B, S, tok.data_ptr(), _lib.ptr(margin),
+                                                      self._stream()))
+        return tok, margin
+
+    def embed(self, ids: torch.Tensor) -> torch.Tensor:
+        """embed_tokens(ids): int64 [...] -> bf16 [..., H]."""
+        ids = ids.to(device=self.device, dtype=torch.long).contiguous()
+        out = torch.empty(*ids.shape, self.hidden_size, dtype=torch.bfloat16, device=self.device)
+        _lib.check(self.lib.b200_shard_embed(self.handle, ids.data_ptr(), ids.numel(), out.data_ptr(), self._stream()))
+        return out
+
+    def _check_hidden(self, hidden: torch.Tensor) -> torch.Tensor:
+        if hidden.ndim != 3 or hidden.shape[-1] != self.hidden_size:
+            raise ValueError(f"[ERROR] hidden_states must be [B, S, {self.hidden_size}], got {tuple(hidden.shape)}")
+        return hidden.to(device=self.device, dtype=torch.bfloat16).contiguous()
+
+    def counters(self) -> dict:
+        arr = (C.c_uint64 * 4)()
+        _lib.check(self.lib.b200_shard_counters(self.handle, arr))
+        return {"launches": arr[0], "bytes": arr[1], "flops": arr[2], "calls": arr[3]}
+
+    def reset_counters(self): _lib.check(self.lib.b200_shard_reset_counters(self.handle))
+    def set_graphs(self, on: bool): _lib.check(self.lib.b200_shard_set_graphs(self.handle, int(on)))
+
+    def close(self):
+        if getattr(self, "handle", None):
+            self.lib.b200_shard_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class PagedKVCache:
+    """Paged K/V storage of one shard.  Exposes ``get_seq_length()`` like the HF cache so that
+    ``build_position_ids`` (utils/forwarding_utils.py:13-16) keeps working on it."""
+
+    def __init__(self, shard: Shard, max_slots: int = 1, page_size: int = 64, n_pages: int | None = None,
+                 max_seq_len: int = 4096):
+        self.shard = shard
+        self.lib = shard.lib
+        self.max_slots, self.page_size = max_slots, page_size
+        if n_pages is None:
+            n_pages = max_slots * ((max_seq_len + page_size - 1) // page_size)
+        self.n_pages = n_pages
+        h = C.c_void_p()
+        _lib.check(self.lib.b200_kv_create(shard.handle, max_slots, page_size, n_pages, C.byref(h)))
+        self.handle = h
+
+    def get_seq_length(self, slot: int = 0) -> int:
+        return _lib.check(self.lib.b200_kv_seq_len(self.handle, slot))
+
+    def reset(self, slot: int = -1) -> None:
+        _lib.check(self.lib.b200_kv_reset(self.handle, slot, _lib.stream_ptr(self.shard.device)))
+
+    def close(self):
+        if getattr(self, "handle", None) and getattr(self.shard, "handle", None):
+            self.lib.b200_kv_destroy(self.handle)
+        self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

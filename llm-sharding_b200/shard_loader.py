@@ -1,0 +1,71 @@
+"""``LlamaShardPart`` with the reference's constructor and ``forward`` signature
+(utils/shard_loader.py:13-15,57), backed by ``libb200shard.so`` instead of a ``ModuleList`` of
+Hugging Face ``LlamaDecoderLayer``."""
+from __future__ import annotations
+
+import os
+
+import torch
+
+from .engine import PagedKVCache, Shard, read_model_config
+
+
+class LlamaShardPart:
+    def __init__(self, shards_path: str, shard_weights: list[str], start: int, end: int,
+                 device="cuda:0", dtype=torch.bfloat16,
+                 add_final_norm=False, final_norm_weight=None, *,
+                 lm_head_weight: str | None = None, embedding_weight: str | None = None,
+                 max_tokens: int = 4096, max_batch: int = 1):
+        """Same positional parameters as the reference.  Keyword-only extras: ``lm_head_weight`` /
+        ``embedding_weight`` (file names) put the tail's ``lm_head`` and the entry node's embedding
+        behind the same C handle; ``max_tokens`` / ``max_batch`` size the workspace."""
+        self.shards_path = shards_path
+        self.shard_weights = shard_weights
+        self.start = start
+        self.end = end
+        self.device = torch.device(device)
+        self.dtype = dtype
+        if dtype != torch.bfloat16:
+            raise ValueError("[ERROR] the B200 shard path computes in bfloat16 (fp32 accumulate); "
+                             f"dtype={dtype} is not built")
+        if len(self.shard_weights) != self.end - self.start:
+            raise ValueError("[ERROR] String list: shard_weights length must be equal to (end - start)")
+        if add_final_norm and final_norm_weight is None:
+            raise ValueError("[ERROR] final_norm_weight is required when add_final_norm is True")
+        self.config = read_model_config(shards_path)
+        self.engine = Shard(self.config, end - start, self.device, has_final_norm=bool(add_final_norm),
+                            has_lm_head=lm_head_weight is not None, has_embedding=embedding_weight is not None,
+                            max_tokens=max_tokens, max_batch=max_batch)
+        for rel_idx, fname in enumerate(self.shard_weights):  # shard-relative index, utils/shard_loader.py:36-45
+            state = torch.load(os.path.join(shards_path, fname), map_location="cpu")
+            self.engine.set_layer(rel_idx, state)
+            del state
+        if add_final_norm:
+            self.final_norm_weight = final_norm_weight
+            self.engine.set_final_norm(torch.load(os.path.join(shards_path, final_norm_weight), map_location="cpu")["weight"])
+        if lm_head_weight is not None:
+            self.engine.set_lm_head(torch.load(os.path.join(shards_path, lm_head_weight), map_location="cpu")["weight"])
+        if embedding_weight is not None:
+            self.engine.set_embedding(torch.load(os.path.join(shards_path, embedding_weight), map_location="cpu")["weight"])
+
+    def eval(self):  # called at utils/node_worker.py:179; there is no training mode here
+        return self
+
+    def new_cache(self, max_slots: int = 1, max_seq_len: int | None = None, page_size: int = 64) -> PagedKVCache:
+        return self.engine.new_kv(max_slots, page_size, None, max_seq_len or self.config["max_position_embeddings"])
+
+    def forward(self, hidden_states, attention_mask=None, past_key_value=None, rotary_emb=None, *, slots=None):
+        """hidden_states [B,S,H] -> [B,S,H] (bf16).
+
+        ``past_key_value`` must be a ``PagedKVCache`` of this shard (the reference passes its
+        ``DynamicCache``).  ``rotary_emb`` is accepted for signature parity and ignored: cos/sin
+        are recomputed on the device from the cache length.  ``attention_mask=None`` is the
+        reference's behaviour, i.e. NON-causal prefill; pass ``"causal"`` for
+        real-Llama masking."""
+        if not isinstance(past_key_value, PagedKVCache):
+            raise ValueError("[ERROR] Unsupported past_key_value structure")
+        if attention_mask is not None and not (isinstance(attention_mask, str) and attention_mask == "causal"):
+            raise ValueError("[ERROR] attention_mask must be None (reference behaviour) or \"causal\"")
+        return self.engine.forward(hidden_states, past_key_value, slots, causal=attention_mask is not None)
+
+    __call__ = forward

@@ -1,0 +1,74 @@
+"""-m gpu: single kernels through the C ABI against a plain torch fp32 reference of the same op
+(floating-point kernels; tolerances stated per test)."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def lib():
+    from llm_sharding_b200 import _lib
+    _lib.require_cuda()
+    return _lib.load()
+
+
+def _st():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def rel_l2(a, b):
+    return float((a.double() - b.double()).norm() / b.double().norm().clamp_min(1e-30))
+
+
+@pytest.mark.parametrize("rows,n", [(1, 256), (3, 4096), (130, 4096), (7, 11008)])
+def test_rmsnorm_matches_llama_rmsnorm(lib, rows, n):
+    from llm_sharding_b200 import _lib
+    g = torch.Generator(device="cuda").manual_seed(rows * 131 + n)
+    x = torch.randn(rows, n, device="cuda", generator=g) * 3.0
+    w = (1 + 0.1 * torch.randn(n, device="cuda", generator=g)).bfloat16()
+    out = torch.empty(rows, n, device="cuda", dtype=torch.bfloat16)
+    _lib.check(lib.b200_rmsnorm(x.data_ptr(), w.data_ptr(), 1e-5, rows, n, out.data_ptr(), _st()))
+    ref = w.float() * (x * torch.rsqrt(x.pow(2).mean(-1, keepdim=True) + 1e-5))
+    # output is bf16: one rounding (2^-8 relative) on top of fp32 arithmetic
+    assert torch.allclose(out.float(), ref, rtol=2 ** -7, atol=1e-6)
+    assert rel_l2(out.float(), ref) < 3e-3
+
+
+@pytest.mark.parametrize("M", [1, 2, 3, 4])
+@pytest.mark.parametrize("N,K", [(256, 256), (1000, 256), (4096, 4096), (4096, 11008), (1536, 640), (32000, 4096)])
+def test_gemv_weight_streaming(lib, M, N, K):
+    from llm_sharding_b200 import _lib
+    g = torch.Generator(device="cuda").manual_seed(M + N + K)
+    x = torch.randn(M, K, device="cuda", generator=g)
+    w = (torch.randn(N, K, device="cuda", generator=g) * 0.02).bfloat16()
+    out = torch.full((M, N), float("nan"), device="cuda")
+    _lib.check(lib.b200_gemv_bf16(x.data_ptr(), w.data_ptr(), M, N, K, out.data_ptr(), _st()))
+    ref = (x.double() @ w.double().t()).float()
+    assert rel_l2(out, ref) < 2e-6  # fp32 accumulation, different summation order only
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 128, 64), (128, 128, 512), (1, 128, 64), (200, 384, 512), (33, 1000, 256),
+                                   (512, 4096, 4096), (260, 12288, 4096), (77, 4096, 11008)])
+def test_gemm_tcgen05(lib, M, N, K):
+    from llm_sharding_b200 import _lib
+    g = torch.Generator(device="cuda").manual_seed(M * 7 + N + K)
+    a = torch.randn(M, K, device="cuda", generator=g).bfloat16()
+    w = (torch.randn(N, K, device="cuda", generator=g) * 0.05).bfloat16()
+    out = torch.full((M, N), float("nan"), device="cuda")
+    _lib.check(lib.b200_gemm_bf16(a.data_ptr(), w.data_ptr(), M, N, K, out.data_ptr(), _st()))
+    torch.cuda.synchronize()
+    ref = (a.double() @ w.double().t()).float()
+    assert not torch.isnan(out).any()
+    assert rel_l2(out, ref) < 1e-5  # exact bf16 products, fp32 accumulation in tensor memory
+
+
+def test_gemv_rejects_bad_shapes(lib):
+    from llm_sharding_b200 import _lib
+    x = torch.zeros(8, 64, device="cuda")
+    w = torch.zeros(8, 64, device="cuda", dtype=torch.bfloat16)
+    o = torch.zeros(8, 8, device="cuda")
+    with pytest.raises(ValueError):
+        _lib.check(lib.b200_gemv_bf16(x.data_ptr(), w.data_ptr(), 5, 8, 64, o.data_ptr(), _st()))
+    with pytest.raises(ValueError):
+        _lib.check(lib.b200_gemm_bf16(w.data_ptr(), w.data_ptr(), 8, 8, 60, o.data_ptr(), _st()))
