@@ -110,6 +110,14 @@ B200_API int b200_shard_lm_head_argmax(b200_shard_t* s, const void* d_hidden, in
 B200_API int b200_shard_forward_argmax(b200_shard_t* s, b200_kv_t* kv, const int32_t* h_slots, const void* d_hidden_in,
                               int B, int S, int causal, void* d_hidden_out, int64_t* d_token_out,
                               float* d_margin_out, void* stream);
+/* Entry node that is also the head (and possibly the tail) of the chain: embed_tokens (utils/node_worker.py:215,302)
+ * + forward (+ lm_head/argmax when the shard holds it) with token ids in and token ids (tail) or hidden states out, so
+ * that one greedy step of a single-GPU model — NodeWorker.receive_next_token's re-embed (utils/node_worker.py:302)
+ * followed by pass_through_shard (:226-272) — is one call and, for S == 1, one CUDA-graph replay.
+ * d_tok_in int64 [B*S]; d_hidden_out may be NULL on a tail shard; d_tok_out / d_margin_out as above. */
+B200_API int b200_shard_step_tokens(b200_shard_t* s, b200_kv_t* kv, const int32_t* h_slots, const int64_t* d_tok_in,
+                                    int B, int S, int causal, void* d_hidden_out, int64_t* d_tok_out,
+                                    float* d_margin_out, void* stream);
 /* Entry node: embed_tokens(ids) (utils/node_worker.py:215,302). d_ids int64 [n] -> bf16 [n,H] */
 B200_API int b200_shard_embed(b200_shard_t* s, const int64_t* d_ids, int n, void* d_hidden_out, void* stream);
 
@@ -125,6 +133,11 @@ B200_API int b200_hop_connect(b200_hop_t* h, const void* h_peer_handle, int peer
 B200_API int b200_hop_send(b200_hop_t* h, const void* d_payload, int64_t bytes, uint64_t seq, void* stream);
 /* wait (on the GPU) for message `seq` in the local mailbox, copy it to d_out; max_wait_us bounds the spin */
 B200_API int b200_hop_recv(b200_hop_t* h, void* d_out, int64_t bytes, uint64_t seq, int64_t max_wait_us, void* stream);
+/* Zero-copy variant: the producer's last kernel writes its output straight into b200_hop_peer_slot(h, seq) (a mapped
+ * peer pointer: the stores cross NVLink) and then calls b200_hop_send with d_payload == NULL (publish only); the
+ * consumer calls b200_hop_recv with d_out == NULL (wait only) and lets its first kernel read b200_hop_local_slot. */
+B200_API void* b200_hop_peer_slot(b200_hop_t* h, uint64_t seq);
+B200_API void* b200_hop_local_slot(b200_hop_t* h, uint64_t seq);
 B200_API int b200_hop_error(b200_hop_t* h); /* nonzero once a recv kernel timed out */
 B200_API int b200_hop_destroy(b200_hop_t* h);
 
@@ -139,6 +152,11 @@ B200_API int b200_shard_reset_counters(b200_shard_t* s);
 B200_API int b200_shard_set_graphs(b200_shard_t* s, int enabled);
 
 /* ---- single-kernel entry points (unit parity tests and micro-benchmarks) -------------- */
+/* Launch ONE of the decode-path kernels of layer `layer` exactly as b200_shard_forward would (same template
+ * instantiation, same buffers; inputs are whatever the workspace holds): kind 0 = RMSNorm+QKV+RoPE+KV-append,
+ * 2 = o_proj+residual, 3 = RMSNorm+gate/up+SwiGLU, 4 = down_proj+residual.  `rows` = token rows (1..4).
+ * Used by bench.py to time the dominant kernel on its own stream for the roofline figure. */
+B200_API int b200_shard_run_kernel(b200_shard_t* s, b200_kv_t* kv, int kind, int layer, int rows, void* stream);
 /* LlamaRMSNorm.forward (transformers modeling_llama.py:62-67): fp32 in -> bf16 out, [rows, n] */
 B200_API int b200_rmsnorm(const float* d_x, const void* d_weight_bf16, float eps, int rows, int n, void* d_out_bf16,
                  void* stream);

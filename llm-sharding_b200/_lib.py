@@ -49,11 +49,15 @@ PROTOTYPES = {
     "b200_shard_lm_head_argmax": (_I, [_P, _P, _I, _I, _P, _P, _P]),
     "b200_shard_forward_argmax": (_I, [_P, _P, C.POINTER(C.c_int32), _P, _I, _I, _I, _P, _P, _P, _P]),
     "b200_shard_embed": (_I, [_P, _P, _I, _P, _P]),
+    "b200_shard_step_tokens": (_I, [_P, _P, C.POINTER(C.c_int32), _P, _I, _I, _I, _P, _P, _P, _P]),
+    "b200_shard_run_kernel": (_I, [_P, _P, _I, _I, _I, _P]),
     "b200_hop_create": (_I, [_I, _I, _I64, C.POINTER(_P)]),
     "b200_hop_export": (_I, [_P, _P]),
     "b200_hop_connect": (_I, [_P, _P, _I, _I]),
     "b200_hop_send": (_I, [_P, _P, _I64, _U64, _P]),
     "b200_hop_recv": (_I, [_P, _P, _I64, _U64, _I64, _P]),
+    "b200_hop_peer_slot": (_P, [_P, _U64]),
+    "b200_hop_local_slot": (_P, [_P, _U64]),
     "b200_hop_error": (_I, [_P]),
     "b200_hop_destroy": (_I, [_P]),
     "b200_last_error": (C.c_char_p, []),

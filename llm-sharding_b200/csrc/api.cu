@@ -41,7 +41,7 @@ struct LayerW {
 
 struct GraphKey {
     int B, causal, with_argmax;
-    const void *in, *out, *tok, *margin;
+    const void *in, *out, *tok, *margin, *tok_in;
     const b200_kv* kv;
     int32_t slots[kMaxBatch];
     bool operator<(const GraphKey& o) const { return memcmp(this, &o, sizeof(GraphKey)) < 0; }
@@ -328,11 +328,17 @@ static int check_call(b200_shard_t* s, b200_kv_t* kv, const int32_t* h_slots, co
 }
 
 // enqueue every kernel of one forward (+ optional tail); no host synchronisation
-static int enqueue_forward(b200_shard_t* s, b200_kv_t* kv, const SlotList& sl, const void* in, int B, int S, int causal,
-                           void* out, int64_t* tok, float* margin, bool with_tail, cudaStream_t st) {
+static int enqueue_forward(b200_shard_t* s, b200_kv_t* kv, const SlotList& sl, const void* in, const int64_t* tok_in,
+                           int B, int S, int causal, void* out, int64_t* tok, float* margin, bool with_tail,
+                           cudaStream_t st) {
     const b200_shard_config_t& c = s->cfg;
     const int M = B * S, H = c.hidden_size, I = c.intermediate_size;
     const int64_t head_stride = (int64_t)kv->dev.page_size * 128;
+    if (tok_in != nullptr) {  // entry == head node: embed_tokens (utils/node_worker.py:215,302) straight into the workspace
+        launch_embed(s->embedding, tok_in, M, H, c.vocab_size, s->xn, st);
+        s->n_launch += 1;
+        in = s->xn;
+    }
     launch_kv_alloc(kv->dev, sl, B, S, s->tm.call_base, st);
     launch_prep(kv->dev, sl, B, S, causal, s->inv, c.n_kv_heads, s->tm, st);
     launch_load_residual(reinterpret_cast<const __nv_bfloat16*>(in), s->x, (int64_t)M * H, st);
@@ -443,10 +449,12 @@ static void account(b200_shard_t* s, b200_kv_t* kv, const SlotList& sl, int B, i
     s->n_calls += 1;
 }
 
-static int forward_impl(b200_shard_t* s, b200_kv_t* kv, const int32_t* h_slots, const void* in, int B, int S, int causal,
-                        void* out, int64_t* tok, float* margin, bool with_tail, void* stream) {
+static int forward_impl(b200_shard_t* s, b200_kv_t* kv, const int32_t* h_slots, const void* in, const int64_t* tok_in,
+                        int B, int S, int causal, void* out, int64_t* tok, float* margin, bool with_tail, void* stream) {
     SlotList sl{};
-    TRY(check_call(s, kv, h_slots, in, B, S, &sl));
+    TRY(check_call(s, kv, h_slots, tok_in != nullptr ? (const void*)tok_in : in, B, S, &sl));
+    if (tok_in != nullptr && (!s->cfg.has_embedding || s->embedding == nullptr))
+        return fail(B200_ESTATE, "[ERROR] this node does not have embedding layer while receiving user request.");
     if (with_tail) {
         if (!s->cfg.has_lm_head || s->lm_head == nullptr) return fail(B200_ESTATE, "[ERROR] this shard does not hold the lm_head");
         if (tok == nullptr) return fail(B200_EINVAL, "[ERROR] null token output");
@@ -460,7 +468,7 @@ static int forward_impl(b200_shard_t* s, b200_kv_t* kv, const int32_t* h_slots, 
         GraphKey key;
         memset(&key, 0, sizeof(key));
         key.B = B; key.causal = causal; key.with_argmax = with_tail ? 1 : 0;
-        key.in = in; key.out = out; key.tok = tok; key.margin = margin; key.kv = kv;
+        key.in = in; key.out = out; key.tok = tok; key.margin = margin; key.kv = kv; key.tok_in = tok_in;
         for (int b = 0; b < B; ++b) key.slots[b] = sl.v[b];
         auto it = s->graph_cache.find(key);
         if (it == s->graph_cache.end()) {
@@ -469,7 +477,7 @@ static int forward_impl(b200_shard_t* s, b200_kv_t* kv, const int32_t* h_slots, 
             CU_TRY(cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking));
             const uint64_t launches_before = s->n_launch;
             CU_TRY(cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal));
-            int r = enqueue_forward(s, kv, sl, in, B, S, causal, out, tok, margin, with_tail, cs);
+            int r = enqueue_forward(s, kv, sl, in, tok_in, B, S, causal, out, tok, margin, with_tail, cs);
             if (r == 0 && with_tail) r = enqueue_tail(s, B, tok, margin, cs);
             cudaGraph_t graph = nullptr;
             cudaError_t ce = cudaStreamEndCapture(cs, &graph);
@@ -488,11 +496,11 @@ static int forward_impl(b200_shard_t* s, b200_kv_t* kv, const int32_t* h_slots, 
             it = s->graph_cache.emplace(key, exec).first;
         }
         CU_TRY(cudaGraphLaunch(it->second, st));
-        s->n_launch += 3 + (uint64_t)s->cfg.n_layers * 6 + (out ? 1 : 0) + (with_tail ? 3 : 0);
+        s->n_launch += 3 + (uint64_t)s->cfg.n_layers * (B <= gemv_row_limit(s) ? 6 : 8) + (out ? 1 : 0) + (with_tail ? 3 : 0) + (tok_in ? 1 : 0);
         done = true;
     }
     if (!done) {
-        TRY(enqueue_forward(s, kv, sl, in, B, S, causal, out, tok, margin, with_tail, st));
+        TRY(enqueue_forward(s, kv, sl, in, tok_in, B, S, causal, out, tok, margin, with_tail, st));
         if (with_tail) TRY(enqueue_tail(s, B, tok, margin, st));
         CU_TRY(cudaGetLastError());
     }
@@ -508,12 +516,57 @@ static int forward_impl(b200_shard_t* s, b200_kv_t* kv, const int32_t* h_slots, 
 extern "C" B200_API int b200_shard_forward(b200_shard_t* s, b200_kv_t* kv, const int32_t* h_slots, const void* in, int B, int S,
                                   int causal, void* out, void* stream) {
     if (out == nullptr) return fail(B200_EINVAL, "[ERROR] null output");
-    return forward_impl(s, kv, h_slots, in, B, S, causal, out, nullptr, nullptr, false, stream);
+    return forward_impl(s, kv, h_slots, in, nullptr, B, S, causal, out, nullptr, nullptr, false, stream);
 }
 extern "C" B200_API int b200_shard_forward_argmax(b200_shard_t* s, b200_kv_t* kv, const int32_t* h_slots, const void* in, int B, int S,
                                          int causal, void* out, int64_t* tok, float* margin, void* stream) {
-    return forward_impl(s, kv, h_slots, in, B, S, causal, out, tok, margin, true, stream);
+    return forward_impl(s, kv, h_slots, in, nullptr, B, S, causal, out, tok, margin, true, stream);
 }
+extern "C" B200_API int b200_shard_step_tokens(b200_shard_t* s, b200_kv_t* kv, const int32_t* h_slots, const int64_t* tok_in, int B,
+                                               int S, int causal, void* out, int64_t* tok, float* margin, void* stream) {
+    if (tok_in == nullptr) return fail(B200_EINVAL, "[ERROR] null token input");
+    const bool tail = s != nullptr && s->cfg.has_lm_head;
+    if (!tail && out == nullptr) return fail(B200_EINVAL, "[ERROR] null output");
+    return forward_impl(s, kv, h_slots, nullptr, tok_in, B, S, causal, out, tail ? tok : nullptr, tail ? margin : nullptr, tail, stream);
+}
+
+extern "C" B200_API int b200_shard_run_kernel(b200_shard_t* s, b200_kv_t* kv, int kind, int layer, int rows, void* stream) {
+    if (s == nullptr || kv == nullptr) return fail(B200_EINVAL, "[ERROR] null argument");
+    if (layer < 0 || layer >= s->cfg.n_layers || rows < 1 || rows > gemv_row_limit(s)) return fail(B200_EINVAL, "[ERROR] bad layer / rows");
+    CU_TRY(cudaSetDevice(s->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    const b200_shard_config_t& c = s->cfg;
+    const LayerW& L = s->layers[layer];
+    const int H = c.hidden_size, I = c.intermediate_size;
+    GemvParams g{};
+    switch (kind) {
+        case 0:
+            g.W = L.wqkv; g.x = s->x; g.norm_w = L.norm1; g.eps = c.rms_eps; g.N = s->qkv_rows; g.K = H;
+            g.q_out = s->q_f; g.k_pool = kv->k_pool + (int64_t)layer * kv->layer_stride; g.v_pool = kv->v_pool + (int64_t)layer * kv->layer_stride;
+            g.kv_off = s->tm.kv_off; g.cos = s->tm.cos; g.sin = s->tm.sin; g.n_heads = c.n_heads; g.n_kv = c.n_kv_heads;
+            g.head_stride = (int64_t)kv->dev.page_size * 128;
+            launch_gemv(g, rows, EPI_QKV, true, s->num_sms, st);
+            break;
+        case 2:
+            g.W = L.wo; g.x = s->attn_f; g.N = H; g.K = s->nq; g.out = s->x;
+            launch_gemv(g, rows, EPI_RESID, false, s->num_sms, st);
+            break;
+        case 3:
+            g.W = L.wgu; g.x = s->x; g.norm_w = L.norm2; g.eps = c.rms_eps; g.N = 2 * I; g.K = H; g.out = s->act_f;
+            launch_gemv(g, rows, EPI_SWIGLU, true, s->num_sms, st);
+            break;
+        case 4:
+            g.W = L.wdown; g.x = s->act_f; g.N = H; g.K = I; g.out = s->x;
+            launch_gemv(g, rows, EPI_RESID, false, s->num_sms, st);
+            break;
+        default:
+            return fail(B200_EINVAL, "[ERROR] unknown kernel kind %d", kind);
+    }
+    CU_TRY(cudaGetLastError());
+    s->n_launch += 1;
+    return 0;
+}
+
 extern "C" B200_API int b200_shard_lm_head_argmax(b200_shard_t* s, const void* hidden, int B, int S, int64_t* tok, float* margin,
                                          void* stream) {
     if (s == nullptr || hidden == nullptr || tok == nullptr) return fail(B200_EINVAL, "[ERROR] null argument");
@@ -644,8 +697,17 @@ extern "C" B200_API int b200_hop_send(b200_hop_t* h, const void* payload, int64_
     CU_TRY(cudaGetLastError());
     return 0;
 }
+extern "C" B200_API void* b200_hop_peer_slot(b200_hop_t* h, uint64_t seq) {
+    if (h == nullptr || h->peer == nullptr) return nullptr;
+    return h->peer + (size_t)(seq % (uint64_t)h->n_slots) * h->slot_bytes;
+}
+extern "C" B200_API void* b200_hop_local_slot(b200_hop_t* h, uint64_t seq) {
+    if (h == nullptr) return nullptr;
+    return h->local + (size_t)(seq % (uint64_t)h->n_slots) * h->slot_bytes;
+}
 extern "C" B200_API int b200_hop_recv(b200_hop_t* h, void* out, int64_t bytes, uint64_t seq, int64_t max_wait_us, void* stream) {
-    if (h == nullptr || out == nullptr) return fail(B200_EINVAL, "[ERROR] null argument");
+    if (h == nullptr) return fail(B200_EINVAL, "[ERROR] null argument");
+    if (out == nullptr) bytes = 0;  // wait only: the consumer reads the mailbox slot in place
     if (bytes < 0 || bytes > h->slot_bytes) return fail(B200_EINVAL, "[ERROR] hop payload exceeds the slot");
     CU_TRY(cudaSetDevice(h->device));
     const int slot = (int)(seq % (uint64_t)h->n_slots);

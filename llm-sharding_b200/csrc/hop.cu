@@ -63,13 +63,13 @@ static int hop_grid(int64_t n16) {
 void launch_hop_send(const void* payload, int64_t bytes, void* peer_slot, uint64_t* peer_flag, uint64_t seq,
                      unsigned int* counter, cudaStream_t st) {
     const int64_t n16 = (bytes + 15) / 16;
-    hop_send_kernel<<<hop_grid(n16), 1024, 0, st>>>(reinterpret_cast<const uint4*>(payload), payload ? n16 : 0,
+    hop_send_kernel<<<hop_grid(payload ? n16 : 0), payload ? 1024 : 32, 0, st>>>(reinterpret_cast<const uint4*>(payload), payload ? n16 : 0,
                                                     reinterpret_cast<uint4*>(peer_slot), peer_flag, seq, counter);
 }
 void launch_hop_recv(void* out, int64_t bytes, const void* local_slot, const uint64_t* local_flag, uint64_t seq,
                      int64_t max_wait_cycles, int* err, cudaStream_t st) {
     const int64_t n16 = (bytes + 15) / 16;
-    hop_recv_kernel<<<hop_grid(n16), 1024, 0, st>>>(reinterpret_cast<uint4*>(out), n16,
+    hop_recv_kernel<<<hop_grid(n16), n16 > 0 ? 1024 : 32, 0, st>>>(reinterpret_cast<uint4*>(out), n16,
                                                     reinterpret_cast<const uint4*>(local_slot), local_flag, seq,
                                                     (long long)max_wait_cycles, err);
 }

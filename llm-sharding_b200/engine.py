@@ -63,6 +63,8 @@ class Shard:
         h = C.c_void_p()
         _lib.check(self.lib.b200_shard_create(C.byref(cfg), self.dev_index, C.byref(h)))
         self.handle = h
+        self.graphs = False
+        self._step_bufs: dict = {}   # B -> persistent (hidden_in, hidden_out, tok, margin) for single-token calls
 
     # ---- weights
     def _stream(self):
@@ -108,16 +110,41 @@ class Shard:
         """LlamaShardPart.forward: bf16 [B,S,H] -> bf16 [B,S,H]."""
         hidden = self._check_hidden(hidden)
         B, S, _ = hidden.shape
+        if S == 1 and self.graphs and out is None:
+            # single-token calls replay a CUDA graph keyed by its pointers: run on persistent buffers and hand
+            # back a fresh tensor (the reference's outputs are fresh tensors too)
+            hin, hout, _, _ = self._bufs(B)
+            hin.copy_(hidden)
+            _lib.check(self.lib.b200_shard_forward(self.handle, kv.handle, self._slots(slots, B), hin.data_ptr(), B, 1,
+                                                   int(causal), hout.data_ptr(), self._stream()))
+            return hout.clone()
         if out is None:
             out = torch.empty_like(hidden)
         _lib.check(self.lib.b200_shard_forward(self.handle, kv.handle, self._slots(slots, B), hidden.data_ptr(), B, S,
                                                int(causal), out.data_ptr(), self._stream()))
         return out
 
+    def _bufs(self, B: int):
+        if B not in self._step_bufs:
+            H = self.hidden_size
+            self._step_bufs[B] = (torch.empty(B, 1, H, dtype=torch.bfloat16, device=self.device),
+                                  torch.empty(B, 1, H, dtype=torch.bfloat16, device=self.device),
+                                  torch.empty(B, dtype=torch.int64, device=self.device),
+                                  torch.empty(B, dtype=torch.float32, device=self.device))
+        return self._step_bufs[B]
+
     def forward_argmax(self, hidden: torch.Tensor, kv: "PagedKVCache", slots=None, causal: bool = False,
                        want_hidden: bool = False, want_margin: bool = False):
         hidden = self._check_hidden(hidden)
         B, S, _ = hidden.shape
+        if S == 1 and self.graphs:
+            hin, hout, tokb, marb = self._bufs(B)
+            hin.copy_(hidden)
+            _lib.check(self.lib.b200_shard_forward_argmax(
+                self.handle, kv.handle, self._slots(slots, B), hin.data_ptr(), B, 1, int(causal),
+                hout.data_ptr() if want_hidden else None, tokb.data_ptr(), marb.data_ptr() if want_margin else None,
+                self._stream()))
+            return tokb.clone(), (hout.clone() if want_hidden else None), (marb.clone() if want_margin else None)
         out = torch.empty_like(hidden) if want_hidden else None
         tok = torch.empty(B, dtype=torch.int64, device=self.device)
         margin = torch.empty(B, dtype=torch.float32, device=self.device) if want_margin else None
@@ -125,6 +152,23 @@ class Shard:
                                                       int(causal), _lib.ptr(out), tok.data_ptr(), _lib.ptr(margin),
                                                       self._stream()))
         return tok, out, margin
+
+    def step_tokens(self, tok_in: torch.Tensor, kv: "PagedKVCache", slots=None, causal: bool = False,
+                    tok_out: torch.Tensor | None = None, S: int = 1, hidden_out: torch.Tensor | None = None,
+                    margin_out: torch.Tensor | None = None):
+        """Token ids in -> token ids out (tail) / hidden out: embed + forward (+ lm_head, argmax) in one call.
+        ``tok_in`` int64 [B*S] on the device; pass the same persistent ``tok_out`` buffer every step (it may
+        alias ``tok_in``) so that the S == 1 CUDA graph is captured once and replayed."""
+        B = tok_in.numel() // S
+        if tok_out is None and self.has_lm_head:
+            tok_out = torch.empty(B, dtype=torch.int64, device=self.device)
+        _lib.check(self.lib.b200_shard_step_tokens(self.handle, kv.handle, self._slots(slots, B), tok_in.data_ptr(), B, S,
+                                                   int(causal), _lib.ptr(hidden_out), _lib.ptr(tok_out),
+                                                   _lib.ptr(margin_out), self._stream()))
+        return tok_out if self.has_lm_head else hidden_out
+
+    def run_kernel(self, kv: "PagedKVCache", kind: int, layer: int, rows: int = 1) -> None:
+        _lib.check(self.lib.b200_shard_run_kernel(self.handle, kv.handle, kind, layer, rows, self._stream()))
 
     def lm_head_argmax(self, hidden: torch.Tensor, want_margin: bool = False):
         hidden = self._check_hidden(hidden)
@@ -153,7 +197,9 @@ class Shard:
         return {"launches": arr[0], "bytes": arr[1], "flops": arr[2], "calls": arr[3]}
 
     def reset_counters(self): _lib.check(self.lib.b200_shard_reset_counters(self.handle))
-    def set_graphs(self, on: bool): _lib.check(self.lib.b200_shard_set_graphs(self.handle, int(on)))
+    def set_graphs(self, on: bool):
+        _lib.check(self.lib.b200_shard_set_graphs(self.handle, int(on)))
+        self.graphs = bool(on)
 
     def close(self):
         if getattr(self, "handle", None):

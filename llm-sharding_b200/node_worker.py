@@ -97,7 +97,7 @@ class NodeWorker:
     def __init__(self, src_addr: str, dst_addr: str, can_receive_user_request: bool, shards_path: str,
                  device="cuda:0", dtype=torch.bfloat16, *, communicator=None, max_tokens: int = 4096,
                  max_batch: int = 1, max_slots: int | None = None, max_seq_len: int | None = None,
-                 causal: bool = False, use_graphs: bool = True):
+                 causal: bool = False, use_graphs: bool = True, state_provider=None):
         """Positional parameters as in the reference (utils/node_worker.py:75-76).  ``communicator``
         lets the chain runtime inject a P2P transport; ``causal=False`` is the reference's
         (non-causal prefill) behaviour."""
@@ -117,6 +117,7 @@ class NodeWorker:
         self.max_seq_len = max_seq_len or self.config["max_position_embeddings"]
         self.causal = causal
         self.use_graphs = use_graphs
+        self.state_provider = state_provider
 
         self.tokenizer = None
         self.embed_tokens = None   # callable ids -> hidden once the shard is loaded
@@ -166,7 +167,7 @@ class NodeWorker:
             add_final_norm=is_tail, final_norm_weight="final_norm.pth" if is_tail else None,
             lm_head_weight="lm_head.pth" if is_tail else None,
             embedding_weight="embedding.pth" if self.can_receive_user_request else None,
-            max_tokens=self.max_tokens, max_batch=self.max_batch)
+            max_tokens=self.max_tokens, max_batch=self.max_batch, state_provider=self.state_provider)
         self.shard.eval()
         self.shard.engine.set_graphs(self.use_graphs)
         if self.start == 0:
@@ -241,11 +242,12 @@ class NodeWorker:
         if not self.can_receive_user_request:
             raise RuntimeError('[ERROR] this node does not store the "generated token id" list, '
                                "but received a next_token_id.")
+        single = next_token_id.item() if next_token_id.numel() == 1 else None  # read where the id lives (no extra sync for host ids)
         next_token_id = next_token_id.to(self.device)
         self.generated_ids.append(next_token_id.unsqueeze(-1))
         reached_eos = False
-        if next_token_id.numel() == 1:
-            next_token = self.tokenizer.decode(next_token_id.item())
+        if single is not None:
+            next_token = self.tokenizer.decode(single)
             print(repr(next_token), end=" ", flush=True)
             reached_eos = next_token == self.tokenizer.eos_token
         reached_end = reached_eos or len(self.generated_ids) > max_new_tokens

@@ -15,10 +15,11 @@ class LlamaShardPart:
                  device="cuda:0", dtype=torch.bfloat16,
                  add_final_norm=False, final_norm_weight=None, *,
                  lm_head_weight: str | None = None, embedding_weight: str | None = None,
-                 max_tokens: int = 4096, max_batch: int = 1):
+                 max_tokens: int = 4096, max_batch: int = 1, state_provider=None):
         """Same positional parameters as the reference.  Keyword-only extras: ``lm_head_weight`` /
         ``embedding_weight`` (file names) put the tail's ``lm_head`` and the entry node's embedding
-        behind the same C handle; ``max_tokens`` / ``max_batch`` size the workspace."""
+        behind the same C handle; ``max_tokens`` / ``max_batch`` size the workspace; ``state_provider``
+        (``file name -> state_dict``) replaces ``torch.load`` of the shard files (synthetic weights)."""
         self.shards_path = shards_path
         self.shard_weights = shard_weights
         self.start = start
@@ -36,17 +37,18 @@ class LlamaShardPart:
         self.engine = Shard(self.config, end - start, self.device, has_final_norm=bool(add_final_norm),
                             has_lm_head=lm_head_weight is not None, has_embedding=embedding_weight is not None,
                             max_tokens=max_tokens, max_batch=max_batch)
+        load = state_provider or (lambda fname: torch.load(os.path.join(shards_path, fname), map_location="cpu"))
         for rel_idx, fname in enumerate(self.shard_weights):  # shard-relative index, utils/shard_loader.py:36-45
-            state = torch.load(os.path.join(shards_path, fname), map_location="cpu")
+            state = load(fname)
             self.engine.set_layer(rel_idx, state)
             del state
         if add_final_norm:
             self.final_norm_weight = final_norm_weight
-            self.engine.set_final_norm(torch.load(os.path.join(shards_path, final_norm_weight), map_location="cpu")["weight"])
+            self.engine.set_final_norm(load(final_norm_weight)["weight"])
         if lm_head_weight is not None:
-            self.engine.set_lm_head(torch.load(os.path.join(shards_path, lm_head_weight), map_location="cpu")["weight"])
+            self.engine.set_lm_head(load(lm_head_weight)["weight"])
         if embedding_weight is not None:
-            self.engine.set_embedding(torch.load(os.path.join(shards_path, embedding_weight), map_location="cpu")["weight"])
+            self.engine.set_embedding(load(embedding_weight)["weight"])
 
     def eval(self):  # called at utils/node_worker.py:179; there is no training mode here
         return self

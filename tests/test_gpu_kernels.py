@@ -60,7 +60,7 @@ def test_gemm_tcgen05(lib, M, N, K):
     torch.cuda.synchronize()
     ref = (a.double() @ w.double().t()).float()
     assert not torch.isnan(out).any()
-    assert rel_l2(out, ref) < 1e-5  # exact bf16 products, fp32 accumulation in tensor memory
+    assert rel_l2(out, ref) < 3e-5  # exact bf16 products; fp32 accumulation order differs (K up to 11008)
 
 
 def test_gemv_rejects_bad_shapes(lib):

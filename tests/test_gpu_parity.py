@@ -97,7 +97,7 @@ def test_kv_reset_reuses_pages_and_reproduces(tmp_root):
         from llm_sharding_b200.chain import generate
         ids = torch.from_numpy(z["prompt"])
         t1, s1 = generate(workers, ids, meta["new_tokens"], record_states=True)
-        assert workers[0].past_key_value.get_seq_length() == meta["prompt_len"] + meta["new_tokens"]
+        assert workers[0].past_key_value.get_seq_length() == meta["prompt_len"] + meta["new_tokens"] - 1  # last token is not fed back
         for w in workers:
             w.clear_KV_cache()
         assert workers[0].past_key_value.get_seq_length() == 0
