@@ -160,6 +160,13 @@ B200_API int b200_shard_run_kernel(b200_shard_t* s, b200_kv_t* kv, int kind, int
 /* LlamaRMSNorm.forward (transformers modeling_llama.py:62-67): fp32 in -> bf16 out, [rows, n] */
 B200_API int b200_rmsnorm(const float* d_x, const void* d_weight_bf16, float eps, int rows, int n, void* d_out_bf16,
                  void* stream);
+/* Split-K decode attention over a paged K/V pool (eager_attention_forward, transformers modeling_llama.py:199-221, for
+ * single-token queries): row r attends to keys [0, d_t_end[r]) found through d_block_table[r][*] (page ids into the
+ * pools, layout [page][kv_head][page_size][128] bf16).  d_q / d_out fp32 [rows, n_heads*128].  d_scratch: caller-owned
+ * global memory for the per-split partials, rows*n_heads*n_splits*130 floats. */
+B200_API int b200_attn_decode(const float* d_q, const void* d_k_pool, const void* d_v_pool, const int32_t* d_block_table,
+                              const int32_t* d_t_end, int rows, int n_heads, int n_kv_heads, int page_size,
+                              int max_pages_per_row, int n_splits, float* d_scratch, float* d_out, void* stream);
 /* out[M,N] (fp32) = A[M,K] (bf16) * W[N,K]^T (bf16): the tcgen05/TMA GEMM used for prefill */
 B200_API int b200_gemm_bf16(const void* d_a, const void* d_w, int M, int N, int K, float* d_out, void* stream);
 /* out[M,N] (fp32) = X[M,K] (fp32) * W[N,K]^T (bf16), M <= 4: the weight-streaming decode kernel */

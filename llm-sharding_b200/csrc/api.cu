@@ -742,6 +742,27 @@ extern "C" B200_API int b200_rmsnorm(const float* x, const void* w, float eps, i
     CU_TRY(cudaGetLastError());
     return 0;
 }
+extern "C" B200_API int b200_attn_decode(const float* q, const void* k_pool, const void* v_pool, const int32_t* block_table,
+                                         const int32_t* t_end, int rows, int n_heads, int n_kv_heads, int page_size,
+                                         int max_pages_per_row, int n_splits, float* scratch, float* out, void* stream) {
+    if (q == nullptr || k_pool == nullptr || v_pool == nullptr || block_table == nullptr || t_end == nullptr ||
+        scratch == nullptr || out == nullptr)
+        return fail(B200_EINVAL, "[ERROR] null argument");
+    if (rows < 1 || rows > kMaxBatch || n_heads < 1 || n_kv_heads < 1 || n_heads % n_kv_heads != 0 || page_size < 64 ||
+        page_size % 64 != 0 || max_pages_per_row < 1 || n_splits < 1 || n_splits > kMaxSplits ||
+        ((int64_t)max_pages_per_row * page_size + n_splits - 1) / n_splits > kMaxChunkKeys)
+        return fail(B200_EINVAL, "[ERROR] attn_decode: need 1 <= rows <= %d, n_heads %% n_kv_heads == 0, page_size %% 64 == 0, "
+                    "1 <= n_splits <= %d and at most %d keys per split", kMaxBatch, kMaxSplits, kMaxChunkKeys);
+    AttnDecodeParams a{};
+    a.q = q; a.k_pool = reinterpret_cast<const __nv_bfloat16*>(k_pool); a.v_pool = reinterpret_cast<const __nv_bfloat16*>(v_pool);
+    a.block_table = block_table; a.t_end = t_end;
+    for (int i = 0; i < rows; ++i) a.slots.v[i] = i;
+    a.S = 1; a.n_heads = n_heads; a.n_kv = n_kv_heads; a.page_size = page_size; a.max_pages_per_slot = max_pages_per_row;
+    a.n_splits = n_splits; a.part = scratch; a.out = out;
+    launch_attn_decode(a, rows, (cudaStream_t)stream);
+    CU_TRY(cudaGetLastError());
+    return 0;
+}
 extern "C" B200_API int b200_gemm_bf16(const void* a, const void* w, int M, int N, int K, float* out, void* stream) {
     if (a == nullptr || w == nullptr || out == nullptr) return fail(B200_EINVAL, "[ERROR] null argument");
     GemmParams g{reinterpret_cast<const __nv_bfloat16*>(a), reinterpret_cast<const __nv_bfloat16*>(w), M, N, K, out, GEMM_STORE_F32};

@@ -72,3 +72,53 @@ def test_gemv_rejects_bad_shapes(lib):
         _lib.check(lib.b200_gemv_bf16(x.data_ptr(), w.data_ptr(), 5, 8, 64, o.data_ptr(), _st()))
     with pytest.raises(ValueError):
         _lib.check(lib.b200_gemm_bf16(w.data_ptr(), w.data_ptr(), 8, 8, 60, o.data_ptr(), _st()))
+
+
+def _paged_kv(rows, n_kv, T_list, page_size, g):
+    """random K/V written into a shuffled page pool; returns pools, block table, dense copies"""
+    max_pages = max((t + page_size - 1) // page_size for t in T_list)
+    n_pages = rows * max_pages + 3
+    k_pool = torch.zeros(n_pages, n_kv, page_size, 128, device="cuda", dtype=torch.bfloat16)
+    v_pool = torch.zeros_like(k_pool)
+    perm = torch.randperm(n_pages, generator=torch.Generator().manual_seed(7)).tolist()
+    bt = torch.full((rows, max_pages), -1, dtype=torch.int32)
+    dense = []
+    for r, T in enumerate(T_list):
+        k = torch.randn(n_kv, T, 128, device="cuda", generator=g).bfloat16()
+        v = torch.randn(n_kv, T, 128, device="cuda", generator=g).bfloat16()
+        dense.append((k, v))
+        for pi in range((T + page_size - 1) // page_size):
+            page = perm.pop()
+            bt[r, pi] = page
+            lo, hi = pi * page_size, min(T, (pi + 1) * page_size)
+            k_pool[page, :, : hi - lo] = k[:, lo:hi]
+            v_pool[page, :, : hi - lo] = v[:, lo:hi]
+    return k_pool, v_pool, bt.cuda(), dense, max_pages
+
+
+def attn_decode_reference(q, dense, n_heads, n_kv):
+    out = torch.empty_like(q)
+    rep = n_heads // n_kv
+    for r, (k, v) in enumerate(dense):
+        qr = q[r].view(n_heads, 128).double()
+        kk = k.double().repeat_interleave(rep, dim=0)
+        vv = v.double().repeat_interleave(rep, dim=0)
+        p = torch.softmax(torch.einsum("hd,htd->ht", qr, kk) * 128 ** -0.5, dim=-1)
+        out[r] = torch.einsum("ht,htd->hd", p, vv).reshape(-1).float()
+    return out
+
+
+@pytest.mark.parametrize("rows,n_heads,n_kv,T_list,n_splits", [
+    (1, 32, 32, [640], 10), (1, 4, 2, [1], 3), (3, 8, 8, [65, 128, 7], 4), (2, 32, 8, [1000, 513], 16), (4, 2, 2, [64, 64, 64, 64], 1)])
+def test_attn_decode_split_k(lib, rows, n_heads, n_kv, T_list, n_splits):
+    from llm_sharding_b200 import _lib
+    g = torch.Generator(device="cuda").manual_seed(rows * 100 + n_heads)
+    k_pool, v_pool, bt, dense, max_pages = _paged_kv(rows, n_kv, T_list, 64, g)
+    q = torch.randn(rows, n_heads * 128, device="cuda", generator=g)
+    t_end = torch.tensor(T_list, dtype=torch.int32, device="cuda")
+    scratch = torch.empty(rows * n_heads * n_splits * 130, device="cuda")
+    out = torch.full_like(q, float("nan"))
+    _lib.check(lib.b200_attn_decode(q.data_ptr(), k_pool.data_ptr(), v_pool.data_ptr(), bt.data_ptr(), t_end.data_ptr(), rows,
+                                    n_heads, n_kv, 64, max_pages, n_splits, scratch.data_ptr(), out.data_ptr(), _st()))
+    ref = attn_decode_reference(q, dense, n_heads, n_kv)
+    assert rel_l2(out, ref) < 1e-5  # fp32 softmax and accumulation over bf16 K/V; only summation order differs
