@@ -167,6 +167,18 @@ B200_API int b200_rmsnorm(const float* d_x, const void* d_weight_bf16, float eps
 B200_API int b200_attn_decode(const float* d_q, const void* d_k_pool, const void* d_v_pool, const int32_t* d_block_table,
                               const int32_t* d_t_end, int rows, int n_heads, int n_kv_heads, int page_size,
                               int max_pages_per_row, int n_splits, float* d_scratch, float* d_out, void* stream);
+/* No counterpart in the reference.  b200_attn_decode without any device-memory allocation, for callers that cannot
+ * allocate: a process whose HBM is already fully owned by another pool (serving runtime, torch caching allocator), a
+ * per-token loop that must not hit the device-wide synchronisation of cudaMalloc / cudaFree, or a tool working on K/V
+ * pages it owns without a shard handle.  The split-K partials go to an array built into the library (about 2 MiB per
+ * GPU, held until the process exits) instead of d_scratch; inputs and outputs are still the caller's.
+ * Limit: rows * n_heads * n_splits <= 4096, otherwise B200_EINVAL.  The first call on a device looks up the array's
+ * address — make it before starting any stream capture on that device.  All calls share the array: calls that can
+ * overlap on the GPU (different streams) race; keep them on one stream or order them with events. */
+B200_API int b200_attn_decode_static(const float* d_q, const void* d_k_pool, const void* d_v_pool,
+                                     const int32_t* d_block_table, const int32_t* d_t_end, int rows, int n_heads,
+                                     int n_kv_heads, int page_size, int max_pages_per_row, int n_splits, float* d_out,
+                                     void* stream);
 /* out[M,N] (fp32) = A[M,K] (bf16) * W[N,K]^T (bf16): the tcgen05/TMA GEMM used for prefill */
 B200_API int b200_gemm_bf16(const void* d_a, const void* d_w, int M, int N, int K, float* d_out, void* stream);
 /* out[M,N] (fp32) = X[M,K] (fp32) * W[N,K]^T (bf16), M <= 4: the weight-streaming decode kernel */

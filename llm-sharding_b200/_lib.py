@@ -67,6 +67,7 @@ PROTOTYPES = {
     "b200_shard_set_graphs": (_I, [_P, _I]),
     "b200_rmsnorm": (_I, [_P, _P, C.c_float, _I, _I, _P, _P]),
     "b200_attn_decode": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P, _P]),
+    "b200_attn_decode_static": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P]),
     "b200_gemm_bf16": (_I, [_P, _P, _I, _I, _I, _P, _P]),
     "b200_gemv_bf16": (_I, [_P, _P, _I, _I, _I, _P, _P]),
 }

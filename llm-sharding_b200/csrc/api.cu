@@ -25,6 +25,9 @@ static int fail(int code, const char* fmt, ...) {
     g_err = buf;
     return code;
 }
+namespace b200 {
+void set_last_error(const char* msg) { g_err = msg ? msg : ""; }
+}  // namespace b200
 #define CU_TRY(expr)                                                                                      \
     do {                                                                                                  \
         cudaError_t e_ = (expr);                                                                          \

@@ -130,6 +130,9 @@ struct GemmParams {
 int launch_gemm(const GemmParams& p, cudaStream_t st);
 const char* gemm_error();
 
+// records the message b200_last_error() returns for the calling thread (defined in api.cu)
+void set_last_error(const char* msg);
+
 // hop
 // payload == nullptr: the payload was already written in place; only publish the flag
 void launch_hop_send(const void* payload, int64_t bytes, void* peer_slot, uint64_t* peer_flag, uint64_t seq,

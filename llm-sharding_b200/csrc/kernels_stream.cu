@@ -3,6 +3,10 @@
 // embedding gather, arg-max, KV page bookkeeping.  Replaces the per-op ATen launches under
 // HF LlamaDecoderLayer (transformers modeling_llama.py:62-67,138-168,182-184,303-332) that the
 // reference calls from utils/shard_loader.py:66-74.
+#include <stdio.h>
+
+#include <mutex>
+
 #include "common.cuh"
 #include "internal.h"
 
@@ -597,6 +601,111 @@ void launch_attn_decode(const AttnDecodeParams& p, int M, cudaStream_t st) {
     dim3 grid2(p.n_heads, M);
     attn_decode_combine_kernel<<<grid2, kHeadDim, 0, st>>>(p);
 }
+
+// =========================================================================== decode attention, allocation-free
+// b200_attn_decode_static: the same split-K decode attention as b200_attn_decode, for callers that cannot
+// allocate device memory at all.
+//
+// Who that is: (1) a host runtime that has already handed every byte of HBM to its own pool (a serving process
+// whose KV pages and weights fill the card, or a torch process whose caching allocator owns the memory) — a
+// cudaMalloc for the split-K partials would either fail or have to come out of somebody else's budget;
+// (2) a latency-sensitive loop (one call per generated token) that must not risk the device-wide
+// synchronisation cudaMalloc / cudaFree imply; (3) a tool that probes attention over K/V pages it already owns
+// (a profiler, a parity checker) and has no shard handle whose workspace it could borrow.
+//
+// How: the partials live in the file-scope __device__ array below instead of caller memory.  Every GPU that
+// loads this library carries the array (kStaticScratchBytes, about 2 MiB) until the process exits.  The kernels
+// are the ones b200_attn_decode launches; only the scratch pointer differs.
+//
+// Rules for callers:
+//  * Capacity: rows * n_heads * n_splits <= kStaticPartials (4096).  Larger problems are refused with
+//    B200_EINVAL and a message; use b200_attn_decode with your own scratch for those.
+//  * The first call on each device resolves the array's device address (cudaGetSymbolAddress, with that device
+//    current) and caches it.  Make that first call before you begin any stream capture on that device.
+//  * The array is shared by every call in the process and keeps whatever the previous call left in it.
+//    Nothing in it has to start at zero: each (row, head, split) partial is written by the split kernel —
+//    empty splits included — before the combine kernel reads it, so there is nothing to clear between calls.
+//  * Because it is shared, two calls whose kernels can overlap on the GPU (different streams, or different
+//    host threads on different streams) race on it and corrupt each other.  Issue them on one stream, or order
+//    them with events.
+//  * No cudaMalloc / cudaFree / allocating library routine is called, here or in the launcher.
+constexpr int kStaticPartials = 4096;
+constexpr size_t kStaticScratchFloats = (size_t)kStaticPartials * kPartStride;
+constexpr size_t kStaticScratchBytes = kStaticScratchFloats * sizeof(float);  // 2,129,920 bytes
+static __device__ __align__(256) float g_attn_static_scratch[kStaticScratchFloats];
+
+constexpr int kMaxDevices = 64;
+static float* g_static_scratch_dev[kMaxDevices];  // per device: resolved DEVICE address of the array above
+static std::mutex g_static_scratch_mu;
+
+// In host code `g_attn_static_scratch` is only a handle for the symbol, not an address a kernel may use.
+static cudaError_t static_scratch_for_current_device(float** out) {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= kMaxDevices) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(g_static_scratch_mu);
+    if (g_static_scratch_dev[dev] == nullptr) {
+        float* ptr = nullptr;
+        e = cudaGetSymbolAddress((void**)&ptr, g_attn_static_scratch);
+        if (e != cudaSuccess) return e;
+        if (ptr == nullptr) return cudaErrorInvalidSymbol;
+        g_static_scratch_dev[dev] = ptr;
+    }
+    *out = g_static_scratch_dev[dev];
+    return cudaSuccess;
+}
+
+}  // namespace b200
+
+extern "C" __attribute__((visibility("default"))) int b200_attn_decode_static(
+    const float* q, const void* k_pool, const void* v_pool, const int32_t* block_table, const int32_t* t_end, int rows,
+    int n_heads, int n_kv_heads, int page_size, int max_pages_per_row, int n_splits, float* out, void* stream) {
+    using namespace b200;
+    char msg[256];
+    if (q == nullptr || k_pool == nullptr || v_pool == nullptr || block_table == nullptr || t_end == nullptr || out == nullptr) {
+        set_last_error("[ERROR] null argument");
+        return -1;
+    }
+    if (rows < 1 || rows > kMaxBatch || n_heads < 1 || n_kv_heads < 1 || n_heads % n_kv_heads != 0 || page_size < 64 ||
+        page_size % 64 != 0 || max_pages_per_row < 1 || n_splits < 1 || n_splits > kMaxSplits ||
+        ((int64_t)max_pages_per_row * page_size + n_splits - 1) / n_splits > kMaxChunkKeys) {
+        snprintf(msg, sizeof(msg), "[ERROR] attn_decode_static: need 1 <= rows <= %d, n_heads %% n_kv_heads == 0, page_size %% 64 == 0, "
+                 "1 <= n_splits <= %d and at most %d keys per split", kMaxBatch, kMaxSplits, kMaxChunkKeys);
+        set_last_error(msg);
+        return -1;
+    }
+    const int64_t partials = (int64_t)rows * n_heads * n_splits;
+    if (partials > kStaticPartials) {
+        snprintf(msg, sizeof(msg), "[ERROR] attn_decode_static: rows*n_heads*n_splits = %lld exceeds the built-in scratch (%d partials, "
+                 "%zu bytes); use b200_attn_decode with caller-provided scratch", (long long)partials, kStaticPartials, kStaticScratchBytes);
+        set_last_error(msg);
+        return -1;
+    }
+    float* scratch = nullptr;
+    cudaError_t e = static_scratch_for_current_device(&scratch);
+    if (e != cudaSuccess) {
+        snprintf(msg, sizeof(msg), "[ERROR] CUDA: could not resolve the built-in scratch array on this device: %s", cudaGetErrorString(e));
+        set_last_error(msg);
+        return -3;
+    }
+    AttnDecodeParams a{};
+    a.q = q; a.k_pool = reinterpret_cast<const __nv_bfloat16*>(k_pool); a.v_pool = reinterpret_cast<const __nv_bfloat16*>(v_pool);
+    a.block_table = block_table; a.t_end = t_end;
+    for (int i = 0; i < rows; ++i) a.slots.v[i] = i;
+    a.S = 1; a.n_heads = n_heads; a.n_kv = n_kv_heads; a.page_size = page_size; a.max_pages_per_slot = max_pages_per_row;
+    a.n_splits = n_splits; a.part = scratch; a.out = out;
+    launch_attn_decode(a, rows, (cudaStream_t)stream);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        snprintf(msg, sizeof(msg), "[ERROR] CUDA: %s (attn_decode_static launch)", cudaGetErrorString(e));
+        set_last_error(msg);
+        return -3;
+    }
+    return 0;
+}
+
+namespace b200 {
 
 // =========================================================================== RoPE + KV append (GEMM path)
 // apply_rotary_pos_emb (modeling_llama.py:146-168) on the fused QKV GEMM output, then
