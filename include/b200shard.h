@@ -181,6 +181,9 @@ B200_API int b200_attn_decode_static(const float* d_q, const void* d_k_pool, con
                                      void* stream);
 /* out[M,N] (fp32) = A[M,K] (bf16) * W[N,K]^T (bf16): the tcgen05/TMA GEMM used for prefill */
 B200_API int b200_gemm_bf16(const void* d_a, const void* d_w, int M, int N, int K, float* d_out, void* stream);
+/* same kernel with fp16 operands (A[M,K] and W[N,K] both fp16): what the shard path runs — it holds the bf16 model
+ * weights as fp16 (exact in fp16's normal range) so that activations carry 10 mantissa bits into the tensor cores */
+B200_API int b200_gemm_f16(const void* d_a, const void* d_w, int M, int N, int K, float* d_out, void* stream);
 /* out[M,N] (fp32) = X[M,K] (fp32) * W[N,K]^T (bf16), M <= 4: the weight-streaming decode kernel */
 B200_API int b200_gemv_bf16(const float* d_x, const void* d_w, int M, int N, int K, float* d_out, void* stream);
 

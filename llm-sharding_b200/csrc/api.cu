@@ -58,7 +58,7 @@ struct b200_shard {
     __nv_bfloat16 *final_norm = nullptr, *lm_head = nullptr, *embedding = nullptr;
     // workspace
     float* x = nullptr;                 // fp32 residual stream [max_tokens, H]
-    __nv_bfloat16 *xn = nullptr, *qkv = nullptr, *qrot = nullptr, *attn_b = nullptr, *act_b = nullptr;
+    __nv_bfloat16 *xn = nullptr, *qrot = nullptr, *qrot_lo = nullptr, *attn_b = nullptr, *act_b = nullptr;  // 16-bit staging (xn / attn_b / act_b hold fp16)
     float *q_f = nullptr, *attn_f = nullptr, *act_f = nullptr;  // GEMV path (<= 4 rows), fp32
     float *lastrow = nullptr, *logits = nullptr, *attn_part = nullptr;
     __nv_bfloat16* lastrow_b = nullptr;
@@ -129,8 +129,8 @@ extern "C" B200_API int b200_shard_create(const b200_shard_config_t* c, int devi
     auto& A = s->allocs;
     r |= dev_alloc(A, &s->x, MT * H);
     r |= dev_alloc(A, &s->xn, MT * H);
-    r |= dev_alloc(A, &s->qkv, MT * s->qkv_rows);
     r |= dev_alloc(A, &s->qrot, MT * s->nq);
+    r |= dev_alloc(A, &s->qrot_lo, MT * s->nq);
     r |= dev_alloc(A, &s->attn_b, MT * s->nq);
     r |= dev_alloc(A, &s->act_b, MT * I);
     r |= dev_alloc(A, &s->q_f, (size_t)kMaxGemvRows * s->nq);
@@ -193,13 +193,13 @@ extern "C" B200_API int b200_shard_set_layer(b200_shard_t* s, int rel, const voi
         L.norm1 = reinterpret_cast<__nv_bfloat16*>(b + o_n1);
         L.norm2 = reinterpret_cast<__nv_bfloat16*>(b + o_n2);
     }
-    launch_convert_to_bf16(q, dtype, L.wqkv, (int64_t)s->nq * H, st);
-    launch_convert_to_bf16(k, dtype, L.wqkv + (size_t)s->nq * H, (int64_t)s->nkvd * H, st);
-    launch_convert_to_bf16(v, dtype, L.wqkv + (size_t)(s->nq + s->nkvd) * H, (int64_t)s->nkvd * H, st);
-    launch_convert_to_bf16(o, dtype, L.wo, (int64_t)n_o, st);
+    launch_convert_to_bf16(q, dtype, L.wqkv, (int64_t)s->nq * H, st, true);
+    launch_convert_to_bf16(k, dtype, L.wqkv + (size_t)s->nq * H, (int64_t)s->nkvd * H, st, true);
+    launch_convert_to_bf16(v, dtype, L.wqkv + (size_t)(s->nq + s->nkvd) * H, (int64_t)s->nkvd * H, st, true);
+    launch_convert_to_bf16(o, dtype, L.wo, (int64_t)n_o, st, true);
     launch_pack_gate_up(gate, dtype, L.wgu, (int)I, (int)H, 0, st);
     launch_pack_gate_up(up, dtype, L.wgu, (int)I, (int)H, 1, st);
-    launch_convert_to_bf16(down, dtype, L.wdown, (int64_t)n_dn, st);
+    launch_convert_to_bf16(down, dtype, L.wdown, (int64_t)n_dn, st, true);
     launch_convert_to_bf16(n1, dtype, L.norm1, (int64_t)H, st);
     launch_convert_to_bf16(n2, dtype, L.norm2, (int64_t)H, st);
     CU_TRY(cudaGetLastError());
@@ -209,12 +209,12 @@ extern "C" B200_API int b200_shard_set_layer(b200_shard_t* s, int rel, const voi
 }
 
 static int set_single(b200_shard_t* s, __nv_bfloat16** dst, const void* w, size_t n, int dtype, void* stream, int present,
-                      const char* what) {
+                      const char* what, bool f16_out = false) {
     if (s == nullptr || w == nullptr) return fail(B200_EINVAL, "[ERROR] null argument");
     if (!present) return fail(B200_ESTATE, "[ERROR] this shard was created without %s", what);
     CU_TRY(cudaSetDevice(s->device));
     if (*dst == nullptr) TRY(dev_alloc(s->allocs, dst, n));
-    launch_convert_to_bf16(w, dtype, *dst, (int64_t)n, (cudaStream_t)stream);
+    launch_convert_to_bf16(w, dtype, *dst, (int64_t)n, (cudaStream_t)stream, f16_out);
     CU_TRY(cudaGetLastError());
     CU_TRY(cudaStreamSynchronize((cudaStream_t)stream));
     return 0;
@@ -224,7 +224,7 @@ extern "C" B200_API int b200_shard_set_final_norm(b200_shard_t* s, const void* w
 }
 extern "C" B200_API int b200_shard_set_lm_head(b200_shard_t* s, const void* w, int dtype, void* stream) {
     return set_single(s, &s->lm_head, w, s ? (size_t)s->cfg.vocab_size * s->cfg.hidden_size : 0, dtype, stream,
-                      s ? s->cfg.has_lm_head : 0, "an lm_head");
+                      s ? s->cfg.has_lm_head : 0, "an lm_head", true);
 }
 extern "C" B200_API int b200_shard_set_embedding(b200_shard_t* s, const void* w, int dtype, void* stream) {
     return set_single(s, &s->embedding, w, s ? (size_t)s->cfg.vocab_size * s->cfg.hidden_size : 0, dtype, stream,
@@ -378,26 +378,31 @@ static int enqueue_forward(b200_shard_t* s, b200_kv_t* kv, const SlotList& sl, c
             launch_gemv(d, M, EPI_RESID, false, s->num_sms, st);
             s->n_launch += 6;
         } else {
-            launch_rmsnorm_bf16(s->x, L.norm1, c.rms_eps, M, H, s->xn, st);
-            GemmParams g{s->xn, L.wqkv, M, s->qkv_rows, H, s->qkv, GEMM_STORE_BF16};
+            // activations feeding the tensor cores are fp16 (10 mantissa bits) against exact bf16 weights; q reaches
+            // attention as a (hi, lo) bf16 pair; K/V are rounded to bf16 exactly once, inside the QKV epilogue
+            launch_rmsnorm_bf16(s->x, L.norm1, c.rms_eps, M, H, s->xn, st, true);
+            GemmParams g{};
+            g.A = s->xn; g.W = L.wqkv; g.M = M; g.N = s->qkv_rows; g.K = H; g.out = nullptr; g.epi = GEMM_QKV_ROPE; g.ab_f16 = 1;
+            g.q_hi = s->qrot; g.q_lo = s->qrot_lo; g.k_pool = kp; g.v_pool = vp; g.kv_off = s->tm.kv_off;
+            g.cos = s->tm.cos; g.sin = s->tm.sin; g.n_heads = c.n_heads; g.n_kv = c.n_kv_heads; g.head_stride = head_stride;
             if (launch_gemm(g, st) != 0) return fail(B200_ECUDA, "[ERROR] %s", gemm_error());
-            RopeAppendParams ra{};
-            ra.qkv = s->qkv; ra.q_out = s->qrot; ra.k_pool = kp; ra.v_pool = vp; ra.kv_off = s->tm.kv_off;
-            ra.cos = s->tm.cos; ra.sin = s->tm.sin; ra.n_heads = c.n_heads; ra.n_kv = c.n_kv_heads; ra.head_stride = head_stride;
-            launch_rope_append(ra, M, st);
             AttnPrefillParams ap{};
-            ap.q = s->qrot; ap.k_pool = kp; ap.v_pool = vp; ap.block_table = kv->dev.block_table; ap.call_base = s->tm.call_base;
+            ap.q = s->qrot; ap.q_lo = s->qrot_lo; ap.out_f16 = 1; ap.k_pool = kp; ap.v_pool = vp; ap.block_table = kv->dev.block_table; ap.call_base = s->tm.call_base;
             ap.slots = sl; ap.B = B; ap.S = S; ap.causal = causal; ap.n_heads = c.n_heads; ap.n_kv = c.n_kv_heads;
             ap.page_size = kv->dev.page_size; ap.max_pages_per_slot = kv->dev.max_pages_per_slot; ap.out = s->attn_b;
             launch_attn_prefill(ap, st);
-            GemmParams o{s->attn_b, L.wo, M, H, s->nq, s->x, GEMM_RESID_F32};
+            GemmParams o{};
+            o.A = s->attn_b; o.W = L.wo; o.M = M; o.N = H; o.K = s->nq; o.out = s->x; o.epi = GEMM_RESID_F32; o.ab_f16 = 1;
             if (launch_gemm(o, st) != 0) return fail(B200_ECUDA, "[ERROR] %s", gemm_error());
-            launch_rmsnorm_bf16(s->x, L.norm2, c.rms_eps, M, H, s->xn, st);
-            GemmParams gu{s->xn, L.wgu, M, 2 * I, H, s->act_b, GEMM_SWIGLU_BF16};
+            launch_rmsnorm_bf16(s->x, L.norm2, c.rms_eps, M, H, s->xn, st, true);
+            GemmParams gu{};
+            gu.A = s->xn; gu.W = L.wgu; gu.M = M; gu.N = 2 * I; gu.K = H; gu.out = s->act_b; gu.epi = GEMM_SWIGLU_BF16;
+            gu.ab_f16 = 1; gu.out_f16 = 1;
             if (launch_gemm(gu, st) != 0) return fail(B200_ECUDA, "[ERROR] %s", gemm_error());
-            GemmParams d{s->act_b, L.wdown, M, H, I, s->x, GEMM_RESID_F32};
+            GemmParams d{};
+            d.A = s->act_b; d.W = L.wdown; d.M = M; d.N = H; d.K = I; d.out = s->x; d.epi = GEMM_RESID_F32; d.ab_f16 = 1;
             if (launch_gemm(d, st) != 0) return fail(B200_ECUDA, "[ERROR] %s", gemm_error());
-            s->n_launch += 8;
+            s->n_launch += 7;
         }
     }
     if (out != nullptr) {  // final RMSNorm when this is the tail shard (utils/shard_loader.py:76-77), else a plain cast
@@ -420,8 +425,10 @@ static int enqueue_tail(b200_shard_t* s, int B, int64_t* tok, float* margin, cud
         g.W = s->lm_head; g.x = s->lastrow; g.N = c.vocab_size; g.K = c.hidden_size; g.out = s->logits;
         launch_gemv(g, B, EPI_STORE, false, s->num_sms, st);
     } else {
-        launch_rmsnorm_bf16(s->lastrow, nullptr, 0.f, B, c.hidden_size, s->lastrow_b, st);
-        GemmParams g{s->lastrow_b, s->lm_head, B, c.vocab_size, c.hidden_size, s->logits, GEMM_STORE_F32};
+        launch_rmsnorm_bf16(s->lastrow, nullptr, 0.f, B, c.hidden_size, s->lastrow_b, st, true);
+        GemmParams g{};
+        g.A = s->lastrow_b; g.W = s->lm_head; g.M = B; g.N = c.vocab_size; g.K = c.hidden_size; g.out = s->logits;
+        g.epi = GEMM_STORE_F32; g.ab_f16 = 1;
         if (launch_gemm(g, st) != 0) return fail(B200_ECUDA, "[ERROR] %s", gemm_error());
         s->n_launch += 1;
     }
@@ -499,7 +506,7 @@ static int forward_impl(b200_shard_t* s, b200_kv_t* kv, const int32_t* h_slots, 
             it = s->graph_cache.emplace(key, exec).first;
         }
         CU_TRY(cudaGraphLaunch(it->second, st));
-        s->n_launch += 3 + (uint64_t)s->cfg.n_layers * (B <= gemv_row_limit(s) ? 6 : 8) + (out ? 1 : 0) + (with_tail ? 3 : 0) + (tok_in ? 1 : 0);
+        s->n_launch += 3 + (uint64_t)s->cfg.n_layers * (B <= gemv_row_limit(s) ? 6 : 7) + (out ? 1 : 0) + (with_tail ? 3 : 0) + (tok_in ? 1 : 0);
         done = true;
     }
     if (!done) {
@@ -768,7 +775,17 @@ extern "C" B200_API int b200_attn_decode(const float* q, const void* k_pool, con
 }
 extern "C" B200_API int b200_gemm_bf16(const void* a, const void* w, int M, int N, int K, float* out, void* stream) {
     if (a == nullptr || w == nullptr || out == nullptr) return fail(B200_EINVAL, "[ERROR] null argument");
-    GemmParams g{reinterpret_cast<const __nv_bfloat16*>(a), reinterpret_cast<const __nv_bfloat16*>(w), M, N, K, out, GEMM_STORE_F32};
+    GemmParams g{};
+    g.A = a; g.W = w; g.M = M; g.N = N; g.K = K; g.out = out; g.epi = GEMM_STORE_F32;
+    if (launch_gemm(g, (cudaStream_t)stream) != 0) return fail(B200_EINVAL, "[ERROR] %s", gemm_error());
+    CU_TRY(cudaGetLastError());
+    return 0;
+}
+extern "C" B200_API int b200_gemm_f16(const void* a, const void* w, int M, int N, int K, float* out, void* stream) {
+    if (a == nullptr || w == nullptr || out == nullptr) return fail(B200_EINVAL, "[ERROR] null argument");
+    GemmParams g{};
+    g.A = a; g.W = reinterpret_cast<const __nv_bfloat16*>(w); g.M = M; g.N = N; g.K = K; g.out = out; g.epi = GEMM_STORE_F32;
+    g.ab_f16 = 1;
     if (launch_gemm(g, (cudaStream_t)stream) != 0) return fail(B200_EINVAL, "[ERROR] %s", gemm_error());
     CU_TRY(cudaGetLastError());
     return 0;
@@ -781,7 +798,7 @@ extern "C" B200_API int b200_gemv_bf16(const float* x, const void* w, int M, int
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     GemvParams g{};
-    g.W = reinterpret_cast<const __nv_bfloat16*>(w); g.x = x; g.N = N; g.K = K; g.out = out;
+    g.W = w; g.w_bf16 = 1; g.x = x; g.N = N; g.K = K; g.out = out;
     launch_gemv(g, M, EPI_STORE, false, sms, (cudaStream_t)stream);
     CU_TRY(cudaGetLastError());
     return 0;

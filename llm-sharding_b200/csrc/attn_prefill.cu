@@ -47,6 +47,8 @@ __global__ void __launch_bounds__(kPrefillThreads) attn_prefill_kernel(const Att
     uint8_t* sQ = smem;                      // 16 KB (reused to stage the output)
     uint8_t* sK = smem + kTileBytes;         // 2 x 16 KB
     uint8_t* sV = smem + 3 * kTileBytes;     // 2 x 16 KB
+    uint8_t* sQlo = smem + 5 * kTileBytes;   // 16 KB, only when q arrives as a (hi, lo) bf16 pair
+    const bool split_q = p.q_lo != nullptr;
     const int qt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int q0 = qt * kBM;
@@ -69,6 +71,7 @@ __global__ void __launch_bounds__(kPrefillThreads) attn_prefill_kernel(const Att
         const bool ok = (q0 + r) < p.S;
         const __nv_bfloat16* src = p.q + (((size_t)b * p.S + (ok ? q0 + r : 0)) * p.n_heads + h) * kHeadDim + c * 8;
         cp_async16(smem_u32(sQ) + swz(r, c), src, ok);
+        if (split_q) cp_async16(smem_u32(sQlo) + swz(r, c), p.q_lo + (src - p.q), ok);
     }
     auto load_kv = [&](int kt, int stage) {
         const int t0 = kt * kBN;
@@ -91,7 +94,6 @@ __global__ void __launch_bounds__(kPrefillThreads) attn_prefill_kernel(const Att
 #pragma unroll
     for (int i = 0; i < 16; ++i) { o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f; }
     float m_run[2] = {-INFINITY, -INFINITY}, l_run[2] = {0.f, 0.f};
-    uint32_t qf[8][4];
     const float scale_log2 = 0.08838834764831845f * 1.4426950408889634f;
     const int row0 = q0 + warp * 16 + (lane >> 2);  // sequence index of this thread's first row (second: +8)
 
@@ -101,26 +103,33 @@ __global__ void __launch_bounds__(kPrefillThreads) attn_prefill_kernel(const Att
         cp_async_commit();
         cp_async_wait<1>();
         __syncthreads();
-        if (kt == 0) {
-#pragma unroll
-            for (int ks = 0; ks < 8; ++ks) {
-                const int mi = lane >> 3, r = lane & 7;
-                ldsm_x4(smem_u32(sQ) + swz(warp * 16 + (mi & 1) * 8 + r, ks * 2 + (mi >> 1)), qf[ks][0], qf[ks][1], qf[ks][2], qf[ks][3]);
-            }
-        }
         const uint32_t kb = smem_u32(sK) + stage * kTileBytes, vb = smem_u32(sV) + stage * kTileBytes;
-        // ---- S = Q K^T
+        // ---- S = Q K^T  (Q fragments are re-read from shared memory per k-step pair: with the hi/lo split they
+        //      would not fit in registers next to the 64 output accumulators)
         float s[8][4];
 #pragma unroll
-        for (int nt = 0; nt < 8; ++nt) {
-            s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
+        for (int nt = 0; nt < 8; ++nt) s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
 #pragma unroll
-            for (int ks = 0; ks < 8; ks += 2) {
+        for (int ks = 0; ks < 8; ks += 2) {
+            const int mi = lane >> 3, r = lane & 7;
+            uint32_t qh0[4], qh1[4], ql0[4], ql1[4];
+            const int qrow = warp * 16 + (mi & 1) * 8 + r;
+            ldsm_x4(smem_u32(sQ) + swz(qrow, ks * 2 + (mi >> 1)), qh0[0], qh0[1], qh0[2], qh0[3]);
+            ldsm_x4(smem_u32(sQ) + swz(qrow, ks * 2 + 2 + (mi >> 1)), qh1[0], qh1[1], qh1[2], qh1[3]);
+            if (split_q) {
+                ldsm_x4(smem_u32(sQlo) + swz(qrow, ks * 2 + (mi >> 1)), ql0[0], ql0[1], ql0[2], ql0[3]);
+                ldsm_x4(smem_u32(sQlo) + swz(qrow, ks * 2 + 2 + (mi >> 1)), ql1[0], ql1[1], ql1[2], ql1[3]);
+            }
+#pragma unroll
+            for (int nt = 0; nt < 8; ++nt) {
                 uint32_t b0, b1, b2, b3;
-                const int mi = lane >> 3, r = lane & 7;
                 ldsm_x4(kb + swz(nt * 8 + r, ks * 2 + mi), b0, b1, b2, b3);
-                mma_bf16(s[nt], qf[ks], b0, b1);
-                mma_bf16(s[nt], qf[ks + 1], b2, b3);
+                mma_bf16(s[nt], qh0, b0, b1);
+                mma_bf16(s[nt], qh1, b2, b3);
+                if (split_q) {
+                    mma_bf16(s[nt], ql0, b0, b1);
+                    mma_bf16(s[nt], ql1, b2, b3);
+                }
             }
         }
         // ---- mask + online softmax (fp32)
@@ -191,21 +200,30 @@ __global__ void __launch_bounds__(kPrefillThreads) attn_prefill_kernel(const Att
 #pragma unroll
     for (int dt = 0; dt < 16; ++dt) {
         const int col = dt * 8 + (lane & 3) * 2;  // element column
-        *reinterpret_cast<uint32_t*>(sQ + swz(lr, col >> 3) + (col & 7) * 2) = pack_bf16(o[dt][0] * inv0, o[dt][1] * inv0);
-        *reinterpret_cast<uint32_t*>(sQ + swz(lr + 8, col >> 3) + (col & 7) * 2) = pack_bf16(o[dt][2] * inv1, o[dt][3] * inv1);
+        uint32_t w0, w1;
+        if (p.out_f16) {
+            __half2 t0 = __floats2half2_rn(o[dt][0] * inv0, o[dt][1] * inv0), t1 = __floats2half2_rn(o[dt][2] * inv1, o[dt][3] * inv1);
+            w0 = *reinterpret_cast<uint32_t*>(&t0);
+            w1 = *reinterpret_cast<uint32_t*>(&t1);
+        } else {
+            w0 = pack_bf16(o[dt][0] * inv0, o[dt][1] * inv0);
+            w1 = pack_bf16(o[dt][2] * inv1, o[dt][3] * inv1);
+        }
+        *reinterpret_cast<uint32_t*>(sQ + swz(lr, col >> 3) + (col & 7) * 2) = w0;
+        *reinterpret_cast<uint32_t*>(sQ + swz(lr + 8, col >> 3) + (col & 7) * 2) = w1;
     }
     __syncthreads();
     for (int i = tid; i < 64 * 16; i += kPrefillThreads) {
         const int r = i >> 4, c = i & 15;
         if (q0 + r < p.S) {
             const uint4 v = *reinterpret_cast<const uint4*>(sQ + swz(r, c));
-            *reinterpret_cast<uint4*>(p.out + (((size_t)b * p.S + q0 + r) * p.n_heads + h) * kHeadDim + c * 8) = v;
+            *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out) + (((size_t)b * p.S + q0 + r) * p.n_heads + h) * kHeadDim + c * 8) = v;
         }
     }
 }
 
 void launch_attn_prefill(const AttnPrefillParams& p, cudaStream_t st) {
-    const size_t smem = 5 * kTileBytes;
+    const size_t smem = 6 * kTileBytes;
     cudaFuncSetAttribute(attn_prefill_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     dim3 grid((p.S + kBM - 1) / kBM, p.n_heads, p.B);
     attn_prefill_kernel<<<grid, kPrefillThreads, smem, st>>>(p);

@@ -7,7 +7,7 @@
 // 128B-swizzled 128x64 tiles of A and W through a 6-stage mbarrier ring), warp 1 = single-thread
 // tcgen05.mma issuer (UMMA 128x128x16, accumulator = 128 TMEM columns), warps 2..5 = epilogue
 // (tcgen05.ld 32x32b, one accumulator row per thread) with the fused epilogues:
-//   STORE_BF16 (QKV), RESID_F32 (o_proj / down_proj + residual add, modeling_llama.py:325,331),
+//   QKV_ROPE (RoPE + paged K/V append + hi/lo split of q), STORE_BF16, RESID_F32 (o_proj / down_proj + residual add, modeling_llama.py:325,331),
 //   SWIGLU_BF16 (silu(gate)*up on the paired gate/up weight layout, :183), STORE_F32 (lm_head).
 #include <cuda.h>
 #include <cuda_runtime.h>
@@ -61,8 +61,18 @@ __device__ __forceinline__ uint64_t umma_desc(uint32_t smem_addr) {
     d |= (uint64_t)2 << 61;                       // SWIZZLE_128B
     return d;
 }
-// kind::f16 instruction descriptor: D=f32, A=B=bf16, both K-major, N=128, M=128
-constexpr uint32_t kIdesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(kBlkN >> 3) << 17) | ((uint32_t)(kBlkM >> 4) << 24);
+// kind::f16 instruction descriptor: D=f32, both operands K-major, N=128, M=128.  Operand format (a_format bits 7..9,
+// b_format bits 10..12): 1 = bf16, 0 = fp16; the two must agree (a mixed fp16 x bf16 descriptor is an illegal
+// instruction on sm_100a — measured).  The shard path runs fp16 x fp16: the bf16 model weights are held as fp16
+// (exact for every bf16 value in fp16's normal range) so that activations can carry 10 mantissa bits — 8x less
+// rounding than bf16 — into the tensor cores at no cost.
+constexpr uint32_t kIdescBase = (1u << 4) | ((uint32_t)(kBlkN >> 3) << 17) | ((uint32_t)(kBlkM >> 4) << 24);
+__device__ __forceinline__ uint32_t pack_f16(float a, float b) {
+    a = fminf(fmaxf(a, -65504.f), 65504.f);
+    b = fminf(fmaxf(b, -65504.f), 65504.f);
+    __half2 t = __floats2half2_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&t);
+}
 
 __device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accum) {
     asm volatile(
@@ -100,6 +110,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n_blk = blockIdx.x, m_blk = blockIdx.y;
     const int num_k = (p.K + kBlkK - 1) / kBlkK;
+    const uint32_t idesc = kIdescBase | (p.ab_f16 ? 0u : ((1u << 7) | (1u << 10)));
 
     if (warp == 0 && lane == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_a) : "memory");
@@ -139,7 +150,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
                 const uint32_t sa = base + st * kStageBytes, sb = sa + kStageBytesA;
 #pragma unroll
                 for (int k = 0; k < kBlkK / 16; ++k)
-                    umma_f16(tmem_base, umma_desc(sa + k * 32), umma_desc(sb + k * 32), kIdesc, (kb > 0 || k > 0) ? 1u : 0u);
+                    umma_f16(tmem_base, umma_desc(sa + k * 32), umma_desc(sb + k * 32), idesc, (kb > 0 || k > 0) ? 1u : 0u);
                 umma_commit(empty0 + 8 * st);  // frees the smem slot when these MMAs retire
             }
             umma_commit(tmem_full);            // accumulator complete
@@ -169,9 +180,69 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
                             for (int e = 0; e < 4; ++e) {
                                 const float g0 = __uint_as_float(g[v * 8 + 2 * e]), g1 = __uint_as_float(g[v * 8 + 2 * e + 1]);
                                 const float u0 = __uint_as_float(u[v * 8 + 2 * e]), u1 = __uint_as_float(u[v * 8 + 2 * e + 1]);
-                                w[e] = pack_bf16(silu(g0) * u0, silu(g1) * u1);
+                                w[e] = p.out_f16 ? pack_f16(silu(g0) * u0, silu(g1) * u1) : pack_bf16(silu(g0) * u0, silu(g1) * u1);
                             }
                             *reinterpret_cast<uint4*>(out + (size_t)row * No + col0 + v * 8) = make_uint4(w[0], w[1], w[2], w[3]);
+                        }
+                    }
+                }
+            }
+        } else if (EPI == GEMM_QKV_ROPE) {
+            // one 128-column tile = one head: apply_rotary_pos_emb (modeling_llama.py:146-168) in fp32 on the
+            // accumulator, then q -> (hi, lo) bf16 pair, k / v -> bf16 straight into the KV pages
+            // (DynamicCache.update, cache_utils.py:102-121, as a paged write).  A single rounding per value.
+            const int head = n_blk;
+            const bool is_q = head < p.n_heads, is_k = !is_q && head < p.n_heads + p.n_kv;
+#pragma unroll 1
+            for (int c = 0; c < 2; ++c) {
+                uint32_t a[32], b[32];
+                tmem_ld32(trow + c * 32, a);
+                tmem_ld32(trow + 64 + c * 32, b);
+                if (row_ok) {
+                    const int j0 = c * 32;
+                    float lo[32], hi[32];
+                    if (is_q || is_k) {
+                        const float4* cs4 = reinterpret_cast<const float4*>(p.cos + (size_t)row * kHalfDim + j0);
+                        const float4* sn4 = reinterpret_cast<const float4*>(p.sin + (size_t)row * kHalfDim + j0);
+#pragma unroll
+                        for (int v = 0; v < 8; ++v) {
+                            const float4 cs = cs4[v], sn = sn4[v];
+                            const float cc[4] = {cs.x, cs.y, cs.z, cs.w}, ss[4] = {sn.x, sn.y, sn.z, sn.w};
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) {
+                                const float x = __uint_as_float(a[v * 4 + e]), y = __uint_as_float(b[v * 4 + e]);
+                                lo[v * 4 + e] = x * cc[e] - y * ss[e];
+                                hi[v * 4 + e] = y * cc[e] + x * ss[e];
+                            }
+                        }
+                    } else {
+#pragma unroll
+                        for (int e = 0; e < 32; ++e) { lo[e] = __uint_as_float(a[e]); hi[e] = __uint_as_float(b[e]); }
+                    }
+                    __nv_bfloat16* dst;
+                    if (is_q) dst = p.q_hi + ((size_t)row * p.n_heads + head) * kHeadDim + j0;
+                    else if (is_k) dst = p.k_pool + p.kv_off[row] + (int64_t)(head - p.n_heads) * p.head_stride + j0;
+                    else dst = p.v_pool + p.kv_off[row] + (int64_t)(head - p.n_heads - p.n_kv) * p.head_stride + j0;
+#pragma unroll
+                    for (int v = 0; v < 4; ++v) {
+                        *reinterpret_cast<uint4*>(dst + v * 8) = make_uint4(pack_bf16(lo[v * 8 + 0], lo[v * 8 + 1]), pack_bf16(lo[v * 8 + 2], lo[v * 8 + 3]),
+                                                                            pack_bf16(lo[v * 8 + 4], lo[v * 8 + 5]), pack_bf16(lo[v * 8 + 6], lo[v * 8 + 7]));
+                        *reinterpret_cast<uint4*>(dst + kHalfDim + v * 8) = make_uint4(pack_bf16(hi[v * 8 + 0], hi[v * 8 + 1]), pack_bf16(hi[v * 8 + 2], hi[v * 8 + 3]),
+                                                                                       pack_bf16(hi[v * 8 + 4], hi[v * 8 + 5]), pack_bf16(hi[v * 8 + 6], hi[v * 8 + 7]));
+                    }
+                    if (is_q) {  // residual of the bf16 rounding, so that attention sees q with ~16 mantissa bits
+                        __nv_bfloat16* dlo = p.q_lo + ((size_t)row * p.n_heads + head) * kHeadDim + j0;
+#pragma unroll
+                        for (int e = 0; e < 32; ++e) {
+                            lo[e] -= __bfloat162float(__float2bfloat16_rn(lo[e]));
+                            hi[e] -= __bfloat162float(__float2bfloat16_rn(hi[e]));
+                        }
+#pragma unroll
+                        for (int v = 0; v < 4; ++v) {
+                            *reinterpret_cast<uint4*>(dlo + v * 8) = make_uint4(pack_bf16(lo[v * 8 + 0], lo[v * 8 + 1]), pack_bf16(lo[v * 8 + 2], lo[v * 8 + 3]),
+                                                                                pack_bf16(lo[v * 8 + 4], lo[v * 8 + 5]), pack_bf16(lo[v * 8 + 6], lo[v * 8 + 7]));
+                            *reinterpret_cast<uint4*>(dlo + kHalfDim + v * 8) = make_uint4(pack_bf16(hi[v * 8 + 0], hi[v * 8 + 1]), pack_bf16(hi[v * 8 + 2], hi[v * 8 + 3]),
+                                                                                           pack_bf16(hi[v * 8 + 4], hi[v * 8 + 5]), pack_bf16(hi[v * 8 + 6], hi[v * 8 + 7]));
                         }
                     }
                 }
@@ -257,6 +328,10 @@ int launch_gemm(const GemmParams& p, cudaStream_t st) {
         snprintf(g_gemm_err, sizeof(g_gemm_err), "gemm: need K%%8==0, N%%8==0, M>0 (M=%d N=%d K=%d)", p.M, p.N, p.K);
         return -1;
     }
+    if (p.epi == GEMM_QKV_ROPE && (p.N != (p.n_heads + 2 * p.n_kv) * 128 || p.q_hi == nullptr || p.q_lo == nullptr)) {
+        snprintf(g_gemm_err, sizeof(g_gemm_err), "gemm qkv+rope: N must be (n_heads + 2 n_kv) * 128 (N=%d)", p.N);
+        return -1;
+    }
     if (p.epi == GEMM_SWIGLU_BF16 && p.N % 128 != 0) {
         snprintf(g_gemm_err, sizeof(g_gemm_err), "gemm swiglu: packed N must be a multiple of 128 (N=%d)", p.N);
         return -1;
@@ -275,6 +350,7 @@ int launch_gemm(const GemmParams& p, cudaStream_t st) {
         case GEMM_STORE_BF16: B200_GEMM_LAUNCH(GEMM_STORE_BF16) break;
         case GEMM_RESID_F32: B200_GEMM_LAUNCH(GEMM_RESID_F32) break;
         case GEMM_SWIGLU_BF16: B200_GEMM_LAUNCH(GEMM_SWIGLU_BF16) break;
+        case GEMM_QKV_ROPE: B200_GEMM_LAUNCH(GEMM_QKV_ROPE) break;
         default: B200_GEMM_LAUNCH(GEMM_STORE_F32) break;
     }
 #undef B200_GEMM_LAUNCH

@@ -37,7 +37,8 @@ struct TokMeta {
 enum GemvEpi { EPI_STORE = 0, EPI_RESID = 1, EPI_QKV = 2, EPI_SWIGLU = 3 };
 
 struct GemvParams {
-    const __nv_bfloat16* W;  // [N,K] row-major
+    const void* W;           // [N,K] row-major, fp16 (w_bf16 == 0) or bf16
+    int w_bf16 = 0;
     const float* x;          // [M,K] fp32
     const __nv_bfloat16* norm_w;  // [K] (NORM prologue) or nullptr
     float eps;
@@ -62,9 +63,9 @@ void launch_prep(const KvDev& kv, const SlotList& slots, int B, int S, int causa
                  const TokMeta& tm, cudaStream_t st);
 
 void launch_load_residual(const __nv_bfloat16* in, float* x, int64_t n, cudaStream_t st);
-// x fp32 [rows,n] -> bf16; norm_w == nullptr: plain convert
+// x fp32 [rows,n] -> bf16 (or fp16 when f16_out); norm_w == nullptr: plain convert
 void launch_rmsnorm_bf16(const float* x, const __nv_bfloat16* norm_w, float eps, int rows, int n,
-                         __nv_bfloat16* out, cudaStream_t st);
+                         void* out, cudaStream_t st, bool f16_out = false);
 // last-row gather + optional norm, fp32 out [B,n] (input rows b*S+S-1)
 void launch_lastrow_norm_f32(const float* x, const __nv_bfloat16* norm_w, float eps, int B, int S, int n,
                              float* out, cudaStream_t st);
@@ -72,10 +73,10 @@ void launch_lastrow_bf16_to_f32(const __nv_bfloat16* h, int B, int S, int n, flo
 void launch_argmax(const float* logits, int B, int V, int64_t* tok, float* margin, cudaStream_t st);
 void launch_embed(const __nv_bfloat16* table, const int64_t* ids, int n, int H, int V, __nv_bfloat16* out,
                   cudaStream_t st);
-void launch_convert_to_bf16(const void* src, int dtype, __nv_bfloat16* dst, int64_t n, cudaStream_t st);
-// dst rows [dst_row0 + (r/64)*128 + half*64 + r%64] <- src row r (gate: half 0, up: half 1)
-void launch_pack_gate_up(const void* src, int dtype, __nv_bfloat16* dst, int rows, int cols, int half,
-                         cudaStream_t st);
+// src (.pth storage dtype) -> bf16, or -> fp16 (saturating) when f16_out
+void launch_convert_to_bf16(const void* src, int dtype, void* dst, int64_t n, cudaStream_t st, bool f16_out = false);
+// dst rows [(r/64)*128 + half*64 + r%64] <- src row r (gate: half 0, up: half 1); fp16 out
+void launch_pack_gate_up(const void* src, int dtype, void* dst, int rows, int cols, int half, cudaStream_t st);
 
 struct AttnDecodeParams {
     const float* q;            // [M, n_heads*128] fp32 (rope applied)
@@ -105,7 +106,9 @@ struct RopeAppendParams {
 void launch_rope_append(const RopeAppendParams& p, int M, cudaStream_t st);
 
 struct AttnPrefillParams {
-    const __nv_bfloat16* q;    // [B*S, n_heads*128] bf16 (rope applied)
+    const __nv_bfloat16* q;    // [B*S, n_heads*128] bf16 (rope applied): high part
+    const __nv_bfloat16* q_lo; // bf16(q - q_hi) or nullptr: second MMA pass over K so q keeps ~16 mantissa bits
+    int out_f16;               // output element type: 0 bf16, 1 fp16
     const __nv_bfloat16* k_pool;
     const __nv_bfloat16* v_pool;
     const int32_t* block_table;
@@ -113,18 +116,30 @@ struct AttnPrefillParams {
     SlotList slots;
     int B, S, causal;
     int n_heads, n_kv, page_size, max_pages_per_slot;
-    __nv_bfloat16* out;        // [B*S, n_heads*128]
+    void* out;                 // [B*S, n_heads*128] 16-bit
 };
 void launch_attn_prefill(const AttnPrefillParams& p, cudaStream_t st);
 
 // tcgen05 GEMM: C[M,N] = A[M,K] * W[N,K]^T with fused epilogues
-enum GemmEpi { GEMM_STORE_BF16 = 0, GEMM_RESID_F32 = 1, GEMM_SWIGLU_BF16 = 2, GEMM_STORE_F32 = 3 };
+enum GemmEpi { GEMM_STORE_BF16 = 0, GEMM_RESID_F32 = 1, GEMM_SWIGLU_BF16 = 2, GEMM_STORE_F32 = 3, GEMM_QKV_ROPE = 4 };
 struct GemmParams {
-    const __nv_bfloat16* A;  // [M,K]
-    const __nv_bfloat16* W;  // [N,K]
+    const void* A;           // [M,K] bf16, or fp16 when ab_f16
+    const void* W;           // [N,K] same element type as A
     int M, N, K;
-    void* out;               // STORE_BF16: bf16 [M,N]; RESID_F32: fp32 [M,N] +=; SWIGLU: bf16 [M,N/2]; STORE_F32
+    void* out;               // STORE_BF16: bf16 [M,N]; RESID_F32: fp32 [M,N] +=; SWIGLU: 16-bit [M,N/2]; STORE_F32
     int epi;
+    int ab_f16 = 0;          // operand element type of A and W: 0 bf16, 1 fp16
+    int out_f16 = 0;         // SWIGLU output element type
+    // QKV_ROPE epilogue
+    __nv_bfloat16* q_hi = nullptr;  // [M, n_heads*128] bf16(q)
+    __nv_bfloat16* q_lo = nullptr;  // [M, n_heads*128] bf16(q - q_hi)
+    __nv_bfloat16* k_pool = nullptr;
+    __nv_bfloat16* v_pool = nullptr;
+    const int64_t* kv_off = nullptr;
+    const float* cos = nullptr;
+    const float* sin = nullptr;
+    int n_heads = 0, n_kv = 0;
+    int64_t head_stride = 0;
 };
 // returns cudaError-like int (0 ok); message via get_gemm_error()
 int launch_gemm(const GemmParams& p, cudaStream_t st);

@@ -21,12 +21,19 @@ namespace b200 {
 //   smem float index = ((step*2+half)*32 + lane)*4 + e
 constexpr int kGemvThreads = 512;
 
+// two packed 16-bit weights -> floats (the shard path holds weights as fp16; the bf16 form serves the unit entry point)
+template <bool WBF16>
+__device__ __forceinline__ float2 unpack2(uint32_t v) {
+    if (WBF16) return make_float2(bf_lo(v), bf_hi(v));
+    return __half22float2(*reinterpret_cast<const __half2*>(&v));
+}
+
 __device__ __forceinline__ int xs_index(int k) {
     const int c = k >> 3, step = c >> 5, lane = c & 31, half = (k >> 2) & 1, e = k & 3;
     return (((step * 2 + half) * 32 + lane) << 2) + e;
 }
 
-template <int M, int R, int EPI, bool NORM>
+template <int M, int R, int EPI, bool NORM, bool WBF16>
 __global__ void __launch_bounds__(kGemvThreads, (M == 1 ? 2 : 1)) gemv_kernel(const GemvParams p) {
     extern __shared__ __align__(16) float xs[];  // [M][Kpad]
     __shared__ float red[33];
@@ -80,7 +87,7 @@ __global__ void __launch_bounds__(kGemvThreads, (M == 1 ? 2 : 1)) gemv_kernel(co
         }
         const uint4* wrow[R];
 #pragma unroll
-        for (int r = 0; r < R; ++r) wrow[r] = reinterpret_cast<const uint4*>(p.W + (size_t)rows[r] * K);
+        for (int r = 0; r < R; ++r) wrow[r] = reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(p.W) + (size_t)rows[r] * K);
 
         float acc[R][M];
 #pragma unroll
@@ -109,15 +116,17 @@ __global__ void __launch_bounds__(kGemvThreads, (M == 1 ? 2 : 1)) gemv_kernel(co
 #pragma unroll
                         for (int r = 0; r < R; ++r) {
                             const uint4 ww = w[u][r];
+                            const float2 w0 = unpack2<WBF16>(ww.x), w1 = unpack2<WBF16>(ww.y), w2 = unpack2<WBF16>(ww.z),
+                                         w3 = unpack2<WBF16>(ww.w);
                             float a = acc[r][m];
-                            a = fmaf(bf_lo(ww.x), xl.x, a);
-                            a = fmaf(bf_hi(ww.x), xl.y, a);
-                            a = fmaf(bf_lo(ww.y), xl.z, a);
-                            a = fmaf(bf_hi(ww.y), xl.w, a);
-                            a = fmaf(bf_lo(ww.z), xh.x, a);
-                            a = fmaf(bf_hi(ww.z), xh.y, a);
-                            a = fmaf(bf_lo(ww.w), xh.z, a);
-                            a = fmaf(bf_hi(ww.w), xh.w, a);
+                            a = fmaf(w0.x, xl.x, a);
+                            a = fmaf(w0.y, xl.y, a);
+                            a = fmaf(w1.x, xl.z, a);
+                            a = fmaf(w1.y, xl.w, a);
+                            a = fmaf(w2.x, xh.x, a);
+                            a = fmaf(w2.y, xh.y, a);
+                            a = fmaf(w3.x, xh.z, a);
+                            a = fmaf(w3.y, xh.w, a);
                             acc[r][m] = a;
                         }
                     }
@@ -180,16 +189,20 @@ __global__ void __launch_bounds__(kGemvThreads, (M == 1 ? 2 : 1)) gemv_kernel(co
 
 template <int M, int R>
 static void gemv_dispatch(const GemvParams& p, int epi, bool norm, int grid, size_t smem, cudaStream_t st) {
-#define B200_GEMV_CASE(E, NRM)                                                                             \
+#define B200_GEMV_CASE(E, NRM, WB)                                                                         \
     {                                                                                                      \
-        auto kfn = gemv_kernel<M, R, E, NRM>;                                                              \
+        auto kfn = gemv_kernel<M, R, E, NRM, WB>;                                                          \
         cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);                 \
         kfn<<<grid, kGemvThreads, smem, st>>>(p);                                                          \
     }
-    if (epi == EPI_STORE) { if (norm) B200_GEMV_CASE(EPI_STORE, true) else B200_GEMV_CASE(EPI_STORE, false) }
-    else if (epi == EPI_RESID) B200_GEMV_CASE(EPI_RESID, false)
-    else if (epi == EPI_QKV) B200_GEMV_CASE(EPI_QKV, true)
-    else B200_GEMV_CASE(EPI_SWIGLU, true)
+    if (epi == EPI_STORE) {
+        if (p.w_bf16) B200_GEMV_CASE(EPI_STORE, false, true)
+        else if (norm) B200_GEMV_CASE(EPI_STORE, true, false)
+        else B200_GEMV_CASE(EPI_STORE, false, false)
+    }
+    else if (epi == EPI_RESID) B200_GEMV_CASE(EPI_RESID, false, false)
+    else if (epi == EPI_QKV) B200_GEMV_CASE(EPI_QKV, true, false)
+    else B200_GEMV_CASE(EPI_SWIGLU, true, false)
 #undef B200_GEMV_CASE
 }
 
@@ -315,6 +328,13 @@ void launch_load_residual(const __nv_bfloat16* in, float* x, int64_t n, cudaStre
 
 // One CTA per row; fp32 in, bf16 out; 128-bit loads/stores.  n % 8 == 0.
 // LlamaRMSNorm.forward (modeling_llama.py:62-67): mean of squares in fp32, rsqrt(var+eps), * weight.
+__device__ __forceinline__ uint32_t pack_f16_sat(float a, float b) {
+    a = fminf(fmaxf(a, -65504.f), 65504.f);
+    b = fminf(fmaxf(b, -65504.f), 65504.f);
+    __half2 t = __floats2half2_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&t);
+}
+template <bool F16OUT>
 __global__ void __launch_bounds__(256) rmsnorm_bf16_kernel(const float* __restrict__ x,
                                                            const __nv_bfloat16* __restrict__ w, float eps, int n,
                                                            __nv_bfloat16* __restrict__ out) {
@@ -343,16 +363,21 @@ __global__ void __launch_bounds__(256) rmsnorm_bf16_kernel(const float* __restri
             for (int e = 0; e < 8; ++e) v[e] = v[e] * rstd * wf[e];
         }
         uint4 o;
-        o.x = pack_bf16(v[0], v[1]);
-        o.y = pack_bf16(v[2], v[3]);
-        o.z = pack_bf16(v[4], v[5]);
-        o.w = pack_bf16(v[6], v[7]);
+        if (F16OUT) {
+            o.x = pack_f16_sat(v[0], v[1]); o.y = pack_f16_sat(v[2], v[3]);
+            o.z = pack_f16_sat(v[4], v[5]); o.w = pack_f16_sat(v[6], v[7]);
+        } else {
+            o.x = pack_bf16(v[0], v[1]); o.y = pack_bf16(v[2], v[3]);
+            o.z = pack_bf16(v[4], v[5]); o.w = pack_bf16(v[6], v[7]);
+        }
         reinterpret_cast<uint4*>(orow)[i] = o;
     }
 }
 void launch_rmsnorm_bf16(const float* x, const __nv_bfloat16* norm_w, float eps, int rows, int n,
-                         __nv_bfloat16* out, cudaStream_t st) {
-    if (rows > 0) rmsnorm_bf16_kernel<<<rows, 256, 0, st>>>(x, norm_w, eps, n, out);
+                         void* out, cudaStream_t st, bool f16_out) {
+    if (rows <= 0) return;
+    if (f16_out) rmsnorm_bf16_kernel<true><<<rows, 256, 0, st>>>(x, norm_w, eps, n, reinterpret_cast<__nv_bfloat16*>(out));
+    else rmsnorm_bf16_kernel<false><<<rows, 256, 0, st>>>(x, norm_w, eps, n, reinterpret_cast<__nv_bfloat16*>(out));
 }
 
 __global__ void __launch_bounds__(256) lastrow_norm_f32_kernel(const float* __restrict__ x,
@@ -453,26 +478,30 @@ __device__ __forceinline__ float load_as_float(const void* src, int dtype, int64
     if (dtype == 1) return reinterpret_cast<const float*>(src)[i];
     return __half2float(reinterpret_cast<const __half*>(src)[i]);
 }
-__global__ void convert_kernel(const void* src, int dtype, __nv_bfloat16* dst, int64_t n) {
+__device__ __forceinline__ __half to_half_sat(float v) { return __float2half_rn(fminf(fmaxf(v, -65504.f), 65504.f)); }
+__global__ void convert_kernel(const void* src, int dtype, void* dst, int64_t n, bool f16_out) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-    for (; i < n; i += stride) dst[i] = __float2bfloat16_rn(load_as_float(src, dtype, i));
+    for (; i < n; i += stride) {
+        const float v = load_as_float(src, dtype, i);
+        if (f16_out) reinterpret_cast<__half*>(dst)[i] = to_half_sat(v);
+        else reinterpret_cast<__nv_bfloat16*>(dst)[i] = __float2bfloat16_rn(v);
+    }
 }
-void launch_convert_to_bf16(const void* src, int dtype, __nv_bfloat16* dst, int64_t n, cudaStream_t st) {
+void launch_convert_to_bf16(const void* src, int dtype, void* dst, int64_t n, cudaStream_t st, bool f16_out) {
     int64_t g = (n + 255) / 256;
     if (g > 148 * 16) g = 148 * 16;
     if (g < 1) g = 1;
-    convert_kernel<<<(int)g, 256, 0, st>>>(src, dtype, dst, n);
+    convert_kernel<<<(int)g, 256, 0, st>>>(src, dtype, dst, n, f16_out);
 }
-__global__ void pack_gate_up_kernel(const void* src, int dtype, __nv_bfloat16* dst, int rows, int cols, int half) {
+__global__ void pack_gate_up_kernel(const void* src, int dtype, __half* dst, int rows, int cols, int half) {
     const int r = blockIdx.x;
     const int64_t drow = (int64_t)(r / 64) * 128 + half * 64 + (r % 64);
     for (int c = threadIdx.x; c < cols; c += blockDim.x)
-        dst[drow * cols + c] = __float2bfloat16_rn(load_as_float(src, dtype, (int64_t)r * cols + c));
+        dst[drow * cols + c] = to_half_sat(load_as_float(src, dtype, (int64_t)r * cols + c));
 }
-void launch_pack_gate_up(const void* src, int dtype, __nv_bfloat16* dst, int rows, int cols, int half,
-                         cudaStream_t st) {
-    pack_gate_up_kernel<<<rows, 256, 0, st>>>(src, dtype, dst, rows, cols, half);
+void launch_pack_gate_up(const void* src, int dtype, void* dst, int rows, int cols, int half, cudaStream_t st) {
+    pack_gate_up_kernel<<<rows, 256, 0, st>>>(src, dtype, reinterpret_cast<__half*>(dst), rows, cols, half);
 }
 
 // =========================================================================== decode attention (split-K)

@@ -122,3 +122,17 @@ def test_attn_decode_split_k(lib, rows, n_heads, n_kv, T_list, n_splits):
                                     n_heads, n_kv, 64, max_pages, n_splits, scratch.data_ptr(), out.data_ptr(), _st()))
     ref = attn_decode_reference(q, dense, n_heads, n_kv)
     assert rel_l2(out, ref) < 1e-5  # fp32 softmax and accumulation over bf16 K/V; only summation order differs
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 128, 64), (200, 384, 512), (512, 4096, 4096), (77, 4096, 11008)])
+def test_gemm_tcgen05_fp16_operands(lib, M, N, K):
+    from llm_sharding_b200 import _lib
+    g = torch.Generator(device="cuda").manual_seed(M * 3 + N + K)
+    a = torch.randn(M, K, device="cuda", generator=g).half()
+    w = (torch.randn(N, K, device="cuda", generator=g) * 0.05).bfloat16().half()  # bf16 model weights held as fp16
+    out = torch.full((M, N), float("nan"), device="cuda")
+    _lib.check(lib.b200_gemm_f16(a.data_ptr(), w.data_ptr(), M, N, K, out.data_ptr(), _st()))
+    torch.cuda.synchronize()
+    ref = (a.double() @ w.double().t()).float()
+    assert not torch.isnan(out).any()
+    assert rel_l2(out, ref) < 3e-5  # exact fp16 x fp16 products, fp32 accumulation
