@@ -345,6 +345,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=8)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--transport", default="p2p", choices=["p2p", "nccl"], help="hop transport for --gpus > 1")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)

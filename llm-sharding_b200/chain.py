@@ -125,3 +125,203 @@ def generate(workers, input_ids: torch.Tensor, max_new_tokens: int, record_state
             break
         msg = {"hidden_states": head.embed_tokens(fed.reshape(-1, 1)), "batch_size": head.batch_size, "seq_len": 1}
     return torch.stack(tokens), states
+
+
+# ----------------------------------------------------------------------------------------------
+# Multi-GPU ring: one process per GPU, one shard per process (the reference's NodeController-per-node
+# model, utils/node_worker.py:385-559 + run_this.sh), messages handed over inside the NVSwitch box.
+# ----------------------------------------------------------------------------------------------
+def layer_range(rank: int, world: int, n_layers: int) -> tuple[int, int]:
+    """Contiguous, as even as possible split [start, end) of the layers over `world` stages (the kind of
+    split ConfigSender.build_config(shards_start, shards_end) describes, utils/config_sender.py:38-39)."""
+    if world < 1 or world > n_layers:
+        raise ValueError("[ERROR] start or end is invalid")
+    base, extra = divmod(n_layers, world)
+    start = rank * base + min(rank, extra)
+    return start, start + base + (1 if rank < extra else 0)
+
+
+class RingSchedule:
+    """Sequence numbers and mailbox slots of one stage of the ring.
+
+    Every stage consumes the messages of its predecessor in the order they were produced, so both sides
+    can count: message number `seq` of a hop lives in mailbox slot `seq % n_slots`.  With `n_streams`
+    request streams served round-robin and n_slots == n_streams, stream i always lands in slot i — which
+    keeps the captured decode graphs (keyed by their pointers) to one per stream."""
+
+    def __init__(self, rank: int, world: int, n_streams: int):
+        if n_streams < 1:
+            raise ValueError("[ERROR] at least one request stream is required")
+        self.rank, self.world, self.n_streams = rank, world, n_streams
+        self.is_head, self.is_tail = rank == 0, rank == world - 1
+        self.seq_in = 0    # next message expected from the predecessor
+        self.seq_out = 0   # next message sent to the successor
+        self.prefilled = [False] * n_streams
+
+    def _slot(self, seq: int) -> int:
+        return seq % self.n_streams
+
+    def prefill(self, stream: int) -> dict:
+        """Work item for the prompt of `stream`.  The head consumes nothing (the prompt comes from its own host)."""
+        if self.prefilled[stream]:
+            raise RuntimeError(f"[ERROR] stream {stream} already holds a request; clear it first")
+        self.prefilled[stream] = True
+        item = {"kind": "prefill", "stream": stream, "kv_slot": stream, "wait": None, "send": None}
+        if not self.is_head:
+            item["wait"] = (self.seq_in, self._slot(self.seq_in))
+            self.seq_in += 1
+        item["send"] = (self.seq_out, self._slot(self.seq_out))
+        self.seq_out += 1
+        return item
+
+    def decode(self, stream: int) -> dict:
+        """Work item for one more token of `stream`: every stage (the head too: it waits for the token id the
+        tail sent back, utils/node_worker.py:515-520) consumes one message and produces one."""
+        if not self.prefilled[stream]:
+            raise RuntimeError(f"[ERROR] stream {stream} has no request to continue")
+        item = {"kind": "decode", "stream": stream, "kv_slot": stream,
+                "wait": (self.seq_in, self._slot(self.seq_in)), "send": (self.seq_out, self._slot(self.seq_out))}
+        self.seq_in += 1
+        self.seq_out += 1
+        return item
+
+    def clear(self) -> None:
+        self.prefilled = [False] * self.n_streams
+
+
+class _DevPtr:
+    def __init__(self, ptr: int, nbytes: int):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
+
+
+def tensor_view(ptr: int, nbytes: int, device) -> torch.Tensor:
+    """uint8 view of LOCAL device memory owned by the library (mailbox slots)."""
+    return torch.as_tensor(_DevPtr(ptr, nbytes), device=device)
+
+
+class ChainStage:
+    """One stage of the layer-sharded ring on its own GPU.  `worker` is this repo's NodeWorker (already
+    `load_shards`-ed with max_slots >= n_streams).  Transport "p2p": hidden states / token ids are written by the
+    producing kernel straight into the next GPU's mailbox over NVLink and published with a flag; "nccl":
+    ncclSend / ncclRecv through torch.distributed (the A/B alternative)."""
+
+    def __init__(self, worker, rank: int, world: int, n_streams: int, max_prompt: int, ctrl_group=None,
+                 transport: str = "p2p", max_wait_us: int = 20_000_000):
+        import torch.distributed as dist
+
+        self.w, self.rank, self.world, self.n_streams = worker, rank, world, n_streams
+        self.sched = RingSchedule(rank, world, n_streams)
+        self.eng, self.kv = worker.shard.engine, worker.past_key_value
+        self.lib = self.eng.lib
+        self.device = worker.device
+        self.H = self.eng.hidden_size
+        self.causal = int(worker.causal)
+        self.transport = transport
+        self.max_wait_us = max_wait_us
+        self.dist = dist
+        self.nxt, self.prv = (rank + 1) % world, (rank - 1) % world
+        self.slot_bytes = max(max_prompt * self.H * 2, 4096)
+        if transport == "p2p":
+            self.hop = P2PHop(self.device, n_streams, self.slot_bytes)
+            mine = (self.hop.export(), self.hop.dev_index)
+            gathered = [None] * world
+            dist.all_gather_object(gathered, mine, group=ctrl_group)
+            self.hop.connect(gathered[self.nxt][0], gathered[self.nxt][1], same_process=False)
+            dist.barrier(group=ctrl_group)
+        else:
+            self.hop = None
+            self.inbuf = [torch.empty(self.slot_bytes, dtype=torch.uint8, device=self.device) for _ in range(n_streams)]
+            self.outbuf = [torch.empty(self.slot_bytes, dtype=torch.uint8, device=self.device) for _ in range(n_streams)]
+        self.tokens = []       # head: device int64[1] tensors, one per recorded decode
+        self.host_tokens = []  # head, via_host mode: python ints
+
+    # -- raw-pointer plumbing
+    def _st(self):
+        return _lib.stream_ptr(self.device)
+
+    def _in_ptr(self, item) -> int:
+        if self.hop is not None:
+            return self.lib.b200_hop_local_slot(self.hop.handle, item["wait"][0])
+        return self.inbuf[item["wait"][1]].data_ptr()
+
+    def _out_ptr(self, item) -> int:
+        if self.hop is not None:
+            return self.lib.b200_hop_peer_slot(self.hop.handle, item["send"][0])
+        return self.outbuf[item["send"][1]].data_ptr()
+
+    def _wait(self, item, nbytes: int) -> None:
+        if item["wait"] is None:
+            return
+        if self.hop is not None:
+            _lib.check(self.lib.b200_hop_recv(self.hop.handle, None, 0, item["wait"][0], self.max_wait_us, self._st()))
+        else:
+            self.dist.recv(self.inbuf[item["wait"][1]][:nbytes], src=self.prv)
+
+    def _publish(self, item, nbytes: int) -> None:
+        if self.hop is not None:
+            _lib.check(self.lib.b200_hop_send(self.hop.handle, None, 0, item["send"][0], self._st()))
+        else:
+            self.dist.send(self.outbuf[item["send"][1]][:nbytes], dst=self.nxt)
+
+    def _run(self, item, S: int, tok_in_ptr: int | None, record: bool, via_host: bool = False) -> None:
+        import ctypes as C
+        slots = (C.c_int32 * 1)(item["kv_slot"])
+        sch = self.sched
+        hid_bytes, tok_bytes = S * self.H * 2, 8
+        in_bytes = tok_bytes if (sch.is_head and item["kind"] == "decode") else hid_bytes
+        out_bytes = tok_bytes if sch.is_tail else hid_bytes
+        self._wait(item, in_bytes)
+        out_ptr = self._out_ptr(item)
+        if sch.is_head:
+            if tok_in_ptr is None:
+                tok_in_ptr = self._in_ptr(item)
+                if via_host:
+                    # end-to-end mode: the id leaves the GPU (D2H, the host blocks until the ring delivered it), is seen
+                    # by the host loop (the reference decodes / prints it there) and comes back from pinned memory (H2D)
+                    src = (tensor_view(tok_in_ptr, 8, self.device) if self.hop is not None else self.inbuf[item["wait"][1]][:8])
+                    if not hasattr(self, "_host_tok"):
+                        self._host_tok = torch.empty(1, dtype=torch.int64).pin_memory()
+                        self._dev_tok = [torch.empty(1, dtype=torch.int64, device=self.device) for _ in range(self.n_streams)]
+                    self._host_tok.copy_(src.view(torch.int64))  # synchronous D2H
+                    self.host_tokens.append(int(self._host_tok[0]))
+                    self._dev_tok[item["stream"]].copy_(self._host_tok, non_blocking=True)
+                    tok_in_ptr = self._dev_tok[item["stream"]].data_ptr()
+                elif record:
+                    self.tokens.append(tensor_view(tok_in_ptr, 8, self.device).view(torch.int64).clone()
+                                       if self.hop is not None else self.inbuf[item["wait"][1]][:8].view(torch.int64).clone())
+            if sch.is_tail:  # single-stage ring: token in, token out
+                _lib.check(self.lib.b200_shard_step_tokens(self.eng.handle, self.kv.handle, slots, tok_in_ptr, 1, S, self.causal,
+                                                           None, out_ptr, None, self._st()))
+            else:
+                _lib.check(self.lib.b200_shard_step_tokens(self.eng.handle, self.kv.handle, slots, tok_in_ptr, 1, S, self.causal,
+                                                           out_ptr, None, None, self._st()))
+        elif sch.is_tail:
+            _lib.check(self.lib.b200_shard_forward_argmax(self.eng.handle, self.kv.handle, slots, self._in_ptr(item), 1, S,
+                                                          self.causal, None, out_ptr, None, self._st()))
+        else:
+            _lib.check(self.lib.b200_shard_forward(self.eng.handle, self.kv.handle, slots, self._in_ptr(item), 1, S,
+                                                   self.causal, out_ptr, self._st()))
+        self._publish(item, out_bytes)
+
+    # -- public
+    def prefill(self, stream: int, prompt_len: int, ids: torch.Tensor | None = None) -> None:
+        """ids: int64 [prompt_len] on this GPU (head only)."""
+        item = self.sched.prefill(stream)
+        if self.sched.is_head and ids is None:
+            raise ValueError("[ERROR] the head stage needs the prompt ids")
+        self._run(item, prompt_len, ids.data_ptr() if self.sched.is_head else None, False)
+        if self.sched.is_head:
+            self._keep = getattr(self, "_keep", []) + [ids]  # keep the prompt alive until the kernels ran
+
+    def decode(self, stream: int, record: bool = False, via_host: bool = False) -> None:
+        """One more token for `stream`.  `via_host` (head only): the token id that came back through the ring makes a
+        round trip through pinned host memory before it is embedded (end-to-end mode)."""
+        item = self.sched.decode(stream)
+        self._run(item, 1, None, record, via_host and self.sched.is_head)
+
+    def error(self) -> int:
+        return self.hop.error() if self.hop is not None else 0
+
+    def close(self) -> None:
+        if self.hop is not None:
+            self.hop.close()

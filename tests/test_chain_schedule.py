@@ -1,0 +1,116 @@
+"""CPU-only: the host-side protocol of the multi-GPU ring (layer split, sequence numbers, mailbox slots), single
+process and across two real processes on the gloo backend (world_size 2)."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from llm_sharding_b200.chain import RingSchedule, layer_range
+
+
+def test_layer_range_covers_all_layers_contiguously():
+    for n_layers, world in [(32, 1), (32, 2), (32, 4), (32, 8), (32, 3), (28, 5), (4, 4)]:
+        spans = [layer_range(r, world, n_layers) for r in range(world)]
+        assert spans[0][0] == 0 and spans[-1][1] == n_layers
+        for (a0, a1), (b0, b1) in zip(spans, spans[1:]):
+            assert a1 == b0 and a1 > a0
+        sizes = [e - s for s, e in spans]
+        assert max(sizes) - min(sizes) <= 1
+    with pytest.raises(ValueError):
+        layer_range(0, 5, 4)
+
+
+def test_ring_schedule_slots_are_stable_per_stream():
+    world, n_streams = 4, 4
+    scheds = [RingSchedule(r, world, n_streams) for r in range(world)]
+    sent = {r: [] for r in range(world)}   # messages produced by stage r, in order
+    for i in range(n_streams):
+        for r in range(world):
+            it = scheds[r].prefill(i)
+            assert (it["wait"] is None) == (r == 0)
+            sent[r].append((it["send"], i))
+    for _ in range(3):
+        for i in range(n_streams):
+            for r in range(world):
+                it = scheds[r].decode(i)
+                assert it["wait"][1] == i and it["send"][1] == i  # stream i always uses mailbox slot i
+                sent[r].append((it["send"], i))
+    # what stage r consumes as its k-th message is what stage r-1 produced as its k-th message
+    for r in range(world):
+        seqs = [s for (s, _), _ in sent[r]]
+        assert seqs == list(range(len(seqs)))
+    with pytest.raises(RuntimeError):
+        scheds[0].prefill(0)
+    with pytest.raises(RuntimeError):
+        RingSchedule(0, 2, 2).decode(1)
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _ring_worker(rank, world, port, n_streams, rounds, out_q):
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        sched = RingSchedule(rank, world, n_streams)
+        nxt, prv = (rank + 1) % world, (rank - 1) % world
+        log, pending = [], []
+        # every "message" carries (seq, slot, stream, hops so far); the consumer checks it is the one it expects.
+        # Sends are non-blocking, like a mailbox store: the head does not consume a prefill's token until it decodes.
+        def handle(item):
+            if item["wait"] is not None:
+                m = torch.zeros(4, dtype=torch.int64)
+                dist.recv(m, src=prv)
+                assert (int(m[0]), int(m[1])) == item["wait"], (rank, m.tolist(), item)
+                assert int(m[2]) == item["stream"]
+                hops = int(m[3]) + 1
+            else:
+                hops = 0
+            msg = torch.tensor([item["send"][0], item["send"][1], item["stream"], hops])
+            pending.append((dist.isend(msg, dst=nxt), msg))
+            log.append(hops)
+        for i in range(n_streams):
+            handle(sched.prefill(i))
+        for _ in range(rounds):
+            for i in range(n_streams):
+                handle(sched.decode(i))
+        # drain: the head still has the last round's tokens in its mailbox
+        if rank == 0:
+            for _ in range(n_streams):
+                m = torch.zeros(4, dtype=torch.int64)
+                dist.recv(m, src=prv)
+        for req, _ in pending:
+            req.wait()
+        gathered = [None] * world
+        dist.all_gather_object(gathered, (rank, layer_range(rank, world, 32), log[-1]))
+        if rank == 0:
+            out_q.put(gathered)
+    finally:
+        dist.destroy_process_group()
+
+
+def test_ring_protocol_two_processes_gloo():
+    world, n_streams, rounds = 2, 2, 5
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_ring_worker, args=(r, world, port, n_streams, rounds, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(90)
+    hung = [p for p in procs if p.is_alive()]
+    for p in hung:
+        p.terminate()
+    assert not hung, "ring protocol deadlocked"
+    assert all(p.exitcode == 0 for p in procs)
+    gathered = q.get(timeout=10)
+    assert [g[1] for g in gathered] == [(0, 16), (16, 32)]
+    # the last message a stage handled has travelled (rounds * world + rank) hops around the ring
+    assert [g[2] for g in gathered] == [rounds * world + r for r in range(world)]

@@ -1,0 +1,118 @@
+"""-m gpu: the hop kernels and the multi-GPU ring.  Single-GPU part: mailbox send/recv on one stream (the flag
+is already published when the receiver runs, so nothing ever spins).  Two-GPU part (skipped on a 1-GPU box): two
+processes, one shard each, tokens compared with the same chain run inside one process."""
+import os
+import socket
+import sys
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def test_hop_mailbox_roundtrip_same_gpu():
+    from llm_sharding_b200.chain import P2PHop
+    hop = P2PHop(torch.device("cuda:0"), 3, 1 << 20)
+    hop.connect(hop.export(), 0, same_process=True)   # a ring of one: my successor is me
+    g = torch.Generator(device="cuda").manual_seed(5)
+    for seq in range(7):  # wraps around the 3 ring slots
+        n = [8192, 16, 1 << 20, 272 * 1024, 8, 4096, 100000][seq]
+        payload = torch.randint(0, 255, (n,), device="cuda", dtype=torch.uint8, generator=g)
+        out = torch.zeros_like(payload)
+        hop.send(payload, seq)
+        hop.recv(out, seq, max_wait_us=1_000_000)
+        torch.cuda.synchronize()
+        assert torch.equal(out, payload), seq
+    assert hop.error() == 0
+    with pytest.raises(ValueError):
+        hop.send(torch.zeros((1 << 20) + 512, dtype=torch.uint8, device="cuda"), 8)
+    hop.close()
+
+
+def test_hop_recv_times_out_instead_of_hanging():
+    from llm_sharding_b200.chain import P2PHop
+    hop = P2PHop(torch.device("cuda:0"), 2, 4096)
+    hop.connect(hop.export(), 0, same_process=True)
+    out = torch.zeros(64, dtype=torch.uint8, device="cuda")
+    hop.recv(out, 0, max_wait_us=20_000)   # nothing was sent: the bounded spin gives up after ~20 ms
+    torch.cuda.synchronize()
+    assert hop.error() == 1
+    hop.close()
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _stage_proc(rank, world, port, shard_dir, n_streams, prompt_len, rounds, q):
+    import torch.distributed as dist
+    from llm_sharding_b200.chain import ChainStage, LoopbackCommunicator, layer_range
+    from llm_sharding_b200.node_worker import NodeWorker
+    from oracle import synth
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        cfg = synth.PRESETS["tiny"]
+        s, e = layer_range(rank, world, cfg.num_hidden_layers)
+        src, dst = f"tcp://*:{47300 + rank}", f"tcp://127.0.0.1:{47300 + (rank + 1) % world}"
+        w = NodeWorker(src, dst, rank == 0, shard_dir, device=f"cuda:{rank}", dtype=torch.bfloat16,
+                       communicator=LoopbackCommunicator(src, dst), max_tokens=prompt_len, max_batch=1, max_slots=n_streams)
+        w.load_shards(s, e)
+        stage = ChainStage(w, rank, world, n_streams, prompt_len, ctrl_group=None, transport="p2p", max_wait_us=10_000_000)
+        prompts = [synth.prompt_ids(cfg, 900 + i, 1, prompt_len)[0].to(f"cuda:{rank}") for i in range(n_streams)]
+        for i in range(n_streams):
+            stage.prefill(i, prompt_len, prompts[i] if rank == 0 else None)
+        for _ in range(rounds):
+            for i in range(n_streams):
+                stage.decode(i, record=True)
+        torch.cuda.synchronize()
+        dist.barrier()
+        if rank == 0:
+            q.put(([int(t[0]) for t in stage.tokens], stage.error()))
+        dist.barrier()
+        stage.close()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_two_gpu_ring_matches_single_process_chain(tmp_path):
+    import torch.multiprocessing as mp
+    from gpu_utils import build_chain, close_chain, shard_dir
+    from llm_sharding_b200.chain import generate
+    from oracle import synth
+    cfg = synth.PRESETS["tiny"]
+    n_streams, prompt_len, rounds = 2, 20, 4
+    d = shard_dir(str(tmp_path), "tiny", 28)
+    # expectation: the same two-shard chain inside one process, one request at a time
+    expected = []
+    workers = build_chain(str(tmp_path), "tiny", 28, [(0, 2), (2, 4)], max_tokens=prompt_len)
+    try:
+        for i in range(n_streams):
+            for w in workers:
+                w.clear_KV_cache()
+            toks, _ = generate(workers, synth.prompt_ids(cfg, 900 + i, 1, prompt_len), rounds)
+            expected.append([int(t) for t in toks[:, 0]])
+    finally:
+        close_chain(workers)
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_stage_proc, args=(r, 2, port, d, n_streams, prompt_len, rounds, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(180)
+    hung = [p for p in procs if p.is_alive()]
+    for p in hung:
+        p.terminate()
+    assert not hung and all(p.exitcode == 0 for p in procs)
+    got, err = q.get(timeout=10)
+    assert err == 0
+    # the head records, per decode, the token that came back: round r, stream i -> token r of stream i
+    by_stream = [[got[r * n_streams + i] for r in range(rounds)] for i in range(n_streams)]
+    assert by_stream == expected
