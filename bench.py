@@ -304,6 +304,21 @@ def run_single(args):
     e1.record()
     torch.cuda.synchronize()
     k_ms = e0.elapsed_time(e1) / (reps * L)
+    # per-kernel breakdown of a decode step: each product kernel timed the same way (warm, back to back over the layers)
+    kernel_us = {}
+    for name, kind in (("qkv_rope_append", 0), ("attention", 1), ("o_proj", 2), ("gate_up_swiglu", 3), ("down_proj", 4), ("lm_head", 5)):
+        n_l = 1 if kind == 5 else L
+        for l in range(n_l):
+            eng.run_kernel(kv, kind, l, 1)
+        torch.cuda.synchronize()
+        a0, a1 = ev(), ev()
+        a0.record()
+        for _ in range(reps * (8 if kind == 5 else 1)):
+            for l in range(n_l):
+                eng.run_kernel(kv, kind, l, 1)
+        a1.record()
+        torch.cuda.synchronize()
+        kernel_us[name] = 1000 * a0.elapsed_time(a1) / (reps * (8 if kind == 5 else 1) * n_l)
     k_bytes = 2 * I * H * 2 + H * 2 + H * 4 + I * 4
     pk = peaks()
     traffic = None
@@ -333,7 +348,7 @@ def run_single(args):
         "clocks": clk.summary(), "e2e": e2e, "gpu_launches": cnt["launches"],
         "roofline": roofline, "step_roofline": step_roofline, "cpu_baseline": cpu,
         "prefill_tok_s": prefill_tok_s, "p50_token_ms": 1000 * per_step[len(per_step) // 2],
-        "p50_token_ms_device": ms_per_step,
+        "p50_token_ms_device": ms_per_step, "kernel_us": kernel_us,
     }
     print(json.dumps(line), flush=True)
 

@@ -154,7 +154,8 @@ B200_API int b200_shard_set_graphs(b200_shard_t* s, int enabled);
 /* ---- single-kernel entry points (unit parity tests and micro-benchmarks) -------------- */
 /* Launch ONE of the decode-path kernels of layer `layer` exactly as b200_shard_forward would (same template
  * instantiation, same buffers; inputs are whatever the workspace holds): kind 0 = RMSNorm+QKV+RoPE+KV-append,
- * 2 = o_proj+residual, 3 = RMSNorm+gate/up+SwiGLU, 4 = down_proj+residual.  `rows` = token rows (1..4).
+ * 1 = decode attention over the slots' current context, 2 = o_proj+residual, 3 = RMSNorm+gate/up+SwiGLU,
+ * 4 = down_proj+residual, 5 = final RMSNorm + lm_head (layer ignored).  `rows` = token rows (1..4).
  * Used by bench.py to time the dominant kernel on its own stream for the roofline figure. */
 B200_API int b200_shard_run_kernel(b200_shard_t* s, b200_kv_t* kv, int kind, int layer, int rows, void* stream);
 /* LlamaRMSNorm.forward (transformers modeling_llama.py:62-67): fp32 in -> bf16 out, [rows, n] */
@@ -163,7 +164,8 @@ B200_API int b200_rmsnorm(const float* d_x, const void* d_weight_bf16, float eps
 /* Split-K decode attention over a paged K/V pool (eager_attention_forward, transformers modeling_llama.py:199-221, for
  * single-token queries): row r attends to keys [0, d_t_end[r]) found through d_block_table[r][*] (page ids into the
  * pools, layout [page][kv_head][page_size][128] bf16).  d_q / d_out fp32 [rows, n_heads*128].  d_scratch: caller-owned
- * global memory for the per-split partials, rows*n_heads*n_splits*130 floats. */
+ * global memory for the per-split partials and
+ * arrival tickets, rows*n_heads*(n_splits*130 + 1) floats; its contents need no initialisation. */
 B200_API int b200_attn_decode(const float* d_q, const void* d_k_pool, const void* d_v_pool, const int32_t* d_block_table,
                               const int32_t* d_t_end, int rows, int n_heads, int n_kv_heads, int page_size,
                               int max_pages_per_row, int n_splits, float* d_scratch, float* d_out, void* stream);

@@ -136,7 +136,7 @@ extern "C" B200_API int b200_shard_create(const b200_shard_config_t* c, int devi
     r |= dev_alloc(A, &s->q_f, (size_t)kMaxGemvRows * s->nq);
     r |= dev_alloc(A, &s->attn_f, (size_t)kMaxGemvRows * s->nq);
     r |= dev_alloc(A, &s->act_f, (size_t)kMaxGemvRows * I);
-    r |= dev_alloc(A, &s->attn_part, (size_t)kMaxGemvRows * c->n_heads * kMaxSplits * 130);
+    r |= dev_alloc(A, &s->attn_part, attn_decode_scratch_floats(kMaxGemvRows, c->n_heads, kMaxSplits));
     r |= dev_alloc(A, &s->lastrow, (size_t)c->max_batch * H);
     r |= dev_alloc(A, &s->lastrow_b, (size_t)c->max_batch * H);
     r |= dev_alloc(A, &s->logits, (size_t)c->max_batch * V);
@@ -147,6 +147,8 @@ extern "C" B200_API int b200_shard_create(const b200_shard_config_t* c, int devi
     r |= dev_alloc(A, &s->tm.cos, MT * 64);
     r |= dev_alloc(A, &s->tm.sin, MT * 64);
     if (r != 0) { b200_shard_destroy(s); return B200_ENOMEM; }
+    // arrival tickets of decode attention start at zero (the kernel re-zeroes them itself afterwards)
+    CU_TRY(cudaMemset(s->attn_part, 0, attn_decode_scratch_floats(kMaxGemvRows, c->n_heads, kMaxSplits) * sizeof(float)));
     *out = s;
     return 0;
 }
@@ -298,10 +300,9 @@ extern "C" B200_API int b200_kv_seq_len(const b200_kv_t* kv, int slot) {
 
 // ------------------------------------------------------------------------------------- forward
 static int gemv_row_limit(const b200_shard* s) {
-    const size_t kmax = (size_t)(s->cfg.intermediate_size > s->cfg.hidden_size ? s->cfg.intermediate_size : s->cfg.hidden_size);
-    const size_t kpad = ((kmax / 8 + 31) / 32) * 256;
-    int lim = (int)((220 * 1024) / (kpad * 4));
-    if (lim > kMaxGemvRows) lim = kMaxGemvRows;
+    const int kmax = s->cfg.intermediate_size > s->cfg.hidden_size ? s->cfg.intermediate_size : s->cfg.hidden_size;
+    int lim = kMaxGemvRows;
+    while (lim > 0 && gemv_smem_bytes(lim, kmax) > 220 * 1024) --lim;
     return lim;
 }
 
@@ -358,7 +359,7 @@ static int enqueue_forward(b200_shard_t* s, b200_kv_t* kv, const SlotList& sl, c
             g.n_heads = c.n_heads; g.n_kv = c.n_kv_heads; g.head_stride = head_stride;
             launch_gemv(g, M, EPI_QKV, true, s->num_sms, st);
             AttnDecodeParams a{};
-            a.q = s->q_f; a.k_pool = kp; a.v_pool = vp; a.block_table = kv->dev.block_table; a.t_end = s->tm.t_end;
+            a.q = s->q_f; a.k_pool = kp; a.v_pool = vp; a.block_table = kv->dev.block_table; a.t_end = s->tm.t_end; a.call_base = s->tm.call_base;
             a.slots = sl; a.S = S; a.n_heads = c.n_heads; a.n_kv = c.n_kv_heads; a.page_size = kv->dev.page_size;
             a.max_pages_per_slot = kv->dev.max_pages_per_slot;
             int ns = (2 * s->num_sms + M * c.n_heads - 1) / (M * c.n_heads);
@@ -366,6 +367,7 @@ static int enqueue_forward(b200_shard_t* s, b200_kv_t* kv, const SlotList& sl, c
             if (ns < ns_cap) ns = ns_cap;
             a.n_splits = ns < 1 ? 1 : (ns > kMaxSplits ? kMaxSplits : ns);
             a.part = s->attn_part; a.out = s->attn_f;
+            a.tickets = reinterpret_cast<unsigned int*>(s->attn_part + (size_t)kMaxGemvRows * c.n_heads * kMaxSplits * 130);
             launch_attn_decode(a, M, st);
             GemvParams o{};
             o.W = L.wo; o.x = s->attn_f; o.N = H; o.K = s->nq; o.out = s->x;
@@ -376,7 +378,7 @@ static int enqueue_forward(b200_shard_t* s, b200_kv_t* kv, const SlotList& sl, c
             GemvParams d{};
             d.W = L.wdown; d.x = s->act_f; d.N = H; d.K = I; d.out = s->x;
             launch_gemv(d, M, EPI_RESID, false, s->num_sms, st);
-            s->n_launch += 6;
+            s->n_launch += 5;
         } else {
             // activations feeding the tensor cores are fp16 (10 mantissa bits) against exact bf16 weights; q reaches
             // attention as a (hi, lo) bf16 pair; K/V are rounded to bf16 exactly once, inside the QKV epilogue
@@ -410,7 +412,7 @@ static int enqueue_forward(b200_shard_t* s, b200_kv_t* kv, const SlotList& sl, c
                             reinterpret_cast<__nv_bfloat16*>(out), st);
         s->n_launch += 1;
     }
-    if (with_tail) {
+    if (with_tail && B > gemv_row_limit(s)) {  // batched tail goes through the GEMM; small batches fuse the norm into the GEMV
         launch_lastrow_norm_f32(s->x, c.has_final_norm ? s->final_norm : nullptr, c.rms_eps, B, S, H, s->lastrow, st);
         s->n_launch += 1;
     }
@@ -418,12 +420,20 @@ static int enqueue_forward(b200_shard_t* s, b200_kv_t* kv, const SlotList& sl, c
     return 0;
 }
 
-static int enqueue_tail(b200_shard_t* s, int B, int64_t* tok, float* margin, cudaStream_t st) {
+// from_residual: the last rows are still in the fp32 residual stream s->x ([B,S,H]); otherwise they are in s->lastrow
+static int enqueue_tail(b200_shard_t* s, int B, int S, bool from_residual, int64_t* tok, float* margin, cudaStream_t st) {
     const b200_shard_config_t& c = s->cfg;
     if (B <= gemv_row_limit(s)) {
         GemvParams g{};
-        g.W = s->lm_head; g.x = s->lastrow; g.N = c.vocab_size; g.K = c.hidden_size; g.out = s->logits;
-        launch_gemv(g, B, EPI_STORE, false, s->num_sms, st);
+        g.W = s->lm_head; g.N = c.vocab_size; g.K = c.hidden_size; g.out = s->logits;
+        if (from_residual) {  // final RMSNorm (utils/shard_loader.py:76-77) as the GEMV's prologue, row S-1 of every batch row
+            g.x = s->x + (size_t)(S - 1) * c.hidden_size; g.x_stride = (int64_t)S * c.hidden_size;
+            g.norm_w = c.has_final_norm ? s->final_norm : nullptr; g.eps = c.rms_eps;
+            launch_gemv(g, B, EPI_STORE, c.has_final_norm != 0, s->num_sms, st);
+        } else {
+            g.x = s->lastrow;
+            launch_gemv(g, B, EPI_STORE, false, s->num_sms, st);
+        }
     } else {
         launch_rmsnorm_bf16(s->lastrow, nullptr, 0.f, B, c.hidden_size, s->lastrow_b, st, true);
         GemmParams g{};
@@ -488,7 +498,7 @@ static int forward_impl(b200_shard_t* s, b200_kv_t* kv, const int32_t* h_slots, 
             const uint64_t launches_before = s->n_launch;
             CU_TRY(cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal));
             int r = enqueue_forward(s, kv, sl, in, tok_in, B, S, causal, out, tok, margin, with_tail, cs);
-            if (r == 0 && with_tail) r = enqueue_tail(s, B, tok, margin, cs);
+            if (r == 0 && with_tail) r = enqueue_tail(s, B, S, true, tok, margin, cs);
             cudaGraph_t graph = nullptr;
             cudaError_t ce = cudaStreamEndCapture(cs, &graph);
             s->n_launch = launches_before;
@@ -506,12 +516,12 @@ static int forward_impl(b200_shard_t* s, b200_kv_t* kv, const int32_t* h_slots, 
             it = s->graph_cache.emplace(key, exec).first;
         }
         CU_TRY(cudaGraphLaunch(it->second, st));
-        s->n_launch += 3 + (uint64_t)s->cfg.n_layers * (B <= gemv_row_limit(s) ? 6 : 7) + (out ? 1 : 0) + (with_tail ? 3 : 0) + (tok_in ? 1 : 0);
+        s->n_launch += 3 + (uint64_t)s->cfg.n_layers * (B <= gemv_row_limit(s) ? 5 : 7) + (out ? 1 : 0) + (with_tail ? (B <= gemv_row_limit(s) ? 2 : 4) : 0) + (tok_in ? 1 : 0);
         done = true;
     }
     if (!done) {
         TRY(enqueue_forward(s, kv, sl, in, tok_in, B, S, causal, out, tok, margin, with_tail, st));
-        if (with_tail) TRY(enqueue_tail(s, B, tok, margin, st));
+        if (with_tail) TRY(enqueue_tail(s, B, S, true, tok, margin, st));
         CU_TRY(cudaGetLastError());
     }
     for (int b = 0; b < B; ++b) {  // host mirror of what kv_alloc_kernel does on the device
@@ -557,6 +567,28 @@ extern "C" B200_API int b200_shard_run_kernel(b200_shard_t* s, b200_kv_t* kv, in
             g.head_stride = (int64_t)kv->dev.page_size * 128;
             launch_gemv(g, rows, EPI_QKV, true, s->num_sms, st);
             break;
+        case 1: {
+            AttnDecodeParams a{};
+            a.q = s->q_f; a.k_pool = kv->k_pool + (int64_t)layer * kv->layer_stride; a.v_pool = kv->v_pool + (int64_t)layer * kv->layer_stride;
+            a.block_table = kv->dev.block_table; a.t_end = s->tm.t_end; a.call_base = s->tm.call_base;
+            for (int i = 0; i < rows; ++i) a.slots.v[i] = i;
+            a.S = 1; a.n_heads = c.n_heads; a.n_kv = c.n_kv_heads; a.page_size = kv->dev.page_size;
+            a.max_pages_per_slot = kv->dev.max_pages_per_slot;
+            int ns = (2 * s->num_sms + rows * c.n_heads - 1) / (rows * c.n_heads);
+            const int ns_cap = (kv->dev.max_pages_per_slot * kv->dev.page_size + kMaxChunkKeys - 1) / kMaxChunkKeys;
+            if (ns < ns_cap) ns = ns_cap;
+            a.n_splits = ns < 1 ? 1 : (ns > kMaxSplits ? kMaxSplits : ns);
+            a.part = s->attn_part; a.out = s->attn_f;
+            a.tickets = reinterpret_cast<unsigned int*>(s->attn_part + (size_t)kMaxGemvRows * c.n_heads * kMaxSplits * 130);
+            launch_attn_decode(a, rows, st);
+            break;
+        }
+        case 5:
+            if (s->lm_head == nullptr) return fail(B200_ESTATE, "[ERROR] this shard does not hold the lm_head");
+            g.W = s->lm_head; g.N = c.vocab_size; g.K = H; g.out = s->logits; g.x = s->x; g.x_stride = H;
+            g.norm_w = c.has_final_norm ? s->final_norm : nullptr; g.eps = c.rms_eps;
+            launch_gemv(g, rows, EPI_STORE, c.has_final_norm != 0, s->num_sms, st);
+            break;
         case 2:
             g.W = L.wo; g.x = s->attn_f; g.N = H; g.K = s->nq; g.out = s->x;
             launch_gemv(g, rows, EPI_RESID, false, s->num_sms, st);
@@ -586,7 +618,7 @@ extern "C" B200_API int b200_shard_lm_head_argmax(b200_shard_t* s, const void* h
     cudaStream_t st = (cudaStream_t)stream;
     launch_lastrow_bf16_to_f32(reinterpret_cast<const __nv_bfloat16*>(hidden), B, S, s->cfg.hidden_size, s->lastrow, st);
     s->n_launch += 1;
-    TRY(enqueue_tail(s, B, tok, margin, st));
+    TRY(enqueue_tail(s, B, S, false, tok, margin, st));
     CU_TRY(cudaGetLastError());
     s->n_bytes += (uint64_t)s->cfg.vocab_size * s->cfg.hidden_size * 2;
     return 0;
@@ -769,6 +801,8 @@ extern "C" B200_API int b200_attn_decode(const float* q, const void* k_pool, con
     for (int i = 0; i < rows; ++i) a.slots.v[i] = i;
     a.S = 1; a.n_heads = n_heads; a.n_kv = n_kv_heads; a.page_size = page_size; a.max_pages_per_slot = max_pages_per_row;
     a.n_splits = n_splits; a.part = scratch; a.out = out;
+    CU_TRY(cudaMemsetAsync(scratch + (size_t)rows * n_heads * n_splits * 130, 0, (size_t)rows * n_heads * sizeof(unsigned int),
+                           (cudaStream_t)stream));
     launch_attn_decode(a, rows, (cudaStream_t)stream);
     CU_TRY(cudaGetLastError());
     return 0;
@@ -792,7 +826,7 @@ extern "C" B200_API int b200_gemm_f16(const void* a, const void* w, int M, int N
 }
 extern "C" B200_API int b200_gemv_bf16(const float* x, const void* w, int M, int N, int K, float* out, void* stream) {
     if (x == nullptr || w == nullptr || out == nullptr) return fail(B200_EINVAL, "[ERROR] null argument");
-    if (M < 1 || M > kMaxGemvRows || K % 8 != 0 || (size_t)M * (((size_t)K / 8 + 31) / 32) * 1024 > 220 * 1024)
+    if (M < 1 || M > kMaxGemvRows || K % 8 != 0 || K < 8 || gemv_smem_bytes(M, K) > 220 * 1024)
         return fail(B200_EINVAL, "[ERROR] gemv: need 1 <= M <= %d, K %% 8 == 0 and M*K*4 bytes of shared memory", kMaxGemvRows);
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);

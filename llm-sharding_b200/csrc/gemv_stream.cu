@@ -1,0 +1,282 @@
+// The weight-streaming skinny GEMM of the decode path: out[m][n] = sum_k W[n][k] * x[m][k] for M <= 4 token rows,
+// 16-bit weights read exactly once at HBM speed.  Replaces the cuBLAS GEMV-shaped calls under q/k/v/o_proj and
+// gate/up/down_proj (transformers modeling_llama.py:182-184,262-264,287-288) and lm_head
+// (utils/node_worker.py:262) when a shard is asked for a handful of tokens, with the surrounding elementwise work
+// fused in: RMSNorm prologue (:62-67), RoPE + paged K/V append (:146-168, cache_utils.py:102-121), residual add
+// (:325,331), SiLU*mul (:183).
+//
+// Layout of the work: the whole CTA (512 threads) reads one weight row at a time — thread t owns the 16-byte chunk
+// t (+512 j) of every row, so a row is one perfectly coalesced 8 KB burst and the thread's slice of x never changes.
+// Rows are handed to CTAs in contiguous ranges that differ by at most one row (148 CTAs, one per SM: <1 % imbalance
+// instead of the 23 % a warp-per-row split costs on 11008 rows).  R = 4 rows are in flight per thread, plus the next
+// 4 prefetched: 128 KB of loads outstanding per SM with two CTAs resident.  Per group of rows: warp-shuffle reduction, one __syncthreads, and
+// a handful of threads finish the sum and run the epilogue while the rest stream on.
+//
+// Programmatic dependent launch: the first group's weights are requested BEFORE griddepcontrol.wait (weights do not
+// depend on the previous kernel), so a successor CTA that lands on an SM a predecessor CTA just left already has its
+// first loads in flight while the predecessor's stragglers drain.
+#include <stdlib.h>
+
+#include "common.cuh"
+#include "internal.h"
+
+namespace b200 {
+
+constexpr int kGemvThreads = 512;
+constexpr int kGemvWarps = kGemvThreads / 32;
+constexpr int kR = 4;  // weight rows per group
+
+template <bool WBF16>
+__device__ __forceinline__ float2 unpack2(uint32_t v) {
+    if (WBF16) return make_float2(bf_lo(v), bf_hi(v));
+    return __half22float2(*reinterpret_cast<const __half2*>(&v));
+}
+
+// element k of an activation row -> float index in shared memory such that thread t's two float4 reads of step j
+// (chunk c = j*512 + t) are contiguous across the CTA: ((j*2 + half)*512 + t)*4 + e
+__device__ __forceinline__ int xs_index(int k) {
+    const int c = k >> 3, j = c >> 9, t = c & 511, half = (k >> 2) & 1, e = k & 3;
+    return (((j * 2 + half) * 512 + t) << 2) + e;
+}
+
+template <int M, int EPI, bool NORM, bool WBF16>
+__global__ void __launch_bounds__(kGemvThreads, (M <= 2 ? 2 : 1)) gemv_kernel(const GemvParams p) {
+    extern __shared__ __align__(16) float smem[];
+    __shared__ float red[33];
+    constexpr bool PAIRED = (EPI == EPI_QKV || EPI == EPI_SWIGLU);
+    const int K = p.K, kchunks = K >> 3;
+    const int NJ = (kchunks + kGemvThreads - 1) / kGemvThreads;
+    const int Kpad = NJ * kGemvThreads * 8;
+    float* xs = smem;                               // [M][Kpad]
+    float* part = smem + (size_t)M * Kpad;          // [2][warps][kR*M]
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+    // contiguous range of row units [ub, ue) for this CTA (paired epilogues: a unit pair = rows j and j+64 of a tile)
+    int ub, ue;
+    if (PAIRED) {
+        const int64_t P = p.N >> 1;
+        ub = 2 * (int)(P * blockIdx.x / gridDim.x);
+        ue = 2 * (int)(P * (blockIdx.x + 1) / gridDim.x);
+    } else {
+        ub = (int)((int64_t)p.N * blockIdx.x / gridDim.x);
+        ue = (int)((int64_t)p.N * (blockIdx.x + 1) / gridDim.x);
+    }
+    auto unit_row = [&](int u) -> int {
+        if (PAIRED) { const int pr = u >> 1; return ((pr >> 6) << 7) + (pr & 63) + ((u & 1) << 6); }
+        return u;
+    };
+    const int n_groups = (ue - ub + kR - 1) / kR;
+    const int total_steps = n_groups * NJ;
+    const uint4* W4 = reinterpret_cast<const uint4*>(p.W);
+    const int64_t row_stride4 = K >> 3;
+
+    auto load_step = [&](int g, int j, uint4 (&w)[kR]) {
+        const int c = j * kGemvThreads + tid;
+#pragma unroll
+        for (int r = 0; r < kR; ++r) {
+            const int u = ub + g * kR + r;
+            w[r] = (u < ue && c < kchunks) ? ld_stream(W4 + (int64_t)unit_row(u) * row_stride4 + c) : make_uint4(0, 0, 0, 0);
+        }
+    };
+    uint4 wc[kR], wn[kR];
+    if (total_steps > 0) load_step(0, 0, wc);
+
+    // everything above touched only weights; from here on we read what the previous kernel produced
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+
+    // ---- prologue: activations -> shared memory, fp32, in ONE pass.  With the RMSNorm prologue the row is staged as
+    // x * norm_weight and the scalar rsqrt(mean(x^2) + eps) is applied to the finished dot products instead
+    // (it commutes with the sum), so the sum of squares is accumulated on the fly and never delays the staging.
+    __shared__ float rstd_s[4];
+#pragma unroll
+    for (int m = 0; m < M; ++m) {
+        const float* xr = p.x + (size_t)m * p.x_stride;
+        float* xm = xs + (size_t)m * Kpad;
+        float ss = 0.f;
+        for (int k = tid * 4; k < Kpad; k += kGemvThreads * 4) {
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (k < K) {
+                v = *reinterpret_cast<const float4*>(xr + k);
+                if (NORM) {
+                    ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+                    const uint2 wb = *reinterpret_cast<const uint2*>(p.norm_w + k);
+                    v.x *= bf_lo(wb.x); v.y *= bf_hi(wb.x); v.z *= bf_lo(wb.y); v.w *= bf_hi(wb.y);
+                }
+            }
+            *reinterpret_cast<float4*>(xm + xs_index(k)) = v;
+        }
+        if (NORM) {
+            ss = block_sum(ss, red);
+            if (tid == 0) rstd_s[m] = rsqrtf(ss / (float)K + p.eps);
+        }
+    }
+    __syncthreads();
+
+    const float4* xs4 = reinterpret_cast<const float4*>(xs);
+    const int m_stride4 = Kpad >> 2;
+    float acc[kR][M];
+#pragma unroll
+    for (int r = 0; r < kR; ++r)
+#pragma unroll
+        for (int m = 0; m < M; ++m) acc[r][m] = 0.f;
+
+    int g = 0, j = 0, buf = 0;
+    for (int step = 0; step < total_steps; ++step) {
+        int gn = g, jn = j + 1;
+        if (jn == NJ) { jn = 0; gn = g + 1; }
+        if (step + 1 < total_steps) load_step(gn, jn, wn);
+        const int i4 = (j * 2) * kGemvThreads + tid;
+#pragma unroll
+        for (int m = 0; m < M; ++m) {
+            const float4 xl = xs4[m * m_stride4 + i4];
+            const float4 xh = xs4[m * m_stride4 + i4 + kGemvThreads];
+#pragma unroll
+            for (int r = 0; r < kR; ++r) {
+                const uint4 ww = wc[r];
+                const float2 w0 = unpack2<WBF16>(ww.x), w1 = unpack2<WBF16>(ww.y), w2 = unpack2<WBF16>(ww.z), w3 = unpack2<WBF16>(ww.w);
+                float a = acc[r][m];
+                a = fmaf(w0.x, xl.x, a); a = fmaf(w0.y, xl.y, a);
+                a = fmaf(w1.x, xl.z, a); a = fmaf(w1.y, xl.w, a);
+                a = fmaf(w2.x, xh.x, a); a = fmaf(w2.y, xh.y, a);
+                a = fmaf(w3.x, xh.z, a); a = fmaf(w3.y, xh.w, a);
+                acc[r][m] = a;
+            }
+        }
+        if (j == NJ - 1) {  // the group's rows are complete: reduce across the CTA and run the epilogue
+            float* pb = part + (size_t)buf * kGemvWarps * kR * M;
+#pragma unroll
+            for (int r = 0; r < kR; ++r)
+#pragma unroll
+                for (int m = 0; m < M; ++m) {
+                    const float v = warp_sum(acc[r][m]);
+                    if (lane == 0) pb[warp * kR * M + r * M + m] = v;
+                    acc[r][m] = 0.f;
+                }
+            __syncthreads();  // one barrier per group; `part` is double buffered so fast warps may run ahead
+            if (PAIRED) {
+                if (tid < (kR / 2) * M) {
+                    const int prl = tid / M, m = tid % M;
+                    const int u0 = ub + g * kR + 2 * prl;
+                    if (u0 < ue) {
+                        float a = 0.f, b = 0.f;
+#pragma unroll
+                        for (int w = 0; w < kGemvWarps; ++w) {
+                            a += pb[w * kR * M + (2 * prl) * M + m];
+                            b += pb[w * kR * M + (2 * prl + 1) * M + m];
+                        }
+                        if (NORM) { a *= rstd_s[m]; b *= rstd_s[m]; }
+                        const int row0 = unit_row(u0);
+                        const int tile = row0 >> 7, jj = row0 & 63;
+                        if (EPI == EPI_SWIGLU) {
+                            p.out[(size_t)m * (p.N >> 1) + tile * 64 + jj] = silu(a) * b;
+                        } else {  // EPI_QKV: tile == head
+                            const int head = tile;
+                            if (head < p.n_heads + p.n_kv) {  // q or k head: rotate (rotate_half convention)
+                                const float c = p.cos[m * kHalfDim + jj], s = p.sin[m * kHalfDim + jj];
+                                const float lo = a * c - b * s, hi = b * c + a * s;
+                                if (head < p.n_heads) {
+                                    float* q = p.q_out + (size_t)m * p.n_heads * kHeadDim + head * kHeadDim + jj;
+                                    q[0] = lo;
+                                    q[kHalfDim] = hi;
+                                } else {
+                                    __nv_bfloat16* kd = p.k_pool + p.kv_off[m] + (int64_t)(head - p.n_heads) * p.head_stride + jj;
+                                    kd[0] = __float2bfloat16_rn(lo);
+                                    kd[kHalfDim] = __float2bfloat16_rn(hi);
+                                }
+                            } else {
+                                __nv_bfloat16* vd = p.v_pool + p.kv_off[m] + (int64_t)(head - p.n_heads - p.n_kv) * p.head_stride + jj;
+                                vd[0] = __float2bfloat16_rn(a);
+                                vd[kHalfDim] = __float2bfloat16_rn(b);
+                            }
+                        }
+                    }
+                }
+            } else {
+                if (tid < kR * M) {
+                    const int r = tid / M, m = tid % M;
+                    const int u = ub + g * kR + r;
+                    if (u < ue) {
+                        float v = 0.f;
+#pragma unroll
+                        for (int w = 0; w < kGemvWarps; ++w) v += pb[w * kR * M + r * M + m];
+                        if (NORM) v *= rstd_s[m];
+                        float* o = p.out + (size_t)m * p.N + u;
+                        *o = (EPI == EPI_RESID) ? (*o + v) : v;
+                    }
+                }
+            }
+            buf ^= 1;
+        }
+#pragma unroll
+        for (int r = 0; r < kR; ++r) wc[r] = wn[r];
+        g = gn;
+        j = jn;
+    }
+}
+
+static bool pdl_enabled() {
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("B200SHARD_PDL");
+        v = (e != nullptr && e[0] == '0') ? 0 : 1;
+    }
+    return v == 1;
+}
+
+template <typename KernelT>
+static void launch_pdl(KernelT kfn, dim3 grid, dim3 block, size_t smem, cudaStream_t st, const GemvParams& p) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    cudaLaunchKernelEx(&cfg, kfn, p);
+}
+
+template <int M>
+static void gemv_dispatch(const GemvParams& p, int epi, bool norm, int grid, size_t smem, cudaStream_t st) {
+#define B200_GEMV_CASE(E, NRM, WB)                                                                         \
+    {                                                                                                      \
+        auto kfn = gemv_kernel<M, E, NRM, WB>;                                                             \
+        cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);                 \
+        launch_pdl(kfn, dim3(grid), dim3(kGemvThreads), smem, st, p);                                      \
+    }
+    if (epi == EPI_STORE) {
+        if (p.w_bf16) B200_GEMV_CASE(EPI_STORE, false, true)
+        else if (norm) B200_GEMV_CASE(EPI_STORE, true, false)
+        else B200_GEMV_CASE(EPI_STORE, false, false)
+    }
+    else if (epi == EPI_RESID) B200_GEMV_CASE(EPI_RESID, false, false)
+    else if (epi == EPI_QKV) B200_GEMV_CASE(EPI_QKV, true, false)
+    else B200_GEMV_CASE(EPI_SWIGLU, true, false)
+#undef B200_GEMV_CASE
+}
+
+size_t gemv_smem_bytes(int M, int K) {
+    const int NJ = (K / 8 + kGemvThreads - 1) / kGemvThreads;
+    return ((size_t)M * NJ * kGemvThreads * 8 + 2 * kGemvWarps * kR * M) * sizeof(float);
+}
+
+void launch_gemv(const GemvParams& p_in, int M, int epi, bool norm, int num_sms, cudaStream_t st) {
+    GemvParams p = p_in;
+    if (p.x_stride == 0) p.x_stride = p.K;
+    const size_t smem = gemv_smem_bytes(M, p.K);
+    // two 512-thread CTAs per SM when registers (M <= 2) and shared memory allow: 128 KB of loads in flight per SM
+    int grid = (M <= 2 && smem <= 100 * 1024) ? 2 * num_sms : num_sms;
+    const int units = (epi == EPI_QKV || epi == EPI_SWIGLU) ? p.N / 2 : p.N;
+    if (grid > units) grid = units > 0 ? units : 1;
+    switch (M) {
+        case 1: gemv_dispatch<1>(p, epi, norm, grid, smem, st); break;
+        case 2: gemv_dispatch<2>(p, epi, norm, grid, smem, st); break;
+        case 3: gemv_dispatch<3>(p, epi, norm, grid, smem, st); break;
+        default: gemv_dispatch<4>(p, epi, norm, grid, smem, st); break;
+    }
+}
+
+}  // namespace b200

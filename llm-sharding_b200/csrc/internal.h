@@ -39,7 +39,8 @@ enum GemvEpi { EPI_STORE = 0, EPI_RESID = 1, EPI_QKV = 2, EPI_SWIGLU = 3 };
 struct GemvParams {
     const void* W;           // [N,K] row-major, fp16 (w_bf16 == 0) or bf16
     int w_bf16 = 0;
-    const float* x;          // [M,K] fp32
+    const float* x;          // [M,K] fp32, row m at x + m * x_stride
+    int64_t x_stride = 0;    // elements between token rows (0: K)
     const __nv_bfloat16* norm_w;  // [K] (NORM prologue) or nullptr
     float eps;
     int N, K;
@@ -55,6 +56,7 @@ struct GemvParams {
     int64_t head_stride;     // page_size*128 elements between kv heads inside a page
 };
 void launch_gemv(const GemvParams& p, int M, int epi, bool norm, int num_sms, cudaStream_t st);
+size_t gemv_smem_bytes(int M, int K);
 
 void launch_kv_alloc(const KvDev& kv, const SlotList& slots, int B, int S, int32_t* call_base, cudaStream_t st);
 void launch_kv_reset(const KvDev& kv, int slot, cudaStream_t st);
@@ -84,13 +86,16 @@ struct AttnDecodeParams {
     const __nv_bfloat16* v_pool;
     const int32_t* block_table;  // [max_slots][max_pages_per_slot]
     const int32_t* t_end;      // [M]
+    const int32_t* call_base;  // [B] keys cached before this call (may be prefetched early) or nullptr
     SlotList slots;            // row b -> slot
     int S;                     // tokens per row (m = b*S + s)
     int n_heads, n_kv, page_size, max_pages_per_slot, n_splits;
-    float* part;               // scratch [M][n_heads][n_splits][130]
+    float* part;               // scratch: [M][n_heads][n_splits][130] partials, then M*n_heads arrival tickets (zeroed)
     float* out;                // [M, n_heads*128] fp32
+    unsigned int* tickets;     // [M*n_heads] arrival counters, zero before the launch (nullptr: right behind the partials)
 };
 void launch_attn_decode(const AttnDecodeParams& p, int M, cudaStream_t st);
+size_t attn_decode_scratch_floats(int rows, int n_heads, int n_splits);
 
 struct RopeAppendParams {
     const __nv_bfloat16* qkv;  // [M, (n_heads+2*n_kv)*128]

@@ -4,6 +4,7 @@
 // HF LlamaDecoderLayer (transformers modeling_llama.py:62-67,138-168,182-184,303-332) that the
 // reference calls from utils/shard_loader.py:66-74.
 #include <stdio.h>
+#include <stdlib.h>
 
 #include <mutex>
 
@@ -11,213 +12,6 @@
 #include "internal.h"
 
 namespace b200 {
-
-// =========================================================================== GEMV
-// out[m][n] = sum_k W[n][k] * xin[m][k],  M <= 4 token rows, weights bf16 streamed once.
-// One warp owns R weight rows at a time ("item"); lanes stride over K in 16-byte chunks.
-// xin lives in shared memory as fp32 (optionally RMS-normalised on the way in), laid out
-// so that each lane's two float4 reads per step are bank-conflict free:
-//   element k -> chunk c=k/8, step=c/32, lane=c%32, half=(k%8)/4, e=k%4
-//   smem float index = ((step*2+half)*32 + lane)*4 + e
-constexpr int kGemvThreads = 512;
-
-// two packed 16-bit weights -> floats (the shard path holds weights as fp16; the bf16 form serves the unit entry point)
-template <bool WBF16>
-__device__ __forceinline__ float2 unpack2(uint32_t v) {
-    if (WBF16) return make_float2(bf_lo(v), bf_hi(v));
-    return __half22float2(*reinterpret_cast<const __half2*>(&v));
-}
-
-__device__ __forceinline__ int xs_index(int k) {
-    const int c = k >> 3, step = c >> 5, lane = c & 31, half = (k >> 2) & 1, e = k & 3;
-    return (((step * 2 + half) * 32 + lane) << 2) + e;
-}
-
-template <int M, int R, int EPI, bool NORM, bool WBF16>
-__global__ void __launch_bounds__(kGemvThreads, (M == 1 ? 2 : 1)) gemv_kernel(const GemvParams p) {
-    extern __shared__ __align__(16) float xs[];  // [M][Kpad]
-    __shared__ float red[33];
-    const int K = p.K;
-    const int nsteps = (K / 8 + 31) / 32;
-    const int Kpad = nsteps * 256;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-
-    // ---- prologue: stage (normalised) activations in shared memory
-#pragma unroll
-    for (int m = 0; m < M; ++m) {
-        const float* xr = p.x + (size_t)m * K;
-        float rstd = 1.f;
-        if (NORM) {
-            float ss = 0.f;
-            for (int k = tid; k < K; k += kGemvThreads) { const float v = xr[k]; ss += v * v; }
-            ss = block_sum(ss, red);
-            rstd = rsqrtf(ss / (float)K + p.eps);
-        }
-        float* xm = xs + (size_t)m * Kpad;
-        for (int k = tid; k < Kpad; k += kGemvThreads) {
-            float v = 0.f;
-            if (k < K) {
-                v = xr[k];
-                if (NORM) v = v * rstd * __bfloat162float(p.norm_w[k]);
-            }
-            xm[xs_index(k)] = v;
-        }
-    }
-    __syncthreads();
-
-    const int warps_per_cta = kGemvThreads / 32;
-    const int gw = blockIdx.x * warps_per_cta + warp;
-    const int total_warps = gridDim.x * warps_per_cta;
-    constexpr bool PAIRED = (EPI == EPI_QKV || EPI == EPI_SWIGLU);
-    const int n_items = PAIRED ? (p.N / 128) * (128 / R) : (p.N + R - 1) / R;
-    const int kchunks = K / 8;
-    const float4* xs4 = reinterpret_cast<const float4*>(xs);
-    const int m_stride4 = Kpad / 4;
-
-    for (int item = gw; item < n_items; item += total_warps) {
-        int rows[R];
-        if (PAIRED) {
-            const int per_tile = 128 / R;
-            const int base = (item / per_tile) * 128 + (item % per_tile) * (R / 2);
-#pragma unroll
-            for (int r = 0; r < R; ++r) rows[r] = base + (r >> 1) + 64 * (r & 1);
-        } else {
-#pragma unroll
-            for (int r = 0; r < R; ++r) rows[r] = min(item * R + r, p.N - 1);
-        }
-        const uint4* wrow[R];
-#pragma unroll
-        for (int r = 0; r < R; ++r) wrow[r] = reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(p.W) + (size_t)rows[r] * K);
-
-        float acc[R][M];
-#pragma unroll
-        for (int r = 0; r < R; ++r)
-#pragma unroll
-            for (int m = 0; m < M; ++m) acc[r][m] = 0.f;
-
-        constexpr int U = (R == 2) ? 4 : 2;  // steps batched per load group: U*R 16-byte loads in flight per lane
-        for (int s0 = 0; s0 < nsteps; s0 += U) {
-            uint4 w[U][R];
-#pragma unroll
-            for (int u = 0; u < U; ++u) {
-                const int c = (s0 + u) * 32 + lane;
-                const bool ok = (s0 + u < nsteps) && (c < kchunks);
-#pragma unroll
-                for (int r = 0; r < R; ++r) w[u][r] = ok ? ld_stream(wrow[r] + c) : make_uint4(0, 0, 0, 0);
-            }
-#pragma unroll
-            for (int u = 0; u < U; ++u) {
-                if (s0 + u < nsteps) {
-                    const int i4 = ((s0 + u) * 2) * 32 + lane;
-#pragma unroll
-                    for (int m = 0; m < M; ++m) {
-                        const float4 xl = xs4[m * m_stride4 + i4];
-                        const float4 xh = xs4[m * m_stride4 + i4 + 32];
-#pragma unroll
-                        for (int r = 0; r < R; ++r) {
-                            const uint4 ww = w[u][r];
-                            const float2 w0 = unpack2<WBF16>(ww.x), w1 = unpack2<WBF16>(ww.y), w2 = unpack2<WBF16>(ww.z),
-                                         w3 = unpack2<WBF16>(ww.w);
-                            float a = acc[r][m];
-                            a = fmaf(w0.x, xl.x, a);
-                            a = fmaf(w0.y, xl.y, a);
-                            a = fmaf(w1.x, xl.z, a);
-                            a = fmaf(w1.y, xl.w, a);
-                            a = fmaf(w2.x, xh.x, a);
-                            a = fmaf(w2.y, xh.y, a);
-                            a = fmaf(w3.x, xh.z, a);
-                            a = fmaf(w3.y, xh.w, a);
-                            acc[r][m] = a;
-                        }
-                    }
-                }
-            }
-        }
-#pragma unroll
-        for (int r = 0; r < R; ++r)
-#pragma unroll
-            for (int m = 0; m < M; ++m) acc[r][m] = warp_sum(acc[r][m]);
-
-        // ---- epilogues (every lane holds every reduced value; lane (r*M+m) / (pair*M+m) writes)
-        if (EPI == EPI_STORE || EPI == EPI_RESID) {
-#pragma unroll
-            for (int r = 0; r < R; ++r)
-#pragma unroll
-                for (int m = 0; m < M; ++m)
-                    if (lane == r * M + m && item * R + r < p.N) {
-                        float* o = p.out + (size_t)m * p.N + rows[r];
-                        *o = (EPI == EPI_RESID) ? (*o + acc[r][m]) : acc[r][m];
-                    }
-        } else if (EPI == EPI_SWIGLU) {
-#pragma unroll
-            for (int pr = 0; pr < R / 2; ++pr)
-#pragma unroll
-                for (int m = 0; m < M; ++m)
-                    if (lane == pr * M + m) {
-                        const int tile = rows[2 * pr] >> 7, j = rows[2 * pr] & 63;
-                        p.out[(size_t)m * (p.N / 2) + tile * 64 + j] = silu(acc[2 * pr][m]) * acc[2 * pr + 1][m];
-                    }
-        } else if (EPI == EPI_QKV) {
-#pragma unroll
-            for (int pr = 0; pr < R / 2; ++pr)
-#pragma unroll
-                for (int m = 0; m < M; ++m)
-                    if (lane == pr * M + m) {
-                        const int head = rows[2 * pr] >> 7, j = rows[2 * pr] & 63;
-                        const float a = acc[2 * pr][m], b = acc[2 * pr + 1][m];
-                        if (head < p.n_heads + p.n_kv) {  // q or k head: rotate (rotate_half convention)
-                            const float c = p.cos[m * kHalfDim + j], s = p.sin[m * kHalfDim + j];
-                            const float lo = a * c - b * s, hi = b * c + a * s;
-                            if (head < p.n_heads) {
-                                float* q = p.q_out + (size_t)m * p.n_heads * kHeadDim + head * kHeadDim + j;
-                                q[0] = lo;
-                                q[kHalfDim] = hi;
-                            } else {
-                                __nv_bfloat16* kd = p.k_pool + p.kv_off[m] + (int64_t)(head - p.n_heads) * p.head_stride + j;
-                                kd[0] = __float2bfloat16_rn(lo);
-                                kd[kHalfDim] = __float2bfloat16_rn(hi);
-                            }
-                        } else {
-                            __nv_bfloat16* vd = p.v_pool + p.kv_off[m] + (int64_t)(head - p.n_heads - p.n_kv) * p.head_stride + j;
-                            vd[0] = __float2bfloat16_rn(a);
-                            vd[kHalfDim] = __float2bfloat16_rn(b);
-                        }
-                    }
-        }
-    }
-}
-
-template <int M, int R>
-static void gemv_dispatch(const GemvParams& p, int epi, bool norm, int grid, size_t smem, cudaStream_t st) {
-#define B200_GEMV_CASE(E, NRM, WB)                                                                         \
-    {                                                                                                      \
-        auto kfn = gemv_kernel<M, R, E, NRM, WB>;                                                          \
-        cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);                 \
-        kfn<<<grid, kGemvThreads, smem, st>>>(p);                                                          \
-    }
-    if (epi == EPI_STORE) {
-        if (p.w_bf16) B200_GEMV_CASE(EPI_STORE, false, true)
-        else if (norm) B200_GEMV_CASE(EPI_STORE, true, false)
-        else B200_GEMV_CASE(EPI_STORE, false, false)
-    }
-    else if (epi == EPI_RESID) B200_GEMV_CASE(EPI_RESID, false, false)
-    else if (epi == EPI_QKV) B200_GEMV_CASE(EPI_QKV, true, false)
-    else B200_GEMV_CASE(EPI_SWIGLU, true, false)
-#undef B200_GEMV_CASE
-}
-
-void launch_gemv(const GemvParams& p, int M, int epi, bool norm, int num_sms, cudaStream_t st) {
-    const int nsteps = (p.K / 8 + 31) / 32;
-    const size_t smem = (size_t)M * nsteps * 256 * sizeof(float);
-    const int ctas_per_sm = (M == 1 && smem <= 100 * 1024) ? 2 : 1;
-    const int grid = num_sms * ctas_per_sm;
-    switch (M) {
-        case 1: gemv_dispatch<1, 2>(p, epi, norm, grid, smem, st); break;
-        case 2: gemv_dispatch<2, 4>(p, epi, norm, grid, smem, st); break;
-        case 3: gemv_dispatch<3, 4>(p, epi, norm, grid, smem, st); break;
-        default: gemv_dispatch<4, 4>(p, epi, norm, grid, smem, st); break;
-    }
-}
 
 // =========================================================================== KV bookkeeping
 __global__ void kv_init_kernel(KvDev kv) {
@@ -505,130 +299,178 @@ void launch_pack_gate_up(const void* src, int dtype, void* dst, int rows, int co
 }
 
 // =========================================================================== decode attention (split-K)
-// eager_attention_forward (modeling_llama.py:199-221) for a handful of query rows: for each
-// (token m, head h) the cached keys [0, t_end[m]) are split into n_splits chunks; each CTA
-// computes an un-normalised partial (running max, sum, acc[128]) with warp-shuffle reductions,
-// the combine kernel merges them.  K/V are read once, 128-bit, from the paged pool.
+// eager_attention_forward (modeling_llama.py:199-221) for a handful of query rows.  For each (token m, head h) the
+// cached keys [0, t_end[m]) are split into n_splits chunks, one CTA each.  Inside a CTA every half-warp owns one key
+// at a time: its 16 lanes read the key's 256-byte K row and V row as one 16-byte chunk each, the dot product is reduced
+// with four warp shuffles, and softmax runs online in fp32 (running max / sum / rescaled accumulator), so K and V are
+// read once, together, with 8 x 16-byte loads in flight per lane.  The eight half-warp partials are merged in shared
+// memory, the CTA's partial goes to scratch, and the last CTA of the (m, h) group to arrive (atomic ticket) merges the
+// n_splits partials and writes the output — one launch, no separate combine pass.
+// Scratch layout (floats): [rows*n_heads*n_splits][130] partials (acc[128], max, sum) followed by rows*n_heads
+// tickets (uint32).  Tickets must be zero when the kernel starts; the last CTA puts its ticket back to zero.
 constexpr int kAttnThreads = 128;
 constexpr int kPartStride = kHeadDim + 2;
 
-__global__ void __launch_bounds__(kAttnThreads) attn_decode_split_kernel(const AttnDecodeParams p) {
-    extern __shared__ __align__(16) float sm[];  // q[128] | red[40] | scores[chunk]
-    float* qs = sm;
-    float* red = sm + kHeadDim;
-    float* sc = sm + kHeadDim + 40;
+__device__ __forceinline__ float dot8(const uint4& k, const float (&q)[8]) {
+    float d = bf_lo(k.x) * q[0];
+    d = fmaf(bf_hi(k.x), q[1], d);
+    d = fmaf(bf_lo(k.y), q[2], d);
+    d = fmaf(bf_hi(k.y), q[3], d);
+    d = fmaf(bf_lo(k.z), q[4], d);
+    d = fmaf(bf_hi(k.z), q[5], d);
+    d = fmaf(bf_lo(k.w), q[6], d);
+    d = fmaf(bf_hi(k.w), q[7], d);
+    return d;
+}
+
+__global__ void __launch_bounds__(kAttnThreads) attn_decode_kernel(const AttnDecodeParams p) {
+    __shared__ float g_acc[8][kHeadDim];
+    __shared__ float g_m[8], g_l[8];
+    __shared__ int s_last;
     const int split = blockIdx.x, h = blockIdx.y, m = blockIdx.z;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int l16 = lane & 15, grp = warp * 2 + (lane >> 4);  // 8 half-warps, 16 lanes x 8 dims each
     const int T = p.t_end[m];
     const int chunk = (T + p.n_splits - 1) / p.n_splits;
     const int t0 = split * chunk, t1 = min(T, t0 + chunk);
-    float* part = p.part + (((size_t)m * p.n_heads + h) * p.n_splits + split) * kPartStride;
-    if (t0 >= t1) {  // empty split
-        if (tid < kHeadDim) part[tid] = 0.f;
-        if (tid == 0) { part[kHeadDim] = -INFINITY; part[kHeadDim + 1] = 0.f; }
-        return;
-    }
     const int b = m / p.S;
     const int slot = p.slots.v[b];
     const int kvh = h / (p.n_heads / p.n_kv);
     const int32_t* bt = p.block_table + (size_t)slot * p.max_pages_per_slot;
     const int64_t head_stride = (int64_t)p.page_size * kHeadDim;
     const int64_t page_stride = (int64_t)p.n_kv * head_stride;
-    qs[tid] = p.q[((size_t)m * p.n_heads + h) * kHeadDim + tid];
-    __syncthreads();
     const float scale_log2 = 0.08838834764831845f * 1.4426950408889634f;  // 128^-0.5 * log2(e)
-
-    // phase 1: one key per thread
-    float lmax = -INFINITY;
-    for (int t = t0 + tid; t < t1; t += kAttnThreads) {
+    // Keys cached before this forward call do not depend on the kernel that precedes us (which only appends the new
+    // tokens' K/V and produces q): request the first window of them BEFORE griddepcontrol.wait, so that their DRAM
+    // latency hides behind the predecessor's tail.  t_end / block_table / call_base were written by kernels that
+    // completed before the predecessor could even start its own dependent part.
+    const int t_old = (p.call_base != nullptr) ? min(t1, p.call_base[b]) : 0;
+    constexpr int U = 8;  // keys in flight per half-warp
+    auto kv_offset = [&](int t) -> int64_t {
         const int page = bt[t / p.page_size];
-        const uint4* kr = reinterpret_cast<const uint4*>(p.k_pool + page * page_stride + kvh * head_stride +
-                                                         (int64_t)(t % p.page_size) * kHeadDim);
-        float d = 0.f;
+        return page * page_stride + kvh * head_stride + (int64_t)(t % p.page_size) * kHeadDim + l16 * 8;
+    };
+    uint4 kk[U], vv[U];
 #pragma unroll
-        for (int c = 0; c < 16; ++c) {
-            const uint4 kk = kr[c];
-            const float4 q0 = reinterpret_cast<const float4*>(qs)[2 * c], q1 = reinterpret_cast<const float4*>(qs)[2 * c + 1];
-            d = fmaf(bf_lo(kk.x), q0.x, d); d = fmaf(bf_hi(kk.x), q0.y, d);
-            d = fmaf(bf_lo(kk.y), q0.z, d); d = fmaf(bf_hi(kk.y), q0.w, d);
-            d = fmaf(bf_lo(kk.z), q1.x, d); d = fmaf(bf_hi(kk.z), q1.y, d);
-            d = fmaf(bf_lo(kk.w), q1.z, d); d = fmaf(bf_hi(kk.w), q1.w, d);
+    for (int u = 0; u < U; ++u) {
+        const int t = t0 + grp + 8 * u;
+        if (t < t_old) {
+            const int64_t off = kv_offset(t);
+            kk[u] = *reinterpret_cast<const uint4*>(p.k_pool + off);
+            vv[u] = *reinterpret_cast<const uint4*>(p.v_pool + off);
+        } else {
+            kk[u] = make_uint4(0, 0, 0, 0);
+            vv[u] = make_uint4(0, 0, 0, 0);
         }
-        d *= scale_log2;
-        sc[t - t0] = d;
-        lmax = fmaxf(lmax, d);
     }
-    lmax = warp_max(lmax);
-    if (lane == 0) red[warp] = lmax;
-    __syncthreads();
-    float mx = fmaxf(fmaxf(red[0], red[1]), fmaxf(red[2], red[3]));
-    // phase 2: weights.  HF casts softmax probabilities to the model dtype before P.V; here they
-    // stay fp32 (the fp32 oracle is the target).
-    float lsum = 0.f;
-    for (int t = t0 + tid; t < t1; t += kAttnThreads) {
-        const float w = exp2f(sc[t - t0] - mx);
-        sc[t - t0] = w;
-        lsum += w;
+    asm volatile("griddepcontrol.wait;" ::: "memory");            // q and the new K/V come from the previous kernel
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    float q[8];
+    {
+        const float4* qp = reinterpret_cast<const float4*>(p.q + ((size_t)m * p.n_heads + h) * kHeadDim + l16 * 8);
+        const float4 a = qp[0], c = qp[1];
+        q[0] = a.x * scale_log2; q[1] = a.y * scale_log2; q[2] = a.z * scale_log2; q[3] = a.w * scale_log2;
+        q[4] = c.x * scale_log2; q[5] = c.y * scale_log2; q[6] = c.z * scale_log2; q[7] = c.w * scale_log2;
     }
-    lsum = warp_sum(lsum);
-    __syncthreads();
-    if (lane == 0) red[8 + warp] = lsum;
-    __syncthreads();
-    const float l = red[8] + red[9] + red[10] + red[11];
-    // phase 3: P.V — thread = (key group g of 8, 16-byte dim chunk c of 16)
-    const int g = tid >> 4, c = tid & 15;
+    float m_run = -INFINITY, l_run = 0.f;
     float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-    for (int t = t0 + g; t < t1; t += 8) {
-        const int page = bt[t / p.page_size];
-        const uint4 vv = reinterpret_cast<const uint4*>(p.v_pool + page * page_stride + kvh * head_stride +
-                                                        (int64_t)(t % p.page_size) * kHeadDim)[c];
-        const float w = sc[t - t0];
-        acc[0] = fmaf(w, bf_lo(vv.x), acc[0]); acc[1] = fmaf(w, bf_hi(vv.x), acc[1]);
-        acc[2] = fmaf(w, bf_lo(vv.y), acc[2]); acc[3] = fmaf(w, bf_hi(vv.y), acc[3]);
-        acc[4] = fmaf(w, bf_lo(vv.z), acc[4]); acc[5] = fmaf(w, bf_hi(vv.z), acc[5]);
-        acc[6] = fmaf(w, bf_lo(vv.w), acc[6]); acc[7] = fmaf(w, bf_hi(vv.w), acc[7]);
+    // trip count is uniform across the CTA (the shuffles below need every lane of the warp); validity is per key
+    for (int tb0 = t0; tb0 < t1; tb0 += 8 * U) {
+        const int tb = tb0 + grp;
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int t = tb + 8 * u;
+            const bool have = (tb0 == t0) && (t < t_old);  // already requested before the wait
+            if (t < t1 && !have) {
+                const int64_t off = kv_offset(t);
+                kk[u] = *reinterpret_cast<const uint4*>(p.k_pool + off);
+                vv[u] = *reinterpret_cast<const uint4*>(p.v_pool + off);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            float d = dot8(kk[u], q);
+            d += __shfl_xor_sync(0xffffffffu, d, 8);
+            d += __shfl_xor_sync(0xffffffffu, d, 4);
+            d += __shfl_xor_sync(0xffffffffu, d, 2);
+            d += __shfl_xor_sync(0xffffffffu, d, 1);
+            if (tb + 8 * u < t1) {  // uniform within the half-warp; no shuffles inside
+                const float m_new = fmaxf(m_run, d);
+                const float alpha = exp2f(m_run - m_new), w = exp2f(d - m_new);
+                l_run = l_run * alpha + w;
+                const uint4 v = vv[u];
+                acc[0] = fmaf(w, bf_lo(v.x), acc[0] * alpha); acc[1] = fmaf(w, bf_hi(v.x), acc[1] * alpha);
+                acc[2] = fmaf(w, bf_lo(v.y), acc[2] * alpha); acc[3] = fmaf(w, bf_hi(v.y), acc[3] * alpha);
+                acc[4] = fmaf(w, bf_lo(v.z), acc[4] * alpha); acc[5] = fmaf(w, bf_hi(v.z), acc[5] * alpha);
+                acc[6] = fmaf(w, bf_lo(v.w), acc[6] * alpha); acc[7] = fmaf(w, bf_hi(v.w), acc[7] * alpha);
+                m_run = m_new;
+            }
+        }
     }
-    // reduce the 8 key groups: lanes (g even/odd within a warp) by shuffle, then across 4 warps in smem
+    // ---- merge the 8 half-warp partials of this CTA
 #pragma unroll
-    for (int e = 0; e < 8; ++e) acc[e] += __shfl_xor_sync(0xffffffffu, acc[e], 16);
-    __syncthreads();  // scores no longer needed
-    float* stage = sc;  // needs 4*128 floats: guaranteed by the launcher (chunk smem >= 512 floats)
-    if (lane < 16) {
+    for (int e = 0; e < 8; ++e) g_acc[grp][l16 * 8 + e] = acc[e];
+    if (l16 == 0) { g_m[grp] = m_run; g_l[grp] = l_run; }
+    __syncthreads();
+    float* part = p.part + (((size_t)m * p.n_heads + h) * p.n_splits + split) * kPartStride;
+    {
+        float mx = g_m[0];
 #pragma unroll
-        for (int e = 0; e < 8; ++e) stage[warp * kHeadDim + c * 8 + e] = acc[e];
+        for (int g = 1; g < 8; ++g) mx = fmaxf(mx, g_m[g]);
+        float num = 0.f, den = 0.f;
+#pragma unroll
+        for (int g = 0; g < 8; ++g) {
+            const float w = (g_m[g] == -INFINITY) ? 0.f : exp2f(g_m[g] - mx);
+            num = fmaf(w, g_acc[g][tid], num);
+            den = fmaf(w, g_l[g], den);
+        }
+        part[tid] = num;
+        if (tid == 0) { part[kHeadDim] = mx; part[kHeadDim + 1] = den; }
+    }
+    // ---- the last CTA of this (m, h) to finish merges the splits
+    unsigned int* ticket = p.tickets + ((size_t)m * p.n_heads + h);
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) {
+        const unsigned int prev = atomicAdd(ticket, 1u);
+        s_last = (prev == (unsigned int)p.n_splits - 1u);
+        if (s_last) *ticket = 0u;  // ready for the next launch (graph replays included)
     }
     __syncthreads();
-    if (tid < kHeadDim) part[tid] = stage[tid] + stage[kHeadDim + tid] + stage[2 * kHeadDim + tid] + stage[3 * kHeadDim + tid];
-    if (tid == 0) { part[kHeadDim] = mx; part[kHeadDim + 1] = l; }
-}
-
-__global__ void __launch_bounds__(kHeadDim) attn_decode_combine_kernel(const AttnDecodeParams p) {
-    const int h = blockIdx.x, m = blockIdx.y, tid = threadIdx.x;
-    const float* part = p.part + ((size_t)m * p.n_heads + h) * p.n_splits * kPartStride;
+    if (!s_last) return;
+    __threadfence();
+    const float* all = p.part + ((size_t)m * p.n_heads + h) * p.n_splits * kPartStride;
     float mx = -INFINITY;
-    for (int s = 0; s < p.n_splits; ++s) mx = fmaxf(mx, part[s * kPartStride + kHeadDim]);
+    for (int s = 0; s < p.n_splits; ++s) mx = fmaxf(mx, __ldcg(all + s * kPartStride + kHeadDim));
     float num = 0.f, den = 0.f;
     for (int s = 0; s < p.n_splits; ++s) {
-        const float pm = part[s * kPartStride + kHeadDim];
+        const float pm = __ldcg(all + s * kPartStride + kHeadDim);
         const float w = (pm == -INFINITY) ? 0.f : exp2f(pm - mx);
-        num = fmaf(w, part[s * kPartStride + tid], num);
-        den = fmaf(w, part[s * kPartStride + kHeadDim + 1], den);
+        num = fmaf(w, __ldcg(all + s * kPartStride + tid), num);
+        den = fmaf(w, __ldcg(all + s * kPartStride + kHeadDim + 1), den);
     }
     p.out[((size_t)m * p.n_heads + h) * kHeadDim + tid] = num / den;
 }
 
-void launch_attn_decode(const AttnDecodeParams& p, int M, cudaStream_t st) {
-    // smem: q + red + scores for the largest possible chunk is unknown on the host when the call is
-    // replayed from a graph (T grows), so size for the slot capacity.
-    const int64_t max_T = (int64_t)p.max_pages_per_slot * p.page_size;
-    int chunk = (int)((max_T + p.n_splits - 1) / p.n_splits);  // <= kMaxChunkKeys by the caller's choice of n_splits
-    if (chunk < 4 * kHeadDim) chunk = 4 * kHeadDim;
-    const size_t smem = (size_t)(kHeadDim + 40 + chunk) * sizeof(float);
-    cudaFuncSetAttribute(attn_decode_split_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    dim3 grid(p.n_splits, p.n_heads, M);
-    attn_decode_split_kernel<<<grid, kAttnThreads, smem, st>>>(p);
-    dim3 grid2(p.n_heads, M);
-    attn_decode_combine_kernel<<<grid2, kHeadDim, 0, st>>>(p);
+void launch_attn_decode(const AttnDecodeParams& p_in, int M, cudaStream_t st) {
+    AttnDecodeParams p = p_in;
+    if (p.tickets == nullptr)  // default placement: right behind this call's partials
+        p.tickets = reinterpret_cast<unsigned int*>(p.part + (size_t)M * p.n_heads * p.n_splits * kPartStride);
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(p.n_splits, p.n_heads, M);
+    cfg.blockDim = dim3(kAttnThreads);
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    const char* e = getenv("B200SHARD_PDL");
+    cfg.numAttrs = (e != nullptr && e[0] == '0') ? 0 : 1;
+    cudaLaunchKernelEx(&cfg, attn_decode_kernel, p);
+}
+size_t attn_decode_scratch_floats(int rows, int n_heads, int n_splits) {
+    return (size_t)rows * n_heads * n_splits * kPartStride + (size_t)rows * n_heads;
 }
 
 // =========================================================================== decode attention, allocation-free
@@ -652,15 +494,16 @@ void launch_attn_decode(const AttnDecodeParams& p, int M, cudaStream_t st) {
 //  * The first call on each device resolves the array's device address (cudaGetSymbolAddress, with that device
 //    current) and caches it.  Make that first call before you begin any stream capture on that device.
 //  * The array is shared by every call in the process and keeps whatever the previous call left in it.
-//    Nothing in it has to start at zero: each (row, head, split) partial is written by the split kernel —
-//    empty splits included — before the combine kernel reads it, so there is nothing to clear between calls.
+//    The partials need no clearing (each one is written before it is read, empty splits included), but the
+//    arrival tickets behind them must be zero when the kernel starts: every call zeroes that region on the
+//    caller's stream first (cudaMemsetAsync: no allocation), so a call that was aborted cannot poison the next.
 //  * Because it is shared, two calls whose kernels can overlap on the GPU (different streams, or different
 //    host threads on different streams) race on it and corrupt each other.  Issue them on one stream, or order
 //    them with events.
 //  * No cudaMalloc / cudaFree / allocating library routine is called, here or in the launcher.
 constexpr int kStaticPartials = 4096;
-constexpr size_t kStaticScratchFloats = (size_t)kStaticPartials * kPartStride;
-constexpr size_t kStaticScratchBytes = kStaticScratchFloats * sizeof(float);  // 2,129,920 bytes
+constexpr size_t kStaticScratchFloats = (size_t)kStaticPartials * kPartStride + kStaticPartials;  // partials + tickets
+constexpr size_t kStaticScratchBytes = kStaticScratchFloats * sizeof(float);  // 2,146,304 bytes
 static __device__ __align__(256) float g_attn_static_scratch[kStaticScratchFloats];
 
 constexpr int kMaxDevices = 64;
@@ -724,8 +567,11 @@ extern "C" __attribute__((visibility("default"))) int b200_attn_decode_static(
     for (int i = 0; i < rows; ++i) a.slots.v[i] = i;
     a.S = 1; a.n_heads = n_heads; a.n_kv = n_kv_heads; a.page_size = page_size; a.max_pages_per_slot = max_pages_per_row;
     a.n_splits = n_splits; a.part = scratch; a.out = out;
-    launch_attn_decode(a, rows, (cudaStream_t)stream);
-    e = cudaGetLastError();
+    e = cudaMemsetAsync(scratch + (size_t)partials * kPartStride, 0, (size_t)rows * n_heads * sizeof(unsigned int), (cudaStream_t)stream);
+    if (e == cudaSuccess) {
+        launch_attn_decode(a, rows, (cudaStream_t)stream);
+        e = cudaGetLastError();
+    }
     if (e != cudaSuccess) {
         snprintf(msg, sizeof(msg), "[ERROR] CUDA: %s (attn_decode_static launch)", cudaGetErrorString(e));
         set_last_error(msg);

@@ -116,7 +116,7 @@ def test_attn_decode_split_k(lib, rows, n_heads, n_kv, T_list, n_splits):
     k_pool, v_pool, bt, dense, max_pages = _paged_kv(rows, n_kv, T_list, 64, g)
     q = torch.randn(rows, n_heads * 128, device="cuda", generator=g)
     t_end = torch.tensor(T_list, dtype=torch.int32, device="cuda")
-    scratch = torch.empty(rows * n_heads * n_splits * 130, device="cuda")
+    scratch = torch.empty(rows * n_heads * (n_splits * 130 + 1), device="cuda")
     out = torch.full_like(q, float("nan"))
     _lib.check(lib.b200_attn_decode(q.data_ptr(), k_pool.data_ptr(), v_pool.data_ptr(), bt.data_ptr(), t_end.data_ptr(), rows,
                                     n_heads, n_kv, 64, max_pages, n_splits, scratch.data_ptr(), out.data_ptr(), _st()))

@@ -36,7 +36,7 @@ def _problem(rows, n_heads, n_kv, T_list, seed):
 def _both(lib, rows, n_heads, n_kv, T_list, n_splits, seed):
     from llm_sharding_b200 import _lib
     q, k_pool, v_pool, bt, t_end, dense, max_pages = _problem(rows, n_heads, n_kv, T_list, seed)
-    scratch = torch.empty(rows * n_heads * n_splits * 130, device="cuda")
+    scratch = torch.empty(rows * n_heads * (n_splits * 130 + 1), device="cuda")
     ref = torch.full_like(q, float("nan"))
     _lib.check(lib.b200_attn_decode(q.data_ptr(), k_pool.data_ptr(), v_pool.data_ptr(), bt.data_ptr(), t_end.data_ptr(), rows,
                                     n_heads, n_kv, 64, max_pages, n_splits, scratch.data_ptr(), ref.data_ptr(), _st()))
@@ -82,7 +82,7 @@ def test_static_scratch_attention_rejects_problems_beyond_its_built_in_capacity(
     with pytest.raises(ValueError):
         _lib.check(rc)
     # the same problem is fine through the allocating entry point
-    scratch = torch.empty(rows * n_heads * n_splits * 130, device="cuda")
+    scratch = torch.empty(rows * n_heads * (n_splits * 130 + 1), device="cuda")
     _lib.check(lib.b200_attn_decode(q.data_ptr(), k_pool.data_ptr(), v_pool.data_ptr(), bt.data_ptr(), t_end.data_ptr(), rows,
                                     n_heads, n_kv, 64, max_pages, n_splits, scratch.data_ptr(), out.data_ptr(), _st()))
     torch.cuda.synchronize()
