@@ -4,6 +4,7 @@
 #include <math.h>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <map>
@@ -299,6 +300,20 @@ extern "C" B200_API int b200_kv_seq_len(const b200_kv_t* kv, int slot) {
 }
 
 // ------------------------------------------------------------------------------------- forward
+// split-K factor of decode attention: about four CTAs per SM, at least what the per-CTA key bound needs
+static int attn_splits(const b200_shard* s, const b200_kv* kv, int M) {
+    static int forced = -1;
+    if (forced < 0) {
+        const char* e = getenv("B200SHARD_ATTN_SPLITS");
+        forced = e ? atoi(e) : 0;
+    }
+    int ns = (4 * s->num_sms + M * s->cfg.n_heads - 1) / (M * s->cfg.n_heads);  // latency-bound: more, shorter CTAs win (measured)
+    if (forced > 0) ns = forced;
+    const int ns_cap = (kv->dev.max_pages_per_slot * kv->dev.page_size + kMaxChunkKeys - 1) / kMaxChunkKeys;
+    if (ns < ns_cap) ns = ns_cap;
+    return ns < 1 ? 1 : (ns > kMaxSplits ? kMaxSplits : ns);
+}
+
 static int gemv_row_limit(const b200_shard* s) {
     const int kmax = s->cfg.intermediate_size > s->cfg.hidden_size ? s->cfg.intermediate_size : s->cfg.hidden_size;
     int lim = kMaxGemvRows;
@@ -362,10 +377,7 @@ static int enqueue_forward(b200_shard_t* s, b200_kv_t* kv, const SlotList& sl, c
             a.q = s->q_f; a.k_pool = kp; a.v_pool = vp; a.block_table = kv->dev.block_table; a.t_end = s->tm.t_end; a.call_base = s->tm.call_base;
             a.slots = sl; a.S = S; a.n_heads = c.n_heads; a.n_kv = c.n_kv_heads; a.page_size = kv->dev.page_size;
             a.max_pages_per_slot = kv->dev.max_pages_per_slot;
-            int ns = (2 * s->num_sms + M * c.n_heads - 1) / (M * c.n_heads);
-            const int ns_cap = (kv->dev.max_pages_per_slot * kv->dev.page_size + kMaxChunkKeys - 1) / kMaxChunkKeys;
-            if (ns < ns_cap) ns = ns_cap;
-            a.n_splits = ns < 1 ? 1 : (ns > kMaxSplits ? kMaxSplits : ns);
+            a.n_splits = attn_splits(s, kv, M);
             a.part = s->attn_part; a.out = s->attn_f;
             a.tickets = reinterpret_cast<unsigned int*>(s->attn_part + (size_t)kMaxGemvRows * c.n_heads * kMaxSplits * 130);
             launch_attn_decode(a, M, st);
@@ -574,10 +586,7 @@ extern "C" B200_API int b200_shard_run_kernel(b200_shard_t* s, b200_kv_t* kv, in
             for (int i = 0; i < rows; ++i) a.slots.v[i] = i;
             a.S = 1; a.n_heads = c.n_heads; a.n_kv = c.n_kv_heads; a.page_size = kv->dev.page_size;
             a.max_pages_per_slot = kv->dev.max_pages_per_slot;
-            int ns = (2 * s->num_sms + rows * c.n_heads - 1) / (rows * c.n_heads);
-            const int ns_cap = (kv->dev.max_pages_per_slot * kv->dev.page_size + kMaxChunkKeys - 1) / kMaxChunkKeys;
-            if (ns < ns_cap) ns = ns_cap;
-            a.n_splits = ns < 1 ? 1 : (ns > kMaxSplits ? kMaxSplits : ns);
+            a.n_splits = attn_splits(s, kv, rows);
             a.part = s->attn_part; a.out = s->attn_f;
             a.tickets = reinterpret_cast<unsigned int*>(s->attn_part + (size_t)kMaxGemvRows * c.n_heads * kMaxSplits * 130);
             launch_attn_decode(a, rows, st);

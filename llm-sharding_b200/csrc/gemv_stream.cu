@@ -32,12 +32,8 @@ __device__ __forceinline__ float2 unpack2(uint32_t v) {
     return __half22float2(*reinterpret_cast<const __half2*>(&v));
 }
 
-// element k of an activation row -> float index in shared memory such that thread t's two float4 reads of step j
-// (chunk c = j*512 + t) are contiguous across the CTA: ((j*2 + half)*512 + t)*4 + e
-__device__ __forceinline__ int xs_index(int k) {
-    const int c = k >> 3, j = c >> 9, t = c & 511, half = (k >> 2) & 1, e = k & 3;
-    return (((j * 2 + half) * 512 + t) << 2) + e;
-}
+// shared-memory layout of an activation row: the two float4 halves of chunk c = j*512 + t live at float4 index
+// (j*2 + half)*512 + t, so that the CTA's reads of one step are contiguous (no bank conflicts)
 
 template <int M, int EPI, bool NORM, bool WBF16>
 __global__ void __launch_bounds__(kGemvThreads, (M <= 2 ? 2 : 1)) gemv_kernel(const GemvParams p) {
@@ -85,33 +81,39 @@ __global__ void __launch_bounds__(kGemvThreads, (M <= 2 ? 2 : 1)) gemv_kernel(co
     asm volatile("griddepcontrol.wait;" ::: "memory");
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 
-    // ---- prologue: activations -> shared memory, fp32, in ONE pass.  With the RMSNorm prologue the row is staged as
-    // x * norm_weight and the scalar rsqrt(mean(x^2) + eps) is applied to the finished dot products instead
-    // (it commutes with the sum), so the sum of squares is accumulated on the fly and never delays the staging.
+    // ---- prologue: activations -> shared memory, fp32, in ONE pass.  Thread t stages exactly the chunks it will
+    // consume itself (c = j*512 + t: 32 contiguous bytes per thread, 16 KB contiguous per CTA), so the main loop needs
+    // no barrier after the staging.  With the RMSNorm prologue the row is staged as x * norm_weight and the scalar
+    // rsqrt(mean(x^2) + eps) is applied to the finished dot products instead (it commutes with the sum), so the sum of
+    // squares is accumulated on the fly; its block reduction is the only synchronisation before the first epilogue.
     __shared__ float rstd_s[4];
 #pragma unroll
     for (int m = 0; m < M; ++m) {
         const float* xr = p.x + (size_t)m * p.x_stride;
-        float* xm = xs + (size_t)m * Kpad;
+        float4* xm4 = reinterpret_cast<float4*>(xs + (size_t)m * Kpad);
         float ss = 0.f;
-        for (int k = tid * 4; k < Kpad; k += kGemvThreads * 4) {
-            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (k < K) {
-                v = *reinterpret_cast<const float4*>(xr + k);
+        for (int jj = 0; jj < NJ; ++jj) {
+            const int c = jj * kGemvThreads + tid;
+            float4 lo = make_float4(0.f, 0.f, 0.f, 0.f), hi = lo;
+            if (c < kchunks) {
+                lo = *reinterpret_cast<const float4*>(xr + c * 8);
+                hi = *reinterpret_cast<const float4*>(xr + c * 8 + 4);
                 if (NORM) {
-                    ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
-                    const uint2 wb = *reinterpret_cast<const uint2*>(p.norm_w + k);
-                    v.x *= bf_lo(wb.x); v.y *= bf_hi(wb.x); v.z *= bf_lo(wb.y); v.w *= bf_hi(wb.y);
+                    ss += lo.x * lo.x + lo.y * lo.y + lo.z * lo.z + lo.w * lo.w + hi.x * hi.x + hi.y * hi.y + hi.z * hi.z + hi.w * hi.w;
+                    const uint4 wb = *reinterpret_cast<const uint4*>(p.norm_w + c * 8);
+                    lo.x *= bf_lo(wb.x); lo.y *= bf_hi(wb.x); lo.z *= bf_lo(wb.y); lo.w *= bf_hi(wb.y);
+                    hi.x *= bf_lo(wb.z); hi.y *= bf_hi(wb.z); hi.z *= bf_lo(wb.w); hi.w *= bf_hi(wb.w);
                 }
             }
-            *reinterpret_cast<float4*>(xm + xs_index(k)) = v;
+            xm4[(jj * 2) * kGemvThreads + tid] = lo;
+            xm4[(jj * 2 + 1) * kGemvThreads + tid] = hi;
         }
         if (NORM) {
             ss = block_sum(ss, red);
             if (tid == 0) rstd_s[m] = rsqrtf(ss / (float)K + p.eps);
         }
     }
-    __syncthreads();
+    // no __syncthreads: every thread reads back only what it wrote; rstd_s is published by the first group barrier
 
     const float4* xs4 = reinterpret_cast<const float4*>(xs);
     const int m_stride4 = Kpad >> 2;
@@ -268,9 +270,14 @@ void launch_gemv(const GemvParams& p_in, int M, int epi, bool norm, int num_sms,
     if (p.x_stride == 0) p.x_stride = p.K;
     const size_t smem = gemv_smem_bytes(M, p.K);
     // two 512-thread CTAs per SM when registers (M <= 2) and shared memory allow: 128 KB of loads in flight per SM
-    int grid = (M <= 2 && smem <= 100 * 1024) ? 2 * num_sms : num_sms;
-    const int units = (epi == EPI_QKV || epi == EPI_SWIGLU) ? p.N / 2 : p.N;
-    if (grid > units) grid = units > 0 ? units : 1;
+    const int max_ctas = (M <= 2 && smem <= 100 * 1024) ? 2 * num_sms : num_sms;
+    // every CTA walks its rows in groups of kR: pick the CTA count so that all CTAs have the same number of groups
+    // (e.g. 4096 rows -> 256 CTAs x 4 groups instead of 296 CTAs x 3.46 -> 4); the kernel is HBM-bound, a few idle
+    // CTA slots cost nothing, an extra group on the critical path does
+    const int groups = (p.N + kR - 1) / kR;
+    const int per_cta = (groups + max_ctas - 1) / max_ctas;
+    int grid = (groups + per_cta - 1) / per_cta;
+    if (grid < 1) grid = 1;
     switch (M) {
         case 1: gemv_dispatch<1>(p, epi, norm, grid, smem, st); break;
         case 2: gemv_dispatch<2>(p, epi, norm, grid, smem, st); break;
