@@ -229,9 +229,29 @@ class ChainStage:
             self.hop.connect(gathered[self.nxt][0], gathered[self.nxt][1], same_process=False)
             dist.barrier(group=ctrl_group)
         else:
+            # NCCL A/B transport.  Two communicators: hidden states travel forward on one, token ids return to the head
+            # on the other, so that a token the head has not asked for yet cannot block the forward traffic.  Sends are
+            # non-blocking (isend): like a mailbox store they must not stall the producer's stream.
             self.hop = None
+            self.pg_fwd = dist.new_group(backend="nccl")
+            self.pg_tok = dist.new_group(backend="nccl")
             self.inbuf = [torch.empty(self.slot_bytes, dtype=torch.uint8, device=self.device) for _ in range(n_streams)]
             self.outbuf = [torch.empty(self.slot_bytes, dtype=torch.uint8, device=self.device) for _ in range(n_streams)]
+            self._pending = []
+            # NCCL builds the pair-wise communicators lazily and that set-up blocks the host until the peer joins:
+            # do it now, in ring order, so that it can never interleave with the asynchronous pipeline
+            probe = torch.zeros(8, dtype=torch.uint8, device=self.device)
+            if not self.sched.is_head:
+                dist.recv(probe, src=self.prv, group=self.pg_fwd)
+            if not self.sched.is_tail:
+                dist.send(probe, dst=self.nxt, group=self.pg_fwd)
+            if world > 1:
+                if self.sched.is_tail:
+                    dist.send(probe, dst=self.nxt, group=self.pg_tok)
+                if self.sched.is_head:
+                    dist.recv(probe, src=self.prv, group=self.pg_tok)
+            torch.cuda.synchronize()
+            dist.barrier(group=ctrl_group)
         self.tokens = []       # head: device int64[1] tensors, one per recorded decode
         self.host_tokens = []  # head, via_host mode: python ints
 
@@ -255,13 +275,17 @@ class ChainStage:
         if self.hop is not None:
             _lib.check(self.lib.b200_hop_recv(self.hop.handle, None, 0, item["wait"][0], self.max_wait_us, self._st()))
         else:
-            self.dist.recv(self.inbuf[item["wait"][1]][:nbytes], src=self.prv)
+            self.dist.recv(self.inbuf[item["wait"][1]][:nbytes], src=self.prv,
+                           group=self.pg_tok if self.sched.is_head else self.pg_fwd)
 
     def _publish(self, item, nbytes: int) -> None:
         if self.hop is not None:
             _lib.check(self.lib.b200_hop_send(self.hop.handle, None, 0, item["send"][0], self._st()))
         else:
-            self.dist.send(self.outbuf[item["send"][1]][:nbytes], dst=self.nxt)
+            self._pending.append(self.dist.isend(self.outbuf[item["send"][1]][:nbytes], dst=self.nxt,
+                                                 group=self.pg_tok if self.sched.is_tail else self.pg_fwd))
+            if len(self._pending) > 4 * self.n_streams:
+                self._pending = [w for w in self._pending if not w.is_completed()]
 
     def _run(self, item, S: int, tok_in_ptr: int | None, record: bool, via_host: bool = False) -> None:
         import ctypes as C

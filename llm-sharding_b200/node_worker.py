@@ -312,6 +312,8 @@ class NodeController:
         self.recv_config_socket.bind(self.listen_addr)
         self.send_request_socket = None
         self.first_node_addr = ""
+        self._seen_tokens = 0     # next-token messages handled (head node)
+        self._token_log = []      # their ids (batch-1 requests)
         self.received_config = self._receive_config()
         if self.received_config["can_receive_user_request"]:
             self._open_request_socket(self.received_config["first_node_addr"])
@@ -404,6 +406,9 @@ class NodeController:
             if isinstance(data, torch.Tensor):
                 if w.start != 0:
                     raise RuntimeError('[ERROR] I\'m not the first node in the model chain, but received "next_token_id".')
+                self._seen_tokens += 1
+                if data.numel() == 1:
+                    self._token_log.append(int(data.item()))
                 reached_end, data = w.receive_next_token(data, max_new_tokens)
                 if reached_end:
                     w.communicator.transfer_data(w.build_clear_KV_cache_command())

@@ -150,3 +150,101 @@ def test_kv_pool_exhaustion_is_reported(tmp_root):
     with pytest.raises(ValueError):
         sh.forward(x[:, :1], kv, [5])
     kv.close(); sh.close()
+
+
+def test_interleaved_requests_on_separate_kv_slots(tmp_root):
+    """SURVEY.md F6 extension: two requests of different lengths share the shards through the `slot` key of the
+    messages; their prefill and decode passes are interleaved, yet each must reproduce what the oracle gives when
+    the request runs alone."""
+    from llm_sharding_b200.chain import generate  # noqa: F401
+    preset, seed, splits = "tiny", 28, [(0, 1), (1, 3), (3, 4)]   # uneven 1/2/1 split
+    cfg = synth.PRESETS[preset]
+    prompts = [synth.prompt_ids(cfg, 201, 1, 9), synth.prompt_ids(cfg, 202, 1, 70)]
+    n_new = 4
+    expected = []
+    for ids in prompts:
+        t, _, m = _oracle(preset, seed, splits, ids, n_new)
+        expected.append((t, m))
+    workers = build_chain(tmp_root, preset, seed, splits, max_batch=1, max_tokens=128)
+    for w in workers:  # two KV slots per stage
+        w.max_slots = 2
+        w.past_key_value = w.shard.new_cache(2, 256)
+    head = workers[0]
+    try:
+        def one_pass(msg):
+            data = msg
+            for w in workers:
+                data = w.pass_through_shard(data)
+            return data
+        toks = [[], []]
+        feed = [None, None]
+        for r, ids in enumerate(prompts):        # both prompts first (different slots, different lengths)
+            msg = dict(head.receive_user_request(input_ids=ids), slot=[r])
+            toks[r].append(int(one_pass(msg)[0]))
+        for step in range(1, n_new):             # then decode steps, alternating between the two requests
+            for r in (1, 0):
+                fed = expected[r][0][step - 1]   # teacher forcing with the oracle's token
+                msg = {"hidden_states": head.embed_tokens(fed.reshape(-1, 1)), "batch_size": 1, "seq_len": 1, "slot": [r]}
+                toks[r].append(int(one_pass(msg)[0]))
+        for r in range(2):
+            exp_t, exp_m = expected[r]
+            for step in range(n_new):
+                if float(exp_m[step, 0]) >= TIE_TOL:
+                    assert toks[r][step] == int(exp_t[step, 0]), (r, step, toks[r], exp_t[:, 0].tolist())
+        assert workers[1].past_key_value.get_seq_length(0) == 9 + n_new - 1
+        assert workers[1].past_key_value.get_seq_length(1) == 70 + n_new - 1
+    finally:
+        close_chain(workers)
+
+
+def test_node_controller_loop_over_zeromq(tmp_root):
+    """The reference's deployment shape on one GPU: two NodeControllers (threads here, processes in run_this.sh)
+    configured by ConfigSender over ZeroMQ, messages over the ZeroMQ Communicator, request injected through
+    receive_request, KV-clear ring at the end (utils/node_worker.py:385-559, utils/config_sender.py)."""
+    import threading
+    import time
+
+    from gpu_utils import shard_dir
+    from llm_sharding_b200.config_sender import ConfigSender
+    from llm_sharding_b200.node_worker import NodeController
+
+    z, meta = load_golden("tiny_b1")
+    d = shard_dir(tmp_root, meta["preset"], meta["seed"])
+    ports = dict(cfg0=45910, cfg1=45911, d0=45920, d1=45921)
+    ctrls = {}
+
+    def boot(name, port):
+        ctrls[name] = NodeController(d, "cuda:0", torch.bfloat16, listen_port=port, max_tokens=64, use_graphs=False)
+
+    threads = [threading.Thread(target=boot, args=("n0", ports["cfg0"])), threading.Thread(target=boot, args=("n1", ports["cfg1"]))]
+    for t in threads:
+        t.start()
+    s0, s1 = ConfigSender(ports["cfg0"]), ConfigSender(ports["cfg1"])
+    s0.build_config(0, 2, True, f"tcp://127.0.0.1:{ports['d0']}", f"tcp://127.0.0.1:{ports['d1']}", f"tcp://127.0.0.1:{ports['d0']}")
+    s1.build_config(2, 4, False, f"tcp://127.0.0.1:{ports['d1']}", f"tcp://127.0.0.1:{ports['d0']}")
+    time.sleep(0.3)
+    s0.send_config("127.0.0.1")
+    s1.send_config("127.0.0.1")
+    for t in threads:
+        t.join(60)
+    assert set(ctrls) == {"n0", "n1"}
+    n0, n1 = ctrls["n0"], ctrls["n1"]
+    try:
+        ids = torch.from_numpy(z["prompt"])
+        n0.receive_request(input_ids=ids)                     # entry node embeds and forwards to the head (itself)
+        head = n0.node_worker
+        deadline = time.time() + 60
+        cleared = False
+        while time.time() < deadline and not cleared:
+            n0.step(meta["new_tokens"])
+            n1.step(meta["new_tokens"])
+            cleared = head.generated_ids == [] and head.past_key_value.get_seq_length() == 0 and \
+                n1.node_worker.past_key_value.get_seq_length() == 0 and n0._seen_tokens >= meta["new_tokens"]
+        assert cleared, "the request did not finish / the KV-clear ring did not come around"
+        assert n0._token_log == [int(t) for t in z["tokens"][:, 0]]
+    finally:
+        for c in (n0, n1):
+            c.node_worker.communicator.close()
+            c.node_worker.past_key_value = None
+            c.node_worker.shard.engine.close()
+        s0.close(); s1.close()
