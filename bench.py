@@ -361,6 +361,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--transport", default="p2p", choices=["p2p", "nccl"], help="hop transport for --gpus > 1")
+    ap.add_argument("--streams", type=int, default=0, help="--gpus > 1: request streams in flight (default: one per GPU)")
+    ap.add_argument("--rows", type=int, default=1, help="--gpus > 1: batch rows per stream; 8 streams x 4 rows = BASELINE configs[2]'s batch 32")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)

@@ -74,7 +74,8 @@ def run_chain(args, config, metric, ClockSampler, peaks):
     transport = getattr(args, "transport", "p2p")
     cfg = synthetic.LLAMA2_7B
     L = cfg["num_hidden_layers"]
-    n_streams = world
+    rows = max(1, getattr(args, "rows", 1))          # batch rows per request stream (micro-batch)
+    n_streams = getattr(args, "streams", 0) or world
     start, end = layer_range(rank, world, L)
     tmp = tempfile.mkdtemp(prefix=f"b200shard_bench_r{rank}_")
     synthetic.write_model_dir(tmp, cfg)
@@ -82,7 +83,7 @@ def run_chain(args, config, metric, ClockSampler, peaks):
         worker = NodeWorker(f"tcp://*:{48900 + rank}", f"tcp://127.0.0.1:{48900 + (rank + 1) % world}", rank == 0, tmp,
                             device=str(device), dtype=torch.bfloat16,
                             communicator=LoopbackCommunicator(f"tcp://*:{48900 + rank}", f"tcp://127.0.0.1:{48900 + (rank + 1) % world}"),
-                            max_tokens=PROMPT_LEN, max_batch=1, max_slots=n_streams,
+                            max_tokens=rows * PROMPT_LEN, max_batch=rows, max_slots=n_streams * rows,
                             max_seq_len=PROMPT_LEN + 2 * (K + W) + 64,
                             state_provider=synthetic.RandomStateProvider(cfg, str(device), seed=0))
         worker.load_shards(start, end)
@@ -92,18 +93,18 @@ def run_chain(args, config, metric, ClockSampler, peaks):
     except Exception as e:  # reported, not required
         hop_lat = {"error": repr(e)} if rank == 0 else None
     try:
-        stage = ChainStage(worker, rank, world, n_streams, PROMPT_LEN, ctrl_group=ctrl, transport=transport)
+        stage = ChainStage(worker, rank, world, n_streams, PROMPT_LEN, ctrl_group=ctrl, transport=transport, rows=rows)
     except Exception as e:
         if transport == "p2p":
             if rank == 0:
                 print(f"[bench] P2P mailbox set-up failed ({e!r}); falling back to NCCL send/recv", flush=True)
             transport = "nccl"
-            stage = ChainStage(worker, rank, world, n_streams, PROMPT_LEN, ctrl_group=ctrl, transport="nccl")
+            stage = ChainStage(worker, rank, world, n_streams, PROMPT_LEN, ctrl_group=ctrl, transport="nccl", rows=rows)
         else:
             raise
     eng = worker.shard.engine
     g = torch.Generator().manual_seed(1234)
-    prompts = [torch.randint(3, cfg["vocab_size"], (PROMPT_LEN,), generator=g, dtype=torch.int64) for _ in range(n_streams)]
+    prompts = [torch.randint(3, cfg["vocab_size"], (rows * PROMPT_LEN,), generator=g, dtype=torch.int64) for _ in range(n_streams)]
 
     def prefill_all():
         for i in range(n_streams):
@@ -135,7 +136,7 @@ def run_chain(args, config, metric, ClockSampler, peaks):
     prefill_all()
     clear_all()
     prefill_ms = timed(prefill_all)
-    prefill_tok_s = n_streams * PROMPT_LEN / (prefill_ms / 1000)
+    prefill_tok_s = n_streams * rows * PROMPT_LEN / (prefill_ms / 1000)
 
     # ---- decode, device resident
     for _ in range(W):
@@ -147,7 +148,7 @@ def run_chain(args, config, metric, ClockSampler, peaks):
         total_ms = timed(lambda: [stage.decode(i) for _ in range(K) for i in range(n_streams)])
     cnt = eng.counters()
     ms_per_step = total_ms / K
-    value = n_streams * 1000.0 / ms_per_step
+    value = n_streams * rows * 1000.0 / ms_per_step
     launches = torch.tensor([cnt["launches"]], dtype=torch.float64)
     bytes_all = torch.tensor([cnt["bytes"]], dtype=torch.float64)
     dist.all_reduce(launches, group=ctrl)
@@ -162,7 +163,7 @@ def run_chain(args, config, metric, ClockSampler, peaks):
             stage.decode(i, via_host=True)
     t0 = time.perf_counter()
     e2e_ms = timed(lambda: [stage.decode(i, via_host=True) for _ in range(K) for i in range(n_streams)])
-    e2e_val = n_streams * K * 1000.0 / e2e_ms
+    e2e_val = n_streams * rows * K * 1000.0 / e2e_ms
     err = torch.tensor([stage.error()], dtype=torch.float64)
     dist.all_reduce(err, op=dist.ReduceOp.MAX, group=ctrl)
 
@@ -173,9 +174,10 @@ def run_chain(args, config, metric, ClockSampler, peaks):
         line = {
             "metric": metric, "value": value, "unit": "tok/s", "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms_per_step,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": dict(config, transport=transport, layers_this_rank=[start, end]),
+            "config": dict(config, transport=transport, layers_this_rank=[start, end], streams=n_streams, rows_per_stream=rows,
+                           batch_in_flight=n_streams * rows),
             "clocks": clk.summary(),
-            "e2e": {"value": e2e_val, "unit": "tok/s", "h2d_bytes_per_step": 8 * n_streams, "d2h_bytes_per_step": 8 * n_streams,
+            "e2e": {"value": e2e_val, "unit": "tok/s", "h2d_bytes_per_step": 8 * n_streams * rows, "d2h_bytes_per_step": 8 * n_streams * rows,
                     "api": "ChainStage.decode(via_host=True): every token id D2H to the head's pinned host memory and H2D back"},
             "gpu_launches": int(launches[0]),
             "roofline": {"bound": "hbm", "kernel": "one shard call (all kernels of 32/N layers, CUDA-graph replay) on the busiest stage",

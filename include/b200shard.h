@@ -78,6 +78,10 @@ B200_API int b200_shard_set_layer(b200_shard_t* s, int rel_layer, const void* d_
 B200_API int b200_shard_set_final_norm(b200_shard_t* s, const void* d_weight, int dtype, void* stream);
 B200_API int b200_shard_set_lm_head(b200_shard_t* s, const void* d_weight, int dtype, void* stream);
 B200_API int b200_shard_set_embedding(b200_shard_t* s, const void* d_weight, int dtype, void* stream);
+/* Replace the RoPE inverse-frequency table (head_dim/2 = 64 floats, host memory).  The default is
+ * 1 / rope_theta^(2j/128) (compute_default_rope_parameters, modeling_llama.py:93-120); scaled variants such as the
+ * Llama-3.x "llama3" rope_type (transformers modeling_rope_utils.py:550-626) are computed by the host and set here. */
+B200_API int b200_shard_set_rope_inv_freq(b200_shard_t* s, const float* h_inv_freq, int n);
 /* `del self.shard` + empty_cache (utils/node_worker.py:139-147) */
 B200_API int b200_shard_destroy(b200_shard_t* s);
 

@@ -40,6 +40,7 @@ PROTOTYPES = {
     "b200_shard_set_final_norm": (_I, [_P, _P, _I, _P]),
     "b200_shard_set_lm_head": (_I, [_P, _P, _I, _P]),
     "b200_shard_set_embedding": (_I, [_P, _P, _I, _P]),
+    "b200_shard_set_rope_inv_freq": (_I, [_P, C.POINTER(C.c_float), _I]),
     "b200_shard_destroy": (_I, [_P]),
     "b200_kv_create": (_I, [_P, _I, _I, _I, C.POINTER(_P)]),
     "b200_kv_reset": (_I, [_P, _I, _P]),

@@ -206,7 +206,7 @@ class ChainStage:
     ncclSend / ncclRecv through torch.distributed (the A/B alternative)."""
 
     def __init__(self, worker, rank: int, world: int, n_streams: int, max_prompt: int, ctrl_group=None,
-                 transport: str = "p2p", max_wait_us: int = 20_000_000):
+                 transport: str = "p2p", max_wait_us: int = 20_000_000, rows: int = 1):
         import torch.distributed as dist
 
         self.w, self.rank, self.world, self.n_streams = worker, rank, world, n_streams
@@ -220,7 +220,8 @@ class ChainStage:
         self.max_wait_us = max_wait_us
         self.dist = dist
         self.nxt, self.prv = (rank + 1) % world, (rank - 1) % world
-        self.slot_bytes = max(max_prompt * self.H * 2, 4096)
+        self.rows = rows  # batch rows of one stream (micro-batch); stream i owns KV slots [i*rows, (i+1)*rows)
+        self.slot_bytes = max(rows * max_prompt * self.H * 2, 4096)
         if transport == "p2p":
             self.hop = P2PHop(self.device, n_streams, self.slot_bytes)
             mine = (self.hop.export(), self.hop.dev_index)
@@ -289,9 +290,10 @@ class ChainStage:
 
     def _run(self, item, S: int, tok_in_ptr: int | None, record: bool, via_host: bool = False) -> None:
         import ctypes as C
-        slots = (C.c_int32 * 1)(item["kv_slot"])
+        B = self.rows
+        slots = (C.c_int32 * B)(*range(item["kv_slot"] * B, item["kv_slot"] * B + B))
         sch = self.sched
-        hid_bytes, tok_bytes = S * self.H * 2, 8
+        hid_bytes, tok_bytes = B * S * self.H * 2, 8 * B
         in_bytes = tok_bytes if (sch.is_head and item["kind"] == "decode") else hid_bytes
         out_bytes = tok_bytes if sch.is_tail else hid_bytes
         self._wait(item, in_bytes)
@@ -302,34 +304,34 @@ class ChainStage:
                 if via_host:
                     # end-to-end mode: the id leaves the GPU (D2H, the host blocks until the ring delivered it), is seen
                     # by the host loop (the reference decodes / prints it there) and comes back from pinned memory (H2D)
-                    src = (tensor_view(tok_in_ptr, 8, self.device) if self.hop is not None else self.inbuf[item["wait"][1]][:8])
+                    src = (tensor_view(tok_in_ptr, 8 * B, self.device) if self.hop is not None else self.inbuf[item["wait"][1]][:8 * B])
                     if not hasattr(self, "_host_tok"):
-                        self._host_tok = torch.empty(1, dtype=torch.int64).pin_memory()
-                        self._dev_tok = [torch.empty(1, dtype=torch.int64, device=self.device) for _ in range(self.n_streams)]
+                        self._host_tok = torch.empty(B, dtype=torch.int64).pin_memory()
+                        self._dev_tok = [torch.empty(B, dtype=torch.int64, device=self.device) for _ in range(self.n_streams)]
                     self._host_tok.copy_(src.view(torch.int64))  # synchronous D2H
-                    self.host_tokens.append(int(self._host_tok[0]))
+                    self.host_tokens.append(self._host_tok.tolist())
                     self._dev_tok[item["stream"]].copy_(self._host_tok, non_blocking=True)
                     tok_in_ptr = self._dev_tok[item["stream"]].data_ptr()
                 elif record:
-                    self.tokens.append(tensor_view(tok_in_ptr, 8, self.device).view(torch.int64).clone()
-                                       if self.hop is not None else self.inbuf[item["wait"][1]][:8].view(torch.int64).clone())
+                    self.tokens.append(tensor_view(tok_in_ptr, 8 * B, self.device).view(torch.int64).clone()
+                                       if self.hop is not None else self.inbuf[item["wait"][1]][:8 * B].view(torch.int64).clone())
             if sch.is_tail:  # single-stage ring: token in, token out
-                _lib.check(self.lib.b200_shard_step_tokens(self.eng.handle, self.kv.handle, slots, tok_in_ptr, 1, S, self.causal,
+                _lib.check(self.lib.b200_shard_step_tokens(self.eng.handle, self.kv.handle, slots, tok_in_ptr, B, S, self.causal,
                                                            None, out_ptr, None, self._st()))
             else:
-                _lib.check(self.lib.b200_shard_step_tokens(self.eng.handle, self.kv.handle, slots, tok_in_ptr, 1, S, self.causal,
+                _lib.check(self.lib.b200_shard_step_tokens(self.eng.handle, self.kv.handle, slots, tok_in_ptr, B, S, self.causal,
                                                            out_ptr, None, None, self._st()))
         elif sch.is_tail:
-            _lib.check(self.lib.b200_shard_forward_argmax(self.eng.handle, self.kv.handle, slots, self._in_ptr(item), 1, S,
+            _lib.check(self.lib.b200_shard_forward_argmax(self.eng.handle, self.kv.handle, slots, self._in_ptr(item), B, S,
                                                           self.causal, None, out_ptr, None, self._st()))
         else:
-            _lib.check(self.lib.b200_shard_forward(self.eng.handle, self.kv.handle, slots, self._in_ptr(item), 1, S,
+            _lib.check(self.lib.b200_shard_forward(self.eng.handle, self.kv.handle, slots, self._in_ptr(item), B, S,
                                                    self.causal, out_ptr, self._st()))
         self._publish(item, out_bytes)
 
     # -- public
     def prefill(self, stream: int, prompt_len: int, ids: torch.Tensor | None = None) -> None:
-        """ids: int64 [prompt_len] on this GPU (head only)."""
+        """ids: int64 [rows * prompt_len] (row-major [rows, prompt_len]) on this GPU (head only)."""
         item = self.sched.prefill(stream)
         if self.sched.is_head and ids is None:
             raise ValueError("[ERROR] the head stage needs the prompt ids")

@@ -653,6 +653,14 @@ extern "C" B200_API int b200_shard_reset_counters(b200_shard_t* s) {
     s->n_launch = s->n_bytes = s->n_flops = s->n_calls = 0;
     return 0;
 }
+extern "C" B200_API int b200_shard_set_rope_inv_freq(b200_shard_t* s, const float* h_inv_freq, int n) {
+    if (s == nullptr || h_inv_freq == nullptr) return fail(B200_EINVAL, "[ERROR] null argument");
+    if (n != 64) return fail(B200_EINVAL, "[ERROR] inv_freq must have head_dim/2 = 64 entries (got %d)", n);
+    for (int j = 0; j < 64; ++j) s->inv.v[j] = h_inv_freq[j];
+    for (auto& g : s->graph_cache) cudaGraphExecDestroy(g.second);  // captured graphs hold the old table by value
+    s->graph_cache.clear();
+    return 0;
+}
 extern "C" B200_API int b200_shard_set_graphs(b200_shard_t* s, int enabled) {
     if (s == nullptr) return fail(B200_EINVAL, "[ERROR] null shard");
     s->graphs = enabled != 0;

@@ -19,6 +19,22 @@ LAYER_KEYS = (  # LlamaDecoderLayer.state_dict() keys as saved in block_{i}.pth 
 )
 
 
+def rope_inv_freq(head_dim: int, theta: float, scaling: dict | None):
+    """Inverse RoPE frequencies as fp32 torch ops, the way transformers computes them: default
+    (modeling_llama.py:116-118) or the Llama-3.x "llama3" rescaling (modeling_rope_utils.py:606-624)."""
+    import math
+    inv = 1.0 / (theta ** (torch.arange(0, head_dim, 2, dtype=torch.int64).to(torch.float) / head_dim))
+    if scaling:
+        f, lo, hi, old = (scaling["factor"], scaling["low_freq_factor"], scaling["high_freq_factor"],
+                          scaling["original_max_position_embeddings"])
+        wavelen = 2 * math.pi / inv
+        scaled = torch.where(wavelen > old / lo, inv / f, inv)
+        smooth = (old / wavelen - lo) / (hi - lo)
+        mid = ~(wavelen < old / hi) * ~(wavelen > old / lo)
+        inv = torch.where(mid, (1 - smooth) * scaled / f + smooth * scaled, scaled)
+    return inv.float().contiguous()
+
+
 def read_model_config(shards_path: str) -> dict:
     """The fields of config.json the path needs (what LlamaConfig.from_pretrained(shards_path)
     supplies at utils/shard_loader.py:35 and utils/node_worker.py:88)."""
@@ -27,9 +43,11 @@ def read_model_config(shards_path: str) -> dict:
     n_heads = c["num_attention_heads"]
     rope = c.get("rope_parameters") or {}
     scaling = c.get("rope_scaling") or ({} if rope.get("rope_type", "default") == "default" else rope)
-    if scaling and scaling.get("rope_type", scaling.get("type", "default")) != "default":
-        raise ValueError("[ERROR] only the default RoPE parametrisation is built (no llama3 / yarn scaling yet)")
+    rope_type = (scaling or {}).get("rope_type", (scaling or {}).get("type", "default"))
+    if rope_type not in ("default", "llama3"):
+        raise ValueError(f"[ERROR] RoPE type {rope_type!r} is not built (default and llama3 are)")
     return {
+        "rope_scaling": dict(scaling, rope_type=rope_type) if rope_type != "default" else None,
         "hidden_size": c["hidden_size"], "intermediate_size": c["intermediate_size"],
         "num_hidden_layers": c["num_hidden_layers"], "num_attention_heads": n_heads,
         "num_key_value_heads": c.get("num_key_value_heads") or n_heads,
@@ -63,6 +81,9 @@ class Shard:
         h = C.c_void_p()
         _lib.check(self.lib.b200_shard_create(C.byref(cfg), self.dev_index, C.byref(h)))
         self.handle = h
+        # the table torch would compute (bit-identical to the reference's LlamaRotaryEmbedding.inv_freq), scaled or not
+        inv = rope_inv_freq(model_cfg["head_dim"], model_cfg["rope_theta"], model_cfg.get("rope_scaling"))
+        _lib.check(self.lib.b200_shard_set_rope_inv_freq(self.handle, inv.numpy().ctypes.data_as(C.POINTER(C.c_float)), inv.numel()))
         self.graphs = False
         self._step_bufs: dict = {}   # B -> persistent (hidden_in, hidden_out, tok, margin) for single-token calls
 

@@ -33,15 +33,31 @@ def rms_norm(x: torch.Tensor, weight: torch.Tensor, eps: float) -> torch.Tensor:
     return weight * h.to(dt)
 
 
-def rope_inv_freq(head_dim: int, theta: float) -> torch.Tensor:
-    """compute_default_rope_parameters, SP:93-120."""
-    return 1.0 / (theta ** (torch.arange(0, head_dim, 2, dtype=torch.int64).to(torch.float) / head_dim))
+def rope_inv_freq(head_dim: int, theta: float, scaling: dict | None = None) -> torch.Tensor:
+    """compute_default_rope_parameters, SP:93-120; with ``scaling`` (rope_type "llama3": factor, low_freq_factor,
+    high_freq_factor, original_max_position_embeddings) the Llama-3.x rescaling of
+    site-packages/transformers/modeling_rope_utils.py:550-626 (_compute_llama3_parameters), op for op."""
+    import math
+    inv_freq = 1.0 / (theta ** (torch.arange(0, head_dim, 2, dtype=torch.int64).to(torch.float) / head_dim))
+    if not scaling or scaling.get("rope_type", "default") == "default":
+        return inv_freq
+    if scaling["rope_type"] != "llama3":
+        raise ValueError(f"[ERROR] unsupported rope_type {scaling['rope_type']}")
+    factor, low, high = scaling["factor"], scaling["low_freq_factor"], scaling["high_freq_factor"]
+    old_len = scaling["original_max_position_embeddings"]
+    low_wavelen, high_wavelen = old_len / low, old_len / high
+    wavelen = 2 * math.pi / inv_freq
+    inv_llama = torch.where(wavelen > low_wavelen, inv_freq / factor, inv_freq)
+    smooth = (old_len / wavelen - low) / (high - low)
+    smoothed = (1 - smooth) * inv_llama / factor + smooth * inv_llama
+    is_medium = ~(wavelen < high_wavelen) * ~(wavelen > low_wavelen)
+    return torch.where(is_medium, smoothed, inv_llama)
 
 
-def rope_cos_sin(position_ids: torch.Tensor, head_dim: int, theta: float, dtype: torch.dtype):
+def rope_cos_sin(position_ids: torch.Tensor, head_dim: int, theta: float, dtype: torch.dtype, scaling: dict | None = None):
     """LlamaRotaryEmbedding.forward, SP:124-135 (called utils/node_worker.py:241): fp32
     ``inv_freq (x) pos``, ``cat(freqs, freqs)``, cos/sin, cast to the activation dtype."""
-    inv = rope_inv_freq(head_dim, theta)[None, :, None].float().expand(position_ids.shape[0], -1, 1)
+    inv = rope_inv_freq(head_dim, theta, scaling)[None, :, None].float().expand(position_ids.shape[0], -1, 1)
     pos = position_ids[:, None, :].float()
     freqs = (inv @ pos).transpose(1, 2)
     emb = torch.cat((freqs, freqs), dim=-1)
@@ -199,7 +215,8 @@ class OracleWorker:
                 raise RuntimeError("[ERROR] after embedding layer, the states should first passing hidden layer 0!")
             self.batch_size = state_info["batch_size"]
             pos = build_position_ids(self.cache.get_seq_length(), state_info["seq_len"], state_info["batch_size"])
-            cos, sin = rope_cos_sin(pos, self.cfg.head_dim, self.cfg.rope_theta, state_info["hidden_states"].dtype)
+            cos, sin = rope_cos_sin(pos, self.cfg.head_dim, self.cfg.rope_theta, state_info["hidden_states"].dtype,
+                                    getattr(self.cfg, "rope_scaling", None))
         elif isinstance(state_info, dict) and "cos" in state_info and "sin" in state_info:
             cos, sin = state_info["cos"], state_info["sin"]
         else:

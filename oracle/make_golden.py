@@ -36,6 +36,8 @@ CASES = {
     "small_b2_single": ("small", 24, [(0, 6)], 2, 40, 4, "batched"),
     "small_b1_s160": ("small", 4, [(0, 3), (3, 6)], 1, 160, 4, "generate"),
     "gqa_b2": ("gqa", 23, [(0, 2), (2, 4)], 2, 17, 4, "batched"),
+    # GQA + llama3 RoPE rescaling, prompt long enough to reach the rescaled frequency bands
+    "llama3ish_b1": ("llama3ish", 7, [(0, 2), (2, 4)], 1, 150, 4, "generate"),
 }
 BIG_CASES = {
     # BASELINE.json configs[0]: Llama-2-7B arch, 2 nodes 0-16/16-32, fp32 CPU, B=1, 32 -> 16 tokens

@@ -49,6 +49,7 @@ class SynthConfig:
     rms_norm_eps: float = 1e-5
     rope_theta: float = 10000.0
     init_std: float = 0.02
+    rope_scaling: dict | None = None   # e.g. the Llama-3.x "llama3" rescaling
 
     @property
     def head_dim(self) -> int:
@@ -60,6 +61,11 @@ PRESETS = {
     "tiny": SynthConfig("tiny", 1000, 256, 640, 4, 2, 2, max_position_embeddings=512),
     "small": SynthConfig("small", 2000, 512, 1408, 6, 4, 4, max_position_embeddings=1024),
     "gqa": SynthConfig("gqa", 1000, 512, 1024, 4, 4, 2, max_position_embeddings=512),
+    # Llama-3.2-style: GQA + "llama3" RoPE rescaling (what start_node.py:14 of the reference actually points at);
+    # original_max_position_embeddings is small so that test positions reach the rescaled / smoothed bands
+    "llama3ish": SynthConfig("llama3ish", 1000, 512, 1024, 4, 4, 2, max_position_embeddings=2048, rope_theta=500000.0,
+                             rope_scaling={"rope_type": "llama3", "factor": 8.0, "low_freq_factor": 1.0,
+                                           "high_freq_factor": 4.0, "original_max_position_embeddings": 64}),
     "llama2_7b": SynthConfig("llama2_7b", 32000, 4096, 11008, 32, 32, 32),
 }
 
@@ -138,6 +144,7 @@ def hf_config_dict(cfg: SynthConfig) -> dict:
         "max_position_embeddings": cfg.max_position_embeddings,
         "rms_norm_eps": cfg.rms_norm_eps,
         "rope_theta": cfg.rope_theta,
+        **({"rope_scaling": dict(cfg.rope_scaling)} if cfg.rope_scaling else {}),
         "hidden_act": "silu",
         "attention_bias": False,
         "mlp_bias": False,

@@ -75,6 +75,8 @@ def _oracle(preset, seed, splits, ids, n_new, causal=False):
     ("small", 106, [(0, 2), (2, 6)], 3, 33, 3, True),
     ("gqa", 107, [(0, 4)], 2, 65, 3, False),
     ("gqa", 108, [(0, 4)], 1, 3, 6, True),
+    ("llama3ish", 109, [(0, 2), (2, 4)], 1, 150, 3, False),   # GQA + llama3 RoPE rescaling, positions past the smoothed band
+    ("llama3ish", 110, [(0, 4)], 2, 3, 4, True),
 ])
 def test_chain_matches_oracle_on_fresh_inputs(preset, seed, splits, B, S, n_new, causal, tmp_root):
     cfg = synth.PRESETS[preset]

@@ -62,3 +62,24 @@ def test_oracle_errors_match_reference_classes():
         w.receive_user_request(synth.prompt_ids(cfg, 1, 1, 4))
     with pytest.raises(RuntimeError):
         w.pass_through_shard({"hidden_states": torch.zeros(1, 1, 256), "batch_size": 1, "seq_len": 1})
+
+
+def test_llama3_rope_rescaling_matches_transformers():
+    """The oracle's and the product host code's inv_freq against the third-party module that carries the arithmetic
+    (transformers LlamaRotaryEmbedding with rope_type llama3) — the dependency the reference calls at
+    utils/node_worker.py:152."""
+    from transformers import LlamaConfig
+    from transformers.models.llama.modeling_llama import LlamaRotaryEmbedding
+
+    from llm_sharding_b200.engine import rope_inv_freq as product_inv_freq
+    from oracle.llama_oracle import rope_inv_freq
+    for old_len in (64, 8192):
+        sc = {"rope_type": "llama3", "factor": 8.0, "low_freq_factor": 1.0, "high_freq_factor": 4.0,
+              "original_max_position_embeddings": old_len}
+        cfg = LlamaConfig(hidden_size=512, num_attention_heads=4, rope_theta=500000.0, rope_scaling=dict(sc),
+                          max_position_embeddings=4096)
+        ref = LlamaRotaryEmbedding(cfg).inv_freq
+        assert torch.equal(rope_inv_freq(128, 500000.0, sc), ref)
+        assert torch.equal(product_inv_freq(128, 500000.0, sc), ref)
+        assert not torch.equal(ref, rope_inv_freq(128, 500000.0, None))
+    assert torch.equal(product_inv_freq(128, 10000.0, None), rope_inv_freq(128, 10000.0))
