@@ -159,7 +159,7 @@ B200_API int b200_shard_set_graphs(b200_shard_t* s, int enabled);
 /* Launch ONE of the decode-path kernels of layer `layer` exactly as b200_shard_forward would (same template
  * instantiation, same buffers; inputs are whatever the workspace holds): kind 0 = RMSNorm+QKV+RoPE+KV-append,
  * 1 = decode attention over the slots' current context, 2 = o_proj+residual, 3 = RMSNorm+gate/up+SwiGLU,
- * 4 = down_proj+residual, 5 = final RMSNorm + lm_head (layer ignored).  `rows` = token rows (1..4).
+ * 4 = down_proj+residual, 5 = final RMSNorm + lm_head (layer ignored).  `rows` = token rows (1..8).
  * Used by bench.py to time the dominant kernel on its own stream for the roofline figure. */
 B200_API int b200_shard_run_kernel(b200_shard_t* s, b200_kv_t* kv, int kind, int layer, int rows, void* stream);
 /* LlamaRMSNorm.forward (transformers modeling_llama.py:62-67): fp32 in -> bf16 out, [rows, n] */
@@ -190,8 +190,9 @@ B200_API int b200_gemm_bf16(const void* d_a, const void* d_w, int M, int N, int 
 /* same kernel with fp16 operands (A[M,K] and W[N,K] both fp16): what the shard path runs — it holds the bf16 model
  * weights as fp16 (exact in fp16's normal range) so that activations carry 10 mantissa bits into the tensor cores */
 B200_API int b200_gemm_f16(const void* d_a, const void* d_w, int M, int N, int K, float* d_out, void* stream);
-/* out[M,N] (fp32) = X[M,K] (fp32) * W[N,K]^T (bf16), M <= 4: the weight-streaming decode kernel */
-B200_API int b200_gemv_bf16(const float* d_x, const void* d_w, int M, int N, int K, float* d_out, void* stream);
+/* out[M,N] (fp32) = X[M,K] (fp32) * W[N,K]^T (fp16), M <= 8: the weight-streaming decode kernels (M == 1: CUDA cores,
+ * fp32 activations; 2 <= M <= 8: mma.sync tensor cores, activations rounded to fp16) */
+B200_API int b200_gemv_f16(const float* d_x, const void* d_w, int M, int N, int K, float* d_out, void* stream);
 
 #ifdef __cplusplus
 }

@@ -841,15 +841,15 @@ extern "C" B200_API int b200_gemm_f16(const void* a, const void* w, int M, int N
     CU_TRY(cudaGetLastError());
     return 0;
 }
-extern "C" B200_API int b200_gemv_bf16(const float* x, const void* w, int M, int N, int K, float* out, void* stream) {
+extern "C" B200_API int b200_gemv_f16(const float* x, const void* w, int M, int N, int K, float* out, void* stream) {
     if (x == nullptr || w == nullptr || out == nullptr) return fail(B200_EINVAL, "[ERROR] null argument");
     if (M < 1 || M > kMaxGemvRows || K % 8 != 0 || K < 8 || gemv_smem_bytes(M, K) > 220 * 1024)
-        return fail(B200_EINVAL, "[ERROR] gemv: need 1 <= M <= %d, K %% 8 == 0 and M*K*4 bytes of shared memory", kMaxGemvRows);
+        return fail(B200_EINVAL, "[ERROR] gemv: need 1 <= M <= %d, K %% 8 == 0 and the token rows must fit in shared memory", kMaxGemvRows);
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     GemvParams g{};
-    g.W = w; g.w_bf16 = 1; g.x = x; g.N = N; g.K = K; g.out = out;
+    g.W = w; g.x = x; g.N = N; g.K = K; g.out = out;
     launch_gemv(g, M, EPI_STORE, false, sms, (cudaStream_t)stream);
     CU_TRY(cudaGetLastError());
     return 0;

@@ -7,7 +7,7 @@
 namespace b200 {
 
 constexpr int kMaxBatch = 64;
-constexpr int kMaxGemvRows = 4;   // token rows served by the weight-streaming SIMT kernels
+constexpr int kMaxGemvRows = 8;   // token rows served by the weight-streaming kernels (1: SIMT fp32, 2..8: mma.sync fp16)
 constexpr int kMaxSplits = 16;    // split-K factor bound of decode attention
 constexpr int kMaxChunkKeys = 8192;  // keys one decode-attention CTA may hold scores for
 struct SlotList { int32_t v[kMaxBatch]; };
@@ -37,8 +37,7 @@ struct TokMeta {
 enum GemvEpi { EPI_STORE = 0, EPI_RESID = 1, EPI_QKV = 2, EPI_SWIGLU = 3 };
 
 struct GemvParams {
-    const void* W;           // [N,K] row-major, fp16 (w_bf16 == 0) or bf16
-    int w_bf16 = 0;
+    const void* W;           // [N,K] row-major, fp16
     const float* x;          // [M,K] fp32, row m at x + m * x_stride
     int64_t x_stride = 0;    // elements between token rows (0: K)
     const __nv_bfloat16* norm_w;  // [K] (NORM prologue) or nullptr

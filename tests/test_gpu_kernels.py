@@ -35,17 +35,24 @@ def test_rmsnorm_matches_llama_rmsnorm(lib, rows, n):
     assert rel_l2(out.float(), ref) < 3e-3
 
 
-@pytest.mark.parametrize("M", [1, 2, 3, 4])
-@pytest.mark.parametrize("N,K", [(256, 256), (1000, 256), (4096, 4096), (4096, 11008), (1536, 640), (32000, 4096)])
+@pytest.mark.parametrize("M", [1, 2, 3, 4, 5, 8])
+@pytest.mark.parametrize("N,K", [(256, 256), (1000, 256), (4096, 4096), (4096, 11008), (1536, 640), (32000, 4096), (24, 72)])
 def test_gemv_weight_streaming(lib, M, N, K):
     from llm_sharding_b200 import _lib
     g = torch.Generator(device="cuda").manual_seed(M + N + K)
     x = torch.randn(M, K, device="cuda", generator=g)
-    w = (torch.randn(N, K, device="cuda", generator=g) * 0.02).bfloat16()
+    w = (torch.randn(N, K, device="cuda", generator=g) * 0.02).bfloat16().half()  # bf16 model weights held as fp16
     out = torch.full((M, N), float("nan"), device="cuda")
-    _lib.check(lib.b200_gemv_bf16(x.data_ptr(), w.data_ptr(), M, N, K, out.data_ptr(), _st()))
-    ref = (x.double() @ w.double().t()).float()
-    assert rel_l2(out, ref) < 2e-6  # fp32 accumulation, different summation order only
+    _lib.check(lib.b200_gemv_f16(x.data_ptr(), w.data_ptr(), M, N, K, out.data_ptr(), _st()))
+    torch.cuda.synchronize()
+    assert not torch.isnan(out).any()
+    if M == 1:   # CUDA-core kernel: fp32 activations and accumulation, only the summation order differs
+        ref = (x.double() @ w.double().t()).float()
+        assert rel_l2(out, ref) < 2e-6
+    else:        # tensor-core kernel: activations rounded to fp16 (2^-11 relative), exact products, fp32 accumulation
+        ref = (x.half().double() @ w.double().t()).float()
+        assert rel_l2(out, ref) < 2e-6
+        assert rel_l2(out, (x.double() @ w.double().t()).float()) < 1e-3
 
 
 @pytest.mark.parametrize("M,N,K", [(128, 128, 64), (128, 128, 512), (1, 128, 64), (200, 384, 512), (33, 1000, 256),
@@ -65,11 +72,11 @@ def test_gemm_tcgen05(lib, M, N, K):
 
 def test_gemv_rejects_bad_shapes(lib):
     from llm_sharding_b200 import _lib
-    x = torch.zeros(8, 64, device="cuda")
+    x = torch.zeros(16, 64, device="cuda")
     w = torch.zeros(8, 64, device="cuda", dtype=torch.bfloat16)
     o = torch.zeros(8, 8, device="cuda")
     with pytest.raises(ValueError):
-        _lib.check(lib.b200_gemv_bf16(x.data_ptr(), w.data_ptr(), 5, 8, 64, o.data_ptr(), _st()))
+        _lib.check(lib.b200_gemv_f16(x.data_ptr(), w.data_ptr(), 9, 8, 64, o.data_ptr(), _st()))
     with pytest.raises(ValueError):
         _lib.check(lib.b200_gemm_bf16(w.data_ptr(), w.data_ptr(), 8, 8, 60, o.data_ptr(), _st()))
 
