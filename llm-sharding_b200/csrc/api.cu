@@ -331,13 +331,16 @@ static int check_call(b200_shard_t* s, b200_kv_t* kv, const int32_t* h_slots, co
     for (auto& l : s->layers)
         if (!l.set) return fail(B200_ESTATE, "[ERROR] a layer of this shard has no weights loaded");
     int need_total = 0;
-    for (int b = 0; b < B; ++b) {
+    for (int b = 0; b < B; ++b) {  // argument errors first (ValueError), capacity second (out-of-memory)
         const int slot = h_slots[b];
         if (slot < 0 || slot >= kv->dev.max_slots) return fail(B200_EINVAL, "[ERROR] kv slot %d out of range", slot);
         for (int c = 0; c < b; ++c)
             if (h_slots[c] == slot) return fail(B200_EINVAL, "[ERROR] kv slot %d used by two rows of one batch", slot);
         if (kv->h_len[slot] != kv->h_len[h_slots[0]])
             return fail(B200_EINVAL, "[ERROR] rows of one batch must have equal cached lengths");
+    }
+    for (int b = 0; b < B; ++b) {
+        const int slot = h_slots[b];
         const int need = (kv->h_len[slot] + S + kv->dev.page_size - 1) / kv->dev.page_size;
         if (need > kv->dev.max_pages_per_slot) return fail(B200_ENOMEM, "[ERROR] KV slot capacity exceeded");
         need_total += need > kv->h_pages[slot] ? need - kv->h_pages[slot] : 0;

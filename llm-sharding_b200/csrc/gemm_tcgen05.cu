@@ -12,6 +12,7 @@
 #include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "common.cuh"
@@ -95,6 +96,132 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
+// One accumulator row per thread: `trow` = TMEM address of this thread's lane at the first column of a 128-column
+// logical tile, `n_blk` = index of that tile along N (one head for QKV_ROPE, one gate/up pair block for SWIGLU).
+template <int EPI>
+__device__ __forceinline__ void gemm_epilogue(const GemmParams& p, const uint32_t trow, const int row, const int n_blk) {
+    const bool row_ok = row < p.M;
+    if (EPI == GEMM_SWIGLU_BF16) {
+        __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(p.out);
+        const int No = p.N / 2;
+#pragma unroll 1
+        for (int c = 0; c < 2; ++c) {
+            uint32_t g[32], u[32];
+            tmem_ld32(trow + c * 32, g);
+            tmem_ld32(trow + 64 + c * 32, u);
+            const int col0 = n_blk * 64 + c * 32;
+            if (row_ok) {
+#pragma unroll
+                for (int v = 0; v < 4; ++v) {
+                    if (col0 + v * 8 < No) {
+                        uint32_t w[4];
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            const float g0 = __uint_as_float(g[v * 8 + 2 * e]), g1 = __uint_as_float(g[v * 8 + 2 * e + 1]);
+                            const float u0 = __uint_as_float(u[v * 8 + 2 * e]), u1 = __uint_as_float(u[v * 8 + 2 * e + 1]);
+                            w[e] = p.out_f16 ? pack_f16(silu(g0) * u0, silu(g1) * u1) : pack_bf16(silu(g0) * u0, silu(g1) * u1);
+                        }
+                        *reinterpret_cast<uint4*>(out + (size_t)row * No + col0 + v * 8) = make_uint4(w[0], w[1], w[2], w[3]);
+                    }
+                }
+            }
+        }
+    } else if (EPI == GEMM_QKV_ROPE) {
+        // one 128-column tile = one head: apply_rotary_pos_emb (modeling_llama.py:146-168) in fp32 on the
+        // accumulator, then q -> (hi, lo) bf16 pair, k / v -> bf16 straight into the KV pages
+        // (DynamicCache.update, cache_utils.py:102-121, as a paged write).  A single rounding per value.
+        const int head = n_blk;
+        const bool is_q = head < p.n_heads, is_k = !is_q && head < p.n_heads + p.n_kv;
+#pragma unroll 1
+        for (int c = 0; c < 2; ++c) {
+            uint32_t a[32], b[32];
+            tmem_ld32(trow + c * 32, a);
+            tmem_ld32(trow + 64 + c * 32, b);
+            if (row_ok) {
+                const int j0 = c * 32;
+                float lo[32], hi[32];
+                if (is_q || is_k) {
+                    const float4* cs4 = reinterpret_cast<const float4*>(p.cos + (size_t)row * kHalfDim + j0);
+                    const float4* sn4 = reinterpret_cast<const float4*>(p.sin + (size_t)row * kHalfDim + j0);
+#pragma unroll
+                    for (int v = 0; v < 8; ++v) {
+                        const float4 cs = cs4[v], sn = sn4[v];
+                        const float cc[4] = {cs.x, cs.y, cs.z, cs.w}, ss[4] = {sn.x, sn.y, sn.z, sn.w};
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            const float x = __uint_as_float(a[v * 4 + e]), y = __uint_as_float(b[v * 4 + e]);
+                            lo[v * 4 + e] = x * cc[e] - y * ss[e];
+                            hi[v * 4 + e] = y * cc[e] + x * ss[e];
+                        }
+                    }
+                } else {
+#pragma unroll
+                    for (int e = 0; e < 32; ++e) { lo[e] = __uint_as_float(a[e]); hi[e] = __uint_as_float(b[e]); }
+                }
+                __nv_bfloat16* dst;
+                if (is_q) dst = p.q_hi + ((size_t)row * p.n_heads + head) * kHeadDim + j0;
+                else if (is_k) dst = p.k_pool + p.kv_off[row] + (int64_t)(head - p.n_heads) * p.head_stride + j0;
+                else dst = p.v_pool + p.kv_off[row] + (int64_t)(head - p.n_heads - p.n_kv) * p.head_stride + j0;
+#pragma unroll
+                for (int v = 0; v < 4; ++v) {
+                    *reinterpret_cast<uint4*>(dst + v * 8) = make_uint4(pack_bf16(lo[v * 8 + 0], lo[v * 8 + 1]), pack_bf16(lo[v * 8 + 2], lo[v * 8 + 3]),
+                                                                        pack_bf16(lo[v * 8 + 4], lo[v * 8 + 5]), pack_bf16(lo[v * 8 + 6], lo[v * 8 + 7]));
+                    *reinterpret_cast<uint4*>(dst + kHalfDim + v * 8) = make_uint4(pack_bf16(hi[v * 8 + 0], hi[v * 8 + 1]), pack_bf16(hi[v * 8 + 2], hi[v * 8 + 3]),
+                                                                                   pack_bf16(hi[v * 8 + 4], hi[v * 8 + 5]), pack_bf16(hi[v * 8 + 6], hi[v * 8 + 7]));
+                }
+                if (is_q) {  // residual of the bf16 rounding, so that attention sees q with ~16 mantissa bits
+                    __nv_bfloat16* dlo = p.q_lo + ((size_t)row * p.n_heads + head) * kHeadDim + j0;
+#pragma unroll
+                    for (int e = 0; e < 32; ++e) {
+                        lo[e] -= __bfloat162float(__float2bfloat16_rn(lo[e]));
+                        hi[e] -= __bfloat162float(__float2bfloat16_rn(hi[e]));
+                    }
+#pragma unroll
+                    for (int v = 0; v < 4; ++v) {
+                        *reinterpret_cast<uint4*>(dlo + v * 8) = make_uint4(pack_bf16(lo[v * 8 + 0], lo[v * 8 + 1]), pack_bf16(lo[v * 8 + 2], lo[v * 8 + 3]),
+                                                                            pack_bf16(lo[v * 8 + 4], lo[v * 8 + 5]), pack_bf16(lo[v * 8 + 6], lo[v * 8 + 7]));
+                        *reinterpret_cast<uint4*>(dlo + kHalfDim + v * 8) = make_uint4(pack_bf16(hi[v * 8 + 0], hi[v * 8 + 1]), pack_bf16(hi[v * 8 + 2], hi[v * 8 + 3]),
+                                                                                       pack_bf16(hi[v * 8 + 4], hi[v * 8 + 5]), pack_bf16(hi[v * 8 + 6], hi[v * 8 + 7]));
+                    }
+                }
+            }
+        }
+    } else {
+#pragma unroll 1
+        for (int c = 0; c < kBlkN / 32; ++c) {
+            uint32_t r[32];
+            tmem_ld32(trow + c * 32, r);
+            const int col0 = n_blk * kBlkN + c * 32;
+            if (row_ok) {
+                if (EPI == GEMM_STORE_BF16) {
+                    __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(p.out) + (size_t)row * p.N + col0;
+#pragma unroll
+                    for (int v = 0; v < 4; ++v)
+                        if (col0 + v * 8 < p.N)
+                            *reinterpret_cast<uint4*>(out + v * 8) = make_uint4(
+                                pack_bf16(__uint_as_float(r[v * 8 + 0]), __uint_as_float(r[v * 8 + 1])),
+                                pack_bf16(__uint_as_float(r[v * 8 + 2]), __uint_as_float(r[v * 8 + 3])),
+                                pack_bf16(__uint_as_float(r[v * 8 + 4]), __uint_as_float(r[v * 8 + 5])),
+                                pack_bf16(__uint_as_float(r[v * 8 + 6]), __uint_as_float(r[v * 8 + 7])));
+                } else {
+                    float* out = reinterpret_cast<float*>(p.out) + (size_t)row * p.N + col0;
+#pragma unroll
+                    for (int v = 0; v < 8; ++v)
+                        if (col0 + v * 4 < p.N) {
+                            float4 acc = make_float4(__uint_as_float(r[v * 4 + 0]), __uint_as_float(r[v * 4 + 1]),
+                                                     __uint_as_float(r[v * 4 + 2]), __uint_as_float(r[v * 4 + 3]));
+                            if (EPI == GEMM_RESID_F32) {
+                                const float4 o = *reinterpret_cast<const float4*>(out + v * 4);
+                                acc.x += o.x; acc.y += o.y; acc.z += o.z; acc.w += o.w;
+                            }
+                            *reinterpret_cast<float4*>(out + v * 4) = acc;
+                        }
+                }
+            }
+        }
+    }
+}
+
 template <int EPI>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
@@ -161,132 +288,134 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
         const int quad = warp & 3;
         const int row = m_blk * kBlkM + quad * 32 + lane;
         const uint32_t trow = tmem_base + ((uint32_t)(quad * 32) << 16);
-        const bool row_ok = row < p.M;
-        if (EPI == GEMM_SWIGLU_BF16) {
-            __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(p.out);
-            const int No = p.N / 2;
-#pragma unroll 1
-            for (int c = 0; c < 2; ++c) {
-                uint32_t g[32], u[32];
-                tmem_ld32(trow + c * 32, g);
-                tmem_ld32(trow + 64 + c * 32, u);
-                const int col0 = n_blk * 64 + c * 32;
-                if (row_ok) {
-#pragma unroll
-                    for (int v = 0; v < 4; ++v) {
-                        if (col0 + v * 8 < No) {
-                            uint32_t w[4];
-#pragma unroll
-                            for (int e = 0; e < 4; ++e) {
-                                const float g0 = __uint_as_float(g[v * 8 + 2 * e]), g1 = __uint_as_float(g[v * 8 + 2 * e + 1]);
-                                const float u0 = __uint_as_float(u[v * 8 + 2 * e]), u1 = __uint_as_float(u[v * 8 + 2 * e + 1]);
-                                w[e] = p.out_f16 ? pack_f16(silu(g0) * u0, silu(g1) * u1) : pack_bf16(silu(g0) * u0, silu(g1) * u1);
-                            }
-                            *reinterpret_cast<uint4*>(out + (size_t)row * No + col0 + v * 8) = make_uint4(w[0], w[1], w[2], w[3]);
-                        }
-                    }
-                }
-            }
-        } else if (EPI == GEMM_QKV_ROPE) {
-            // one 128-column tile = one head: apply_rotary_pos_emb (modeling_llama.py:146-168) in fp32 on the
-            // accumulator, then q -> (hi, lo) bf16 pair, k / v -> bf16 straight into the KV pages
-            // (DynamicCache.update, cache_utils.py:102-121, as a paged write).  A single rounding per value.
-            const int head = n_blk;
-            const bool is_q = head < p.n_heads, is_k = !is_q && head < p.n_heads + p.n_kv;
-#pragma unroll 1
-            for (int c = 0; c < 2; ++c) {
-                uint32_t a[32], b[32];
-                tmem_ld32(trow + c * 32, a);
-                tmem_ld32(trow + 64 + c * 32, b);
-                if (row_ok) {
-                    const int j0 = c * 32;
-                    float lo[32], hi[32];
-                    if (is_q || is_k) {
-                        const float4* cs4 = reinterpret_cast<const float4*>(p.cos + (size_t)row * kHalfDim + j0);
-                        const float4* sn4 = reinterpret_cast<const float4*>(p.sin + (size_t)row * kHalfDim + j0);
-#pragma unroll
-                        for (int v = 0; v < 8; ++v) {
-                            const float4 cs = cs4[v], sn = sn4[v];
-                            const float cc[4] = {cs.x, cs.y, cs.z, cs.w}, ss[4] = {sn.x, sn.y, sn.z, sn.w};
-#pragma unroll
-                            for (int e = 0; e < 4; ++e) {
-                                const float x = __uint_as_float(a[v * 4 + e]), y = __uint_as_float(b[v * 4 + e]);
-                                lo[v * 4 + e] = x * cc[e] - y * ss[e];
-                                hi[v * 4 + e] = y * cc[e] + x * ss[e];
-                            }
-                        }
-                    } else {
-#pragma unroll
-                        for (int e = 0; e < 32; ++e) { lo[e] = __uint_as_float(a[e]); hi[e] = __uint_as_float(b[e]); }
-                    }
-                    __nv_bfloat16* dst;
-                    if (is_q) dst = p.q_hi + ((size_t)row * p.n_heads + head) * kHeadDim + j0;
-                    else if (is_k) dst = p.k_pool + p.kv_off[row] + (int64_t)(head - p.n_heads) * p.head_stride + j0;
-                    else dst = p.v_pool + p.kv_off[row] + (int64_t)(head - p.n_heads - p.n_kv) * p.head_stride + j0;
-#pragma unroll
-                    for (int v = 0; v < 4; ++v) {
-                        *reinterpret_cast<uint4*>(dst + v * 8) = make_uint4(pack_bf16(lo[v * 8 + 0], lo[v * 8 + 1]), pack_bf16(lo[v * 8 + 2], lo[v * 8 + 3]),
-                                                                            pack_bf16(lo[v * 8 + 4], lo[v * 8 + 5]), pack_bf16(lo[v * 8 + 6], lo[v * 8 + 7]));
-                        *reinterpret_cast<uint4*>(dst + kHalfDim + v * 8) = make_uint4(pack_bf16(hi[v * 8 + 0], hi[v * 8 + 1]), pack_bf16(hi[v * 8 + 2], hi[v * 8 + 3]),
-                                                                                       pack_bf16(hi[v * 8 + 4], hi[v * 8 + 5]), pack_bf16(hi[v * 8 + 6], hi[v * 8 + 7]));
-                    }
-                    if (is_q) {  // residual of the bf16 rounding, so that attention sees q with ~16 mantissa bits
-                        __nv_bfloat16* dlo = p.q_lo + ((size_t)row * p.n_heads + head) * kHeadDim + j0;
-#pragma unroll
-                        for (int e = 0; e < 32; ++e) {
-                            lo[e] -= __bfloat162float(__float2bfloat16_rn(lo[e]));
-                            hi[e] -= __bfloat162float(__float2bfloat16_rn(hi[e]));
-                        }
-#pragma unroll
-                        for (int v = 0; v < 4; ++v) {
-                            *reinterpret_cast<uint4*>(dlo + v * 8) = make_uint4(pack_bf16(lo[v * 8 + 0], lo[v * 8 + 1]), pack_bf16(lo[v * 8 + 2], lo[v * 8 + 3]),
-                                                                                pack_bf16(lo[v * 8 + 4], lo[v * 8 + 5]), pack_bf16(lo[v * 8 + 6], lo[v * 8 + 7]));
-                            *reinterpret_cast<uint4*>(dlo + kHalfDim + v * 8) = make_uint4(pack_bf16(hi[v * 8 + 0], hi[v * 8 + 1]), pack_bf16(hi[v * 8 + 2], hi[v * 8 + 3]),
-                                                                                           pack_bf16(hi[v * 8 + 4], hi[v * 8 + 5]), pack_bf16(hi[v * 8 + 6], hi[v * 8 + 7]));
-                        }
-                    }
-                }
-            }
-        } else {
-#pragma unroll 1
-            for (int c = 0; c < kBlkN / 32; ++c) {
-                uint32_t r[32];
-                tmem_ld32(trow + c * 32, r);
-                const int col0 = n_blk * kBlkN + c * 32;
-                if (row_ok) {
-                    if (EPI == GEMM_STORE_BF16) {
-                        __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(p.out) + (size_t)row * p.N + col0;
-#pragma unroll
-                        for (int v = 0; v < 4; ++v)
-                            if (col0 + v * 8 < p.N)
-                                *reinterpret_cast<uint4*>(out + v * 8) = make_uint4(
-                                    pack_bf16(__uint_as_float(r[v * 8 + 0]), __uint_as_float(r[v * 8 + 1])),
-                                    pack_bf16(__uint_as_float(r[v * 8 + 2]), __uint_as_float(r[v * 8 + 3])),
-                                    pack_bf16(__uint_as_float(r[v * 8 + 4]), __uint_as_float(r[v * 8 + 5])),
-                                    pack_bf16(__uint_as_float(r[v * 8 + 6]), __uint_as_float(r[v * 8 + 7])));
-                    } else {
-                        float* out = reinterpret_cast<float*>(p.out) + (size_t)row * p.N + col0;
-#pragma unroll
-                        for (int v = 0; v < 8; ++v)
-                            if (col0 + v * 4 < p.N) {
-                                float4 acc = make_float4(__uint_as_float(r[v * 4 + 0]), __uint_as_float(r[v * 4 + 1]),
-                                                         __uint_as_float(r[v * 4 + 2]), __uint_as_float(r[v * 4 + 3]));
-                                if (EPI == GEMM_RESID_F32) {
-                                    const float4 o = *reinterpret_cast<const float4*>(out + v * 4);
-                                    acc.x += o.x; acc.y += o.y; acc.z += o.z; acc.w += o.w;
-                                }
-                                *reinterpret_cast<float4*>(out + v * 4) = acc;
-                            }
-                    }
-                }
-            }
-        }
+        gemm_epilogue<EPI>(p, trow, row, n_blk);
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     }
     __syncthreads();
     if (warp == 1) {
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(kTmemCols) : "memory");
+    }
+}
+
+// ================================================================================================================
+// CTA-pair variant for M > 128: one 256 x 256 output tile per pair of CTAs (cluster of 2 on one TPC),
+// tcgen05.mma.cta_group::2 with UMMA M = 256.  Each CTA stages its own 128 rows of A and only HALF of the 256-row B
+// tile (16 KB + 16 KB per k-step for 128 x 256 outputs per CTA): twice the arithmetic intensity of the single-CTA
+// kernel above, which ncu shows bound by L2 -> shared-memory traffic (profiles/prefill_gemm_r1_summary.md).
+// Protocol: both CTAs run a TMA producer; every TMA signals the LEADER's (cluster rank 0) full barrier; the leader's
+// single MMA thread issues for the pair and commits with a multicast arrive onto both CTAs' empty / tmem_full
+// barriers; each CTA drains its own 128 TMEM lanes x 256 columns through the shared epilogue (two 128-column halves).
+constexpr int kBlkN2 = 256;
+constexpr uint32_t kStageBytesB2 = (kBlkN2 / 2) * kBlkK * 2;         // this CTA's half of the B tile
+constexpr uint32_t kStageBytes2 = kStageBytesA + kStageBytesB2;      // 32 KB per CTA per stage
+constexpr uint32_t kTmemCols2 = 256;
+constexpr uint32_t kPeerMask = 0xFEFFFFFFu;                          // shared::cluster address of the same offset in CTA rank 0
+constexpr uint32_t kIdescBase2 = (1u << 4) | ((uint32_t)(kBlkN2 >> 3) << 17) | ((uint32_t)(256 >> 4) << 24);
+
+__device__ __forceinline__ void tma_load_2d_pair(const CUtensorMap* map, uint32_t leader_bar, uint32_t dst, int x, int y) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(dst), "l"(map), "r"(leader_bar), "r"(x), "r"(y) : "memory");
+}
+__device__ __forceinline__ void umma_f16_pair(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accum) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(accum) : "memory");
+}
+__device__ __forceinline__ void umma_commit_pair(uint32_t bar) {  // arrives on `bar` in BOTH CTAs of the pair
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(bar), "h"((uint16_t)3) : "memory");
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
+template <int EPI>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
+gemm_pair_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
+                         const GemmParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t raw = s_u32(smem_raw);
+    const uint32_t base = (raw + 1023u) & ~1023u;
+    uint8_t* gen_base = smem_raw + (base - raw);
+    const uint32_t bars = base + kStages * kStageBytes2;
+    const uint32_t full0 = bars, empty0 = bars + 8 * kStages, tmem_full = bars + 16 * kStages;
+    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(gen_base + kStages * kStageBytes2 + 16 * kStages + 8);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    uint32_t cta_rank;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(cta_rank));
+    const bool leader = cta_rank == 0;
+    const int m_pair = blockIdx.x >> 1, n_blk = blockIdx.y;
+    const int m_row0 = m_pair * 256 + (int)cta_rank * kBlkM;            // this CTA's 128 rows of A / of the output
+    const int n_row0 = n_blk * kBlkN2 + (int)cta_rank * (kBlkN2 / 2);   // this CTA's half of the B tile
+    const int num_k = (p.K + kBlkK - 1) / kBlkK;
+    const uint32_t idesc = kIdescBase2 | (p.ab_f16 ? 0u : ((1u << 7) | (1u << 10)));
+
+    if (warp == 0 && lane == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_a) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_b) : "memory");
+        for (int i = 0; i < kStages; ++i) { mbar_init(full0 + 8 * i, 1); mbar_init(empty0 + 8 * i, 1); }
+        mbar_init(tmem_full, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {  // the same warp of both CTAs allocates for the pair
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(s_u32((const void*)tmem_slot)), "n"(kTmemCols2) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    cluster_sync_all();  // barriers of both CTAs are initialised before anybody signals across the pair
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {  // ===== TMA producer (both CTAs): own A rows + own half of B, completion counted on the leader
+            for (int kb = 0; kb < num_k; ++kb) {
+                const int st = kb % kStages;
+                const uint32_t ph = (uint32_t)(kb / kStages) & 1u;
+                mbar_wait(empty0 + 8 * st, ph ^ 1u);
+                if (leader) mbar_expect_tx(full0 + 8 * st, 2 * kStageBytes2);
+                const uint32_t sa = base + st * kStageBytes2, sb = sa + kStageBytesA;
+                const uint32_t lbar = (full0 + 8 * st) & kPeerMask;
+                tma_load_2d_pair(&tma_a, lbar, sa, kb * kBlkK, m_row0);
+                tma_load_2d_pair(&tma_b, lbar, sb, kb * kBlkK, n_row0);
+            }
+        }
+    } else if (warp == 1) {
+        if (leader && lane == 0) {  // ===== MMA issuer: one thread for the pair
+            for (int kb = 0; kb < num_k; ++kb) {
+                const int st = kb % kStages;
+                const uint32_t ph = (uint32_t)(kb / kStages) & 1u;
+                mbar_wait(full0 + 8 * st, ph);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint32_t sa = base + st * kStageBytes2, sb = sa + kStageBytesA;
+#pragma unroll
+                for (int k = 0; k < kBlkK / 16; ++k)
+                    umma_f16_pair(tmem_base, umma_desc(sa + k * 32), umma_desc(sb + k * 32), idesc, (kb > 0 || k > 0) ? 1u : 0u);
+                umma_commit_pair(empty0 + 8 * st);
+            }
+            umma_commit_pair(tmem_full);
+        }
+    } else {  // ===== epilogue (both CTAs): own 128 lanes, 256 columns = two logical 128-column tiles
+        mbar_wait(tmem_full, 0);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const int quad = warp & 3;
+        const int row = m_row0 + quad * 32 + lane;
+        const uint32_t trow = tmem_base + ((uint32_t)(quad * 32) << 16);
+#pragma unroll 1
+        for (int sub = 0; sub < 2; ++sub)
+            if ((n_blk * 2 + sub) * kBlkN < p.N) gemm_epilogue<EPI>(p, trow + sub * kBlkN, row, n_blk * 2 + sub);
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    }
+    __syncthreads();
+    cluster_sync_all();  // neither CTA may free TMEM / leave while the other still reads its shared memory or TMEM
+    if (warp == 1) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(kTmemCols2) : "memory");
     }
 }
 
@@ -339,6 +468,30 @@ int launch_gemm(const GemmParams& p, cudaStream_t st) {
     CUtensorMap ma, mb;
     if (make_map(&ma, p.A, p.M, p.K, kBlkM) != 0) return -1;
     if (make_map(&mb, p.W, p.N, p.K, kBlkN) != 0) return -1;
+    static int pair_mode = -1;
+    if (pair_mode < 0) {
+        const char* e = getenv("B200SHARD_GEMM_PAIR");
+        pair_mode = (e != nullptr && e[0] == '0') ? 0 : 1;
+    }
+    if (pair_mode == 1 && p.M > kBlkM) {  // CTA pairs: 256 x 256 tiles, half the L2 -> shared-memory traffic per flop
+        dim3 grid2(2 * ((p.M + 255) / 256), (p.N + kBlkN2 - 1) / kBlkN2);
+        const size_t smem2 = 1024 + (size_t)kStages * kStageBytes2 + 256;
+#define B200_GEMM2_LAUNCH(E)                                                                                \
+    {                                                                                                       \
+        auto kfn = gemm_pair_tcgen05_kernel<E>;                                                             \
+        cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);                 \
+        kfn<<<grid2, kGemmThreads, smem2, st>>>(ma, mb, p);                                                 \
+    }
+        switch (p.epi) {
+            case GEMM_STORE_BF16: B200_GEMM2_LAUNCH(GEMM_STORE_BF16) break;
+            case GEMM_RESID_F32: B200_GEMM2_LAUNCH(GEMM_RESID_F32) break;
+            case GEMM_SWIGLU_BF16: B200_GEMM2_LAUNCH(GEMM_SWIGLU_BF16) break;
+            case GEMM_QKV_ROPE: B200_GEMM2_LAUNCH(GEMM_QKV_ROPE) break;
+            default: B200_GEMM2_LAUNCH(GEMM_STORE_F32) break;
+        }
+#undef B200_GEMM2_LAUNCH
+        return 0;
+    }
     dim3 grid((p.N + kBlkN - 1) / kBlkN, (p.M + kBlkM - 1) / kBlkM);
 #define B200_GEMM_LAUNCH(E)                                                                                 \
     {                                                                                                       \

@@ -251,3 +251,25 @@ def test_node_controller_loop_over_zeromq(tmp_root):
             c.node_worker.past_key_value = None
             c.node_worker.shard.engine.close()
         s0.close(); s1.close()
+
+
+def test_node_profiler_runs_on_the_b200_worker(tmp_root):
+    """the reference's acceptance harness (NodeProfiler) on this repo's worker — latency sweeps with
+    its timing protocol, its latency fits, capacity probe and the in-process four-node ring."""
+    from gpu_utils import shard_dir
+    from llm_sharding_b200.node_profiler import NodeProfiler
+    z, meta = load_golden("tiny_b1")
+    prof = NodeProfiler(shard_dir(tmp_root, meta["preset"], meta["seed"]), device="cuda:0", dtype=torch.bfloat16)
+    prof.PROFILE_PREFILL_INPUT_TOKEN_LENGTHS = [8, 16, 32, 64]
+    prof.PROFILE_DECODE_OUTPUT_TOKEN_LENGTHS = [8, 16]
+    prof.PROFILE_REPEAT_NUM = 2
+    assert prof.profile_max_layer_num() == 4
+    r = prof.profile_compute_capability(max_layer_num=2)
+    assert r["loaded_layer_num"] == 2 and len(r["prefill"]["latencies_s"]) == 4 and len(r["decode"]["cumulative_latencies_s"]) == 16
+    assert all(t > 0 for t in r["prefill"]["latencies_s"])
+    assert all(b > a for a, b in zip(r["decode"]["cumulative_latencies_s"], r["decode"]["cumulative_latencies_s"][1:]))
+    assert r["decode"]["fit"]["linear"]["r_squared"] > 0.9       # decode latency is linear in the token count
+    assert prof.profile_cold_start_latency(2)["cold_start_s"] > 0
+    # the four-node ring reproduces the reference chain's tokens for the golden prompt
+    toks = prof.go_through_every_shards(meta["new_tokens"], splits=[(0, 1), (1, 2), (2, 3), (3, 4)], input_ids=torch.from_numpy(z["prompt"]))
+    assert toks[:, 0].tolist() == z["tokens"][:, 0].tolist()

@@ -107,3 +107,17 @@ def test_shard_layout_matches_model_sharder_keys(tmp_path):
     from llm_sharding_b200.engine import LAYER_KEYS
     assert tuple(st) == LAYER_KEYS == synth.LAYER_KEYS
     assert st["mlp.down_proj.weight"].shape == (cfg.hidden_size, cfg.intermediate_size)
+
+
+def test_profiler_latency_fit_recovers_models():
+    from llm_sharding_b200.node_profiler import NodeProfiler
+    s = [8, 16, 32, 64, 128, 256, 512]
+    fit = NodeProfiler._fit_latency_models(s, [2e-6 * x * x + 3e-4 * x + 0.01 for x in s])
+    a, b, c = fit["quadratic"]["coefficients"]
+    assert abs(a - 2e-6) < 1e-10 and abs(b - 3e-4) < 1e-8 and abs(c - 0.01) < 1e-6
+    assert fit["quadratic"]["rmse"] < 1e-9 and fit["quadratic"]["r_squared"] > 0.999999
+    assert fit["linear"]["r_squared"] < fit["quadratic"]["r_squared"]
+    with pytest.raises(ValueError):
+        NodeProfiler._fit_latency_models([1, 2], [1.0, 2.0])
+    with pytest.raises(ValueError):
+        NodeProfiler._fit_latency_models([1, 2, 3], [1.0, 2.0])
