@@ -309,7 +309,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
 constexpr int kBlkN2 = 256;
 constexpr uint32_t kStageBytesB2 = (kBlkN2 / 2) * kBlkK * 2;         // this CTA's half of the B tile
 constexpr uint32_t kStageBytes2 = kStageBytesA + kStageBytesB2;      // 32 KB per CTA per stage
-constexpr uint32_t kTmemCols2 = 256;
+
 constexpr uint32_t kPeerMask = 0xFEFFFFFFu;                          // shared::cluster address of the same offset in CTA rank 0
 constexpr uint32_t kIdescBase2 = (1u << 4) | ((uint32_t)(kBlkN2 >> 3) << 17) | ((uint32_t)(256 >> 4) << 24);
 
@@ -333,6 +333,14 @@ __device__ __forceinline__ void cluster_sync_all() {
     asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
 
+// Remote arrive on the barrier at the same shared-memory offset in the leader CTA (cluster rank 0).
+__device__ __forceinline__ void mbar_arrive_leader(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(bar & kPeerMask) : "memory");
+}
+
+// Persistent: one CTA pair per SM pair walks over the 256 x 256 tiles (m fastest, so that concurrently running pairs
+// share the weight tile in L2).  The accumulator is double buffered in tensor memory (2 x 256 columns): the epilogue of
+// tile i (TMEM -> registers -> global, with the fused RoPE / SwiGLU / residual work) overlaps the MMAs of tile i+1.
 template <int EPI>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
 gemm_pair_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
@@ -342,16 +350,16 @@ gemm_pair_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
     const uint32_t base = (raw + 1023u) & ~1023u;
     uint8_t* gen_base = smem_raw + (base - raw);
     const uint32_t bars = base + kStages * kStageBytes2;
-    const uint32_t full0 = bars, empty0 = bars + 8 * kStages, tmem_full = bars + 16 * kStages;
-    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(gen_base + kStages * kStageBytes2 + 16 * kStages + 8);
+    const uint32_t full0 = bars, empty0 = bars + 8 * kStages, tfull0 = bars + 16 * kStages, tempty0 = tfull0 + 16;
+    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(gen_base + kStages * kStageBytes2 + 16 * kStages + 32);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     uint32_t cta_rank;
     asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(cta_rank));
     const bool leader = cta_rank == 0;
-    const int m_pair = blockIdx.x >> 1, n_blk = blockIdx.y;
-    const int m_row0 = m_pair * 256 + (int)cta_rank * kBlkM;            // this CTA's 128 rows of A / of the output
-    const int n_row0 = n_blk * kBlkN2 + (int)cta_rank * (kBlkN2 / 2);   // this CTA's half of the B tile
+    const int pair_id = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
+    const int n_m = (p.M + 255) / 256, n_n = (p.N + kBlkN2 - 1) / kBlkN2;
+    const int n_tiles = n_m * n_n;
     const int num_k = (p.K + kBlkK - 1) / kBlkK;
     const uint32_t idesc = kIdescBase2 | (p.ab_f16 ? 0u : ((1u << 7) | (1u << 10)));
 
@@ -359,11 +367,11 @@ gemm_pair_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
         asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_a) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_b) : "memory");
         for (int i = 0; i < kStages; ++i) { mbar_init(full0 + 8 * i, 1); mbar_init(empty0 + 8 * i, 1); }
-        mbar_init(tmem_full, 1);
+        for (int i = 0; i < 2; ++i) { mbar_init(tfull0 + 8 * i, 1); mbar_init(tempty0 + 8 * i, 8); }  // 4 epilogue warps x 2 CTAs
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == 1) {  // the same warp of both CTAs allocates for the pair
-        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(s_u32((const void*)tmem_slot)), "n"(kTmemCols2) : "memory");
+    if (warp == 1) {  // the same warp of both CTAs allocates for the pair: all 512 columns (two accumulators)
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(s_u32((const void*)tmem_slot)), "n"(512) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -374,48 +382,65 @@ gemm_pair_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
 
     if (warp == 0) {
         if (lane == 0) {  // ===== TMA producer (both CTAs): own A rows + own half of B, completion counted on the leader
-            for (int kb = 0; kb < num_k; ++kb) {
-                const int st = kb % kStages;
-                const uint32_t ph = (uint32_t)(kb / kStages) & 1u;
-                mbar_wait(empty0 + 8 * st, ph ^ 1u);
-                if (leader) mbar_expect_tx(full0 + 8 * st, 2 * kStageBytes2);
-                const uint32_t sa = base + st * kStageBytes2, sb = sa + kStageBytesA;
-                const uint32_t lbar = (full0 + 8 * st) & kPeerMask;
-                tma_load_2d_pair(&tma_a, lbar, sa, kb * kBlkK, m_row0);
-                tma_load_2d_pair(&tma_b, lbar, sb, kb * kBlkK, n_row0);
+            uint32_t it = 0;
+            for (int t = pair_id; t < n_tiles; t += n_pairs) {
+                const int m_row0 = (t % n_m) * 256 + (int)cta_rank * kBlkM;
+                const int n_row0 = (t / n_m) * kBlkN2 + (int)cta_rank * (kBlkN2 / 2);
+                for (int kb = 0; kb < num_k; ++kb, ++it) {
+                    const uint32_t st = it % kStages, ph = (it / kStages) & 1u;
+                    mbar_wait(empty0 + 8 * st, ph ^ 1u);
+                    if (leader) mbar_expect_tx(full0 + 8 * st, 2 * kStageBytes2);
+                    const uint32_t sa = base + st * kStageBytes2, sb = sa + kStageBytesA;
+                    const uint32_t lbar = (full0 + 8 * st) & kPeerMask;
+                    tma_load_2d_pair(&tma_a, lbar, sa, kb * kBlkK, m_row0);
+                    tma_load_2d_pair(&tma_b, lbar, sb, kb * kBlkK, n_row0);
+                }
             }
         }
     } else if (warp == 1) {
         if (leader && lane == 0) {  // ===== MMA issuer: one thread for the pair
-            for (int kb = 0; kb < num_k; ++kb) {
-                const int st = kb % kStages;
-                const uint32_t ph = (uint32_t)(kb / kStages) & 1u;
-                mbar_wait(full0 + 8 * st, ph);
+            uint32_t it = 0, ti = 0;
+            for (int t = pair_id; t < n_tiles; t += n_pairs, ++ti) {
+                const uint32_t buf = ti & 1u;
+                mbar_wait(tempty0 + 8 * buf, ((ti >> 1) & 1u) ^ 1u);  // both CTAs' epilogues have drained this accumulator
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                const uint32_t sa = base + st * kStageBytes2, sb = sa + kStageBytesA;
+                const uint32_t acc = tmem_base + buf * kBlkN2;
+                for (int kb = 0; kb < num_k; ++kb, ++it) {
+                    const uint32_t st = it % kStages, ph = (it / kStages) & 1u;
+                    mbar_wait(full0 + 8 * st, ph);
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    const uint32_t sa = base + st * kStageBytes2, sb = sa + kStageBytesA;
 #pragma unroll
-                for (int k = 0; k < kBlkK / 16; ++k)
-                    umma_f16_pair(tmem_base, umma_desc(sa + k * 32), umma_desc(sb + k * 32), idesc, (kb > 0 || k > 0) ? 1u : 0u);
-                umma_commit_pair(empty0 + 8 * st);
+                    for (int k = 0; k < kBlkK / 16; ++k)
+                        umma_f16_pair(acc, umma_desc(sa + k * 32), umma_desc(sb + k * 32), idesc, (kb > 0 || k > 0) ? 1u : 0u);
+                    umma_commit_pair(empty0 + 8 * st);
+                }
+                umma_commit_pair(tfull0 + 8 * buf);
             }
-            umma_commit_pair(tmem_full);
         }
     } else {  // ===== epilogue (both CTAs): own 128 lanes, 256 columns = two logical 128-column tiles
-        mbar_wait(tmem_full, 0);
-        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         const int quad = warp & 3;
-        const int row = m_row0 + quad * 32 + lane;
-        const uint32_t trow = tmem_base + ((uint32_t)(quad * 32) << 16);
+        uint32_t ti = 0;
+        for (int t = pair_id; t < n_tiles; t += n_pairs, ++ti) {
+            const uint32_t buf = ti & 1u;
+            const int m_row0 = (t % n_m) * 256 + (int)cta_rank * kBlkM, n_blk = t / n_m;
+            mbar_wait(tfull0 + 8 * buf, (ti >> 1) & 1u);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const int row = m_row0 + quad * 32 + lane;
+            const uint32_t trow = tmem_base + buf * kBlkN2 + ((uint32_t)(quad * 32) << 16);
 #pragma unroll 1
-        for (int sub = 0; sub < 2; ++sub)
-            if ((n_blk * 2 + sub) * kBlkN < p.N) gemm_epilogue<EPI>(p, trow + sub * kBlkN, row, n_blk * 2 + sub);
-        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            for (int sub = 0; sub < 2; ++sub)
+                if ((n_blk * 2 + sub) * kBlkN < p.N) gemm_epilogue<EPI>(p, trow + sub * kBlkN, row, n_blk * 2 + sub);
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) mbar_arrive_leader(tempty0 + 8 * buf);  // this warp no longer reads accumulator `buf`
+        }
     }
     __syncthreads();
     cluster_sync_all();  // neither CTA may free TMEM / leave while the other still reads its shared memory or TMEM
     if (warp == 1) {
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(kTmemCols2) : "memory");
+        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(512) : "memory");
     }
 }
 
@@ -473,8 +498,15 @@ int launch_gemm(const GemmParams& p, cudaStream_t st) {
         const char* e = getenv("B200SHARD_GEMM_PAIR");
         pair_mode = (e != nullptr && e[0] == '0') ? 0 : 1;
     }
-    if (pair_mode == 1 && p.M > kBlkM) {  // CTA pairs: 256 x 256 tiles, half the L2 -> shared-memory traffic per flop
-        dim3 grid2(2 * ((p.M + 255) / 256), (p.N + kBlkN2 - 1) / kBlkN2);
+    // CTA pairs (256 x 256 tiles, half the L2 -> shared-memory traffic per flop) once there are enough tiles to occupy
+    // most SM pairs; small problems keep the finer 128 x 128 tiling (measured: profiles/gemm_bench_r1.md)
+    if (pair_mode == 1 && p.M > kBlkM && (int64_t)((p.M + 255) / 256) * ((p.N + kBlkN2 - 1) / kBlkN2) >= 64) {
+        int n_sms = 148, dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, dev);
+        const int64_t tiles2 = (int64_t)((p.M + 255) / 256) * ((p.N + kBlkN2 - 1) / kBlkN2);
+        const int pairs = (int)(tiles2 < n_sms / 2 ? tiles2 : n_sms / 2);
+        dim3 grid2(2 * pairs);
         const size_t smem2 = 1024 + (size_t)kStages * kStageBytes2 + 256;
 #define B200_GEMM2_LAUNCH(E)                                                                                \
     {                                                                                                       \
