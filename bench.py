@@ -169,7 +169,7 @@ def run_reference(args):
     rank, world, _ = dist_env()
     if rank != 0:
         return
-    base = cpu_decode_baseline(args.steps, max(1, min(args.warmup, 3)), time_budget_s=150.0)
+    base = cpu_decode_baseline(args.steps, max(1, min(args.warmup, 3)), time_budget_s=150.0, prompt_len=PROMPT_LEN)
     line = {
         "impl": "reference", "metric": METRIC, "value": base["value"], "unit": "tok/s", "n_gpus": args.gpus,
         "steps": base["steps_timed"], "warmup": max(1, min(args.warmup, 3)), "ms_per_step": base["ms_per_step"],
@@ -336,7 +336,7 @@ def run_single(args):
     cpu = None
     if not args.no_cpu_baseline:
         try:
-            cpu = cpu_decode_baseline(steps=16, warmup=1, time_budget_s=25.0)
+            cpu = cpu_decode_baseline(steps=16, warmup=1, time_budget_s=25.0, prompt_len=PROMPT_LEN)
             cpu = {k: cpu[k] for k in ("value", "unit", "cores", "kind", "sample")}
         except Exception as e:  # the baseline is reported, never required
             cpu = {"value": None, "unit": "tok/s", "cores": 0, "kind": "port", "sample": f"failed: {e!r}"}
@@ -354,16 +354,19 @@ def run_single(args):
 
 
 def main():
+    global PROMPT_LEN
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=NEW_TOKENS)
     ap.add_argument("--warmup", type=int, default=8)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--prompt-len", type=int, default=PROMPT_LEN, help="prompt tokens per request (default: BASELINE configs[1]'s 512)")
     ap.add_argument("--transport", default="p2p", choices=["p2p", "nccl"], help="hop transport for --gpus > 1")
     ap.add_argument("--streams", type=int, default=0, help="--gpus > 1: request streams in flight (default: one per GPU)")
     ap.add_argument("--rows", type=int, default=1, help="--gpus > 1: batch rows per stream; 8 streams x 4 rows = BASELINE configs[2]'s batch 32")
     args = ap.parse_args()
+    PROMPT_LEN = args.prompt_len
     if args.impl == "reference":
         return run_reference(args)
     if not torch.cuda.is_available():

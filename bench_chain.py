@@ -70,6 +70,8 @@ def run_chain(args, config, metric, ClockSampler, peaks):
     device = torch.device(f"cuda:{local}")
     dist.init_process_group("nccl", device_id=device)
     ctrl = dist.new_group(backend="gloo")
+    global PROMPT_LEN
+    PROMPT_LEN = getattr(args, "prompt_len", PROMPT_LEN)
     K, W = args.steps, max(args.warmup, 3)
     transport = getattr(args, "transport", "p2p")
     cfg = synthetic.LLAMA2_7B
