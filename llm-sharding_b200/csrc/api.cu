@@ -408,7 +408,14 @@ static int enqueue_forward(b200_shard_t* s, b200_kv_t* kv, const SlotList& sl, c
             ap.q = s->qrot; ap.q_lo = s->qrot_lo; ap.out_f16 = 1; ap.k_pool = kp; ap.v_pool = vp; ap.block_table = kv->dev.block_table; ap.call_base = s->tm.call_base;
             ap.slots = sl; ap.B = B; ap.S = S; ap.causal = causal; ap.n_heads = c.n_heads; ap.n_kv = c.n_kv_heads;
             ap.page_size = kv->dev.page_size; ap.max_pages_per_slot = kv->dev.max_pages_per_slot; ap.out = s->attn_b;
-            launch_attn_prefill(ap, st);
+            static int attn_tc = -1;
+            if (attn_tc < 0) { const char* e = getenv("B200SHARD_ATTN_TC"); attn_tc = (e != nullptr && e[0] == '0') ? 0 : 1; }
+            if (attn_tc == 1) {  // tcgen05 + TMA kernel; B200SHARD_ATTN_TC=0 keeps the mma.sync kernel for A/B checks
+                if (launch_attn_prefill_tc(ap, (int64_t)kv->dev.n_pages * c.n_kv_heads * kv->dev.page_size, st) != 0)
+                    return fail(B200_ECUDA, "[ERROR] %s", gemm_error());
+            } else {
+                launch_attn_prefill(ap, st);
+            }
             GemmParams o{};
             o.A = s->attn_b; o.W = L.wo; o.M = M; o.N = H; o.K = s->nq; o.out = s->x; o.epi = GEMM_RESID_F32; o.ab_f16 = 1;
             if (launch_gemm(o, st) != 0) return fail(B200_ECUDA, "[ERROR] %s", gemm_error());

@@ -477,6 +477,11 @@ static int make_map(CUtensorMap* map, const void* ptr, int rows, int K, int box_
     return 0;
 }
 
+// 2-D row-major 16-bit tensor [rows, cols], box = 64 columns x box_rows rows, 128-byte swizzle
+int tma_map_2d(void* map_out, const void* ptr, int rows, int cols, int box_rows) {
+    return make_map(reinterpret_cast<CUtensorMap*>(map_out), ptr, rows, cols, box_rows);
+}
+
 int launch_gemm(const GemmParams& p, cudaStream_t st) {
     if (p.K % 8 != 0 || p.N % 8 != 0 || p.M <= 0) {
         snprintf(g_gemm_err, sizeof(g_gemm_err), "gemm: need K%%8==0, N%%8==0, M>0 (M=%d N=%d K=%d)", p.M, p.N, p.K);

@@ -123,6 +123,9 @@ struct AttnPrefillParams {
     void* out;                 // [B*S, n_heads*128] 16-bit
 };
 void launch_attn_prefill(const AttnPrefillParams& p, cudaStream_t st);
+// tcgen05 / TMA version (needs q as a hi/lo pair); pool_rows = n_pages * n_kv * page_size rows of 128 in one layer's pool
+int launch_attn_prefill_tc(const AttnPrefillParams& p, int64_t pool_rows, cudaStream_t st);
+int tma_map_2d(void* map_out, const void* ptr, int rows, int cols, int box_rows);
 
 // tcgen05 GEMM: C[M,N] = A[M,K] * W[N,K]^T with fused epilogues
 enum GemmEpi { GEMM_STORE_BF16 = 0, GEMM_RESID_F32 = 1, GEMM_SWIGLU_BF16 = 2, GEMM_STORE_F32 = 3, GEMM_QKV_ROPE = 4 };
