@@ -309,6 +309,7 @@ static int attn_splits(const b200_shard* s, const b200_kv* kv, int M) {
     }
     // latency-bound kernel; measured sweet spot on B200 (32 heads): 16 splits for one row, 8 for 2..8 rows
     int ns = (M == 1) ? (4 * s->num_sms + s->cfg.n_heads - 1) / s->cfg.n_heads : 8;
+    if (attn_decode_cluster_splits() > 0) ns = attn_decode_cluster_splits();  // one cluster per (row, head), partials over DSMEM
     if (forced > 0) ns = forced;
     const int ns_cap = (kv->dev.max_pages_per_slot * kv->dev.page_size + kMaxChunkKeys - 1) / kMaxChunkKeys;
     if (ns < ns_cap) ns = ns_cap;

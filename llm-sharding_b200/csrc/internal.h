@@ -95,6 +95,7 @@ struct AttnDecodeParams {
 };
 void launch_attn_decode(const AttnDecodeParams& p, int M, cudaStream_t st);
 size_t attn_decode_scratch_floats(int rows, int n_heads, int n_splits);
+int attn_decode_cluster_splits();  // split count served by the cluster variant (0: disabled by B200SHARD_ATTN_CLUSTER=0)
 
 struct RopeAppendParams {
     const __nv_bfloat16* qkv;  // [M, (n_heads+2*n_kv)*128]

@@ -323,13 +323,22 @@ __device__ __forceinline__ float dot8(const uint4& k, const float (&q)[8]) {
     return d;
 }
 
-__global__ void __launch_bounds__(kAttnThreads) attn_decode_kernel(const AttnDecodeParams p) {
-    __shared__ float g_acc[8][kHeadDim];
-    __shared__ float g_m[8], g_l[8];
+// CLUSTER = true: the n_splits CTAs of one (m, h) form a thread-block cluster (n_splits == kAttnCluster); the partials
+// travel to cluster rank 0 through distributed shared memory and one hardware cluster barrier replaces the global
+// scratch round trip (store, fence, atomic ticket, reload) — the longest links of this latency-bound kernel's chain.
+constexpr int kAttnCluster = 8;
+constexpr int kAttnClusterThreads = 256;
+
+template <int NT, bool CLUSTER>
+__global__ void __launch_bounds__(NT) attn_decode_kernel(const AttnDecodeParams p) {
+    constexpr int NG = NT / 16;  // half-warps: keys processed side by side
+    __shared__ float g_acc[NG][kHeadDim];
+    __shared__ float g_m[NG], g_l[NG];
     __shared__ int s_last;
+    __shared__ float c_part[CLUSTER ? kAttnCluster : 1][kPartStride];  // rank 0's copy gathers the cluster's partials
     const int split = blockIdx.x, h = blockIdx.y, m = blockIdx.z;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int l16 = lane & 15, grp = warp * 2 + (lane >> 4);  // 8 half-warps, 16 lanes x 8 dims each
+    const int l16 = lane & 15, grp = warp * 2 + (lane >> 4);  // NG half-warps, 16 lanes x 8 dims each
     const int T = p.t_end[m];
     const int chunk = (T + p.n_splits - 1) / p.n_splits;
     const int t0 = split * chunk, t1 = min(T, t0 + chunk);
@@ -353,7 +362,7 @@ __global__ void __launch_bounds__(kAttnThreads) attn_decode_kernel(const AttnDec
     uint4 kk[U], vv[U];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
-        const int t = t0 + grp + 8 * u;
+        const int t = t0 + grp + NG * u;
         if (t < t_old) {
             const int64_t off = kv_offset(t);
             kk[u] = *reinterpret_cast<const uint4*>(p.k_pool + off);
@@ -375,11 +384,11 @@ __global__ void __launch_bounds__(kAttnThreads) attn_decode_kernel(const AttnDec
     float m_run = -INFINITY, l_run = 0.f;
     float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     // trip count is uniform across the CTA (the shuffles below need every lane of the warp); validity is per key
-    for (int tb0 = t0; tb0 < t1; tb0 += 8 * U) {
+    for (int tb0 = t0; tb0 < t1; tb0 += NG * U) {
         const int tb = tb0 + grp;
 #pragma unroll
         for (int u = 0; u < U; ++u) {
-            const int t = tb + 8 * u;
+            const int t = tb + NG * u;
             const bool have = (tb0 == t0) && (t < t_old);  // already requested before the wait
             if (t < t1 && !have) {
                 const int64_t off = kv_offset(t);
@@ -394,7 +403,7 @@ __global__ void __launch_bounds__(kAttnThreads) attn_decode_kernel(const AttnDec
             d += __shfl_xor_sync(0xffffffffu, d, 4);
             d += __shfl_xor_sync(0xffffffffu, d, 2);
             d += __shfl_xor_sync(0xffffffffu, d, 1);
-            if (tb + 8 * u < t1) {  // uniform within the half-warp; no shuffles inside
+            if (tb + NG * u < t1) {  // uniform within the half-warp; no shuffles inside
                 const float m_new = fmaxf(m_run, d);
                 const float alpha = exp2f(m_run - m_new), w = exp2f(d - m_new);
                 l_run = l_run * alpha + w;
@@ -407,23 +416,54 @@ __global__ void __launch_bounds__(kAttnThreads) attn_decode_kernel(const AttnDec
             }
         }
     }
-    // ---- merge the 8 half-warp partials of this CTA
+    // ---- merge the half-warp partials of this CTA
 #pragma unroll
     for (int e = 0; e < 8; ++e) g_acc[grp][l16 * 8 + e] = acc[e];
     if (l16 == 0) { g_m[grp] = m_run; g_l[grp] = l_run; }
     __syncthreads();
-    float* part = p.part + (((size_t)m * p.n_heads + h) * p.n_splits + split) * kPartStride;
-    {
-        float mx = g_m[0];
+    float num = 0.f, den = 0.f, mx = -INFINITY;
+    if (tid < kHeadDim) {
 #pragma unroll
-        for (int g = 1; g < 8; ++g) mx = fmaxf(mx, g_m[g]);
-        float num = 0.f, den = 0.f;
+        for (int g = 0; g < NG; ++g) mx = fmaxf(mx, g_m[g]);
 #pragma unroll
-        for (int g = 0; g < 8; ++g) {
+        for (int g = 0; g < NG; ++g) {
             const float w = (g_m[g] == -INFINITY) ? 0.f : exp2f(g_m[g] - mx);
             num = fmaf(w, g_acc[g][tid], num);
             den = fmaf(w, g_l[g], den);
         }
+    }
+    if (CLUSTER) {
+        uint32_t rank;
+        asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
+        if (tid < kHeadDim) {
+            uint32_t dst;
+            asm volatile("mapa.shared::cluster.u32 %0, %1, 0;" : "=r"(dst) : "r"((uint32_t)__cvta_generic_to_shared(&c_part[rank][0])));
+            asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(dst + 4u * (uint32_t)tid), "f"(num) : "memory");
+            if (tid == 0) {
+                asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(dst + 4u * kHeadDim), "f"(mx) : "memory");
+                asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(dst + 4u * (kHeadDim + 1)), "f"(den) : "memory");
+            }
+        }
+        // every thread of every CTA of the cluster arrives (empty splits included); rank 0 outlives all remote stores
+        asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+        asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+        if (rank != 0 || tid >= kHeadDim) return;
+        float gmx = -INFINITY;
+#pragma unroll
+        for (int s = 0; s < kAttnCluster; ++s) gmx = fmaxf(gmx, c_part[s][kHeadDim]);
+        float n2 = 0.f, d2 = 0.f;
+#pragma unroll
+        for (int s = 0; s < kAttnCluster; ++s) {
+            const float pm = c_part[s][kHeadDim];
+            const float w = (pm == -INFINITY) ? 0.f : exp2f(pm - gmx);
+            n2 = fmaf(w, c_part[s][tid], n2);
+            d2 = fmaf(w, c_part[s][kHeadDim + 1], d2);
+        }
+        p.out[((size_t)m * p.n_heads + h) * kHeadDim + tid] = n2 / d2;
+        return;
+    }
+    float* part = p.part + (((size_t)m * p.n_heads + h) * p.n_splits + split) * kPartStride;
+    if (tid < kHeadDim) {
         part[tid] = num;
         if (tid == 0) { part[kHeadDim] = mx; part[kHeadDim + 1] = den; }
     }
@@ -437,37 +477,60 @@ __global__ void __launch_bounds__(kAttnThreads) attn_decode_kernel(const AttnDec
         if (s_last) *ticket = 0u;  // ready for the next launch (graph replays included)
     }
     __syncthreads();
-    if (!s_last) return;
+    if (!s_last || tid >= kHeadDim) return;
     __threadfence();
     const float* all = p.part + ((size_t)m * p.n_heads + h) * p.n_splits * kPartStride;
-    float mx = -INFINITY;
-    for (int s = 0; s < p.n_splits; ++s) mx = fmaxf(mx, __ldcg(all + s * kPartStride + kHeadDim));
-    float num = 0.f, den = 0.f;
+    float gmx = -INFINITY;
+    for (int s = 0; s < p.n_splits; ++s) gmx = fmaxf(gmx, __ldcg(all + s * kPartStride + kHeadDim));
+    float n2 = 0.f, d2 = 0.f;
     for (int s = 0; s < p.n_splits; ++s) {
         const float pm = __ldcg(all + s * kPartStride + kHeadDim);
-        const float w = (pm == -INFINITY) ? 0.f : exp2f(pm - mx);
-        num = fmaf(w, __ldcg(all + s * kPartStride + tid), num);
-        den = fmaf(w, __ldcg(all + s * kPartStride + kHeadDim + 1), den);
+        const float w = (pm == -INFINITY) ? 0.f : exp2f(pm - gmx);
+        n2 = fmaf(w, __ldcg(all + s * kPartStride + tid), n2);
+        d2 = fmaf(w, __ldcg(all + s * kPartStride + kHeadDim + 1), d2);
     }
-    p.out[((size_t)m * p.n_heads + h) * kHeadDim + tid] = num / den;
+    p.out[((size_t)m * p.n_heads + h) * kHeadDim + tid] = n2 / d2;
 }
+
+static bool attn_cluster_enabled() {
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("B200SHARD_ATTN_CLUSTER");
+        v = (e != nullptr && e[0] == '0') ? 0 : 1;
+    }
+    return v == 1;
+}
+int attn_decode_cluster_splits() { return attn_cluster_enabled() ? kAttnCluster : 0; }
 
 void launch_attn_decode(const AttnDecodeParams& p_in, int M, cudaStream_t st) {
     AttnDecodeParams p = p_in;
     if (p.tickets == nullptr)  // default placement: right behind this call's partials
         p.tickets = reinterpret_cast<unsigned int*>(p.part + (size_t)M * p.n_heads * p.n_splits * kPartStride);
+    const bool cluster = attn_cluster_enabled() && p.n_splits == kAttnCluster;
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(p.n_splits, p.n_heads, M);
-    cfg.blockDim = dim3(kAttnThreads);
+    cfg.blockDim = dim3(cluster ? kAttnClusterThreads : kAttnThreads);
     cfg.dynamicSmemBytes = 0;
     cfg.stream = st;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = attr;
+    cudaLaunchAttribute attr[2];
+    int na = 0;
+    if (cluster) {
+        attr[na].id = cudaLaunchAttributeClusterDimension;
+        attr[na].val.clusterDim.x = kAttnCluster;
+        attr[na].val.clusterDim.y = 1;
+        attr[na].val.clusterDim.z = 1;
+        ++na;
+    }
     const char* e = getenv("B200SHARD_PDL");
-    cfg.numAttrs = (e != nullptr && e[0] == '0') ? 0 : 1;
-    cudaLaunchKernelEx(&cfg, attn_decode_kernel, p);
+    if (!(e != nullptr && e[0] == '0')) {
+        attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[na].val.programmaticStreamSerializationAllowed = 1;
+        ++na;
+    }
+    cfg.attrs = attr;
+    cfg.numAttrs = na;
+    if (cluster) cudaLaunchKernelEx(&cfg, attn_decode_kernel<kAttnClusterThreads, true>, p);
+    else cudaLaunchKernelEx(&cfg, attn_decode_kernel<kAttnThreads, false>, p);
 }
 size_t attn_decode_scratch_floats(int rows, int n_heads, int n_splits) {
     return (size_t)rows * n_heads * n_splits * kPartStride + (size_t)rows * n_heads;
