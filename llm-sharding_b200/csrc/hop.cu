@@ -24,12 +24,16 @@ __global__ void __launch_bounds__(1024) hop_send_kernel(const uint4* __restrict_
     __threadfence_system();
     __syncthreads();
     if (threadIdx.x == 0) {
-        const unsigned int done = atomicAdd(counter, 1u) + 1u;
-        if (done == gridDim.x) {
-            *counter = 0u;
-            __threadfence_system();
-            st_release_sys(peer_flag, seq + 1);
+        bool last = true;
+        if (gridDim.x > 1) {  // a single CTA (payloads up to 64 KiB, flag-only sends) needs no arrival counter
+            const unsigned int done = atomicAdd(counter, 1u) + 1u;
+            last = (done == gridDim.x);
+            if (last) {
+                *counter = 0u;
+                __threadfence_system();
+            }
         }
+        if (last) st_release_sys(peer_flag, seq + 1);  // cumulative: ordered after every store fenced before the barrier
     }
 }
 

@@ -509,7 +509,10 @@ void launch_attn_decode(const AttnDecodeParams& p_in, int M, cudaStream_t st) {
     const bool cluster = attn_cluster_enabled() && p.n_splits == kAttnCluster;
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(p.n_splits, p.n_heads, M);
-    cfg.blockDim = dim3(cluster ? kAttnClusterThreads : kAttnThreads);
+    // one row: 256 threads (128 keys per pass, one pass up to 1024 cached tokens); several rows: 128-thread CTAs pack
+    // four to an SM and finish the rows x heads x 8 CTAs in fewer waves (4 rows: 16.3 us against 19.8 us)
+    const bool wide = cluster && M == 1;
+    cfg.blockDim = dim3(wide ? kAttnClusterThreads : kAttnThreads);
     cfg.dynamicSmemBytes = 0;
     cfg.stream = st;
     cudaLaunchAttribute attr[2];
@@ -529,7 +532,8 @@ void launch_attn_decode(const AttnDecodeParams& p_in, int M, cudaStream_t st) {
     }
     cfg.attrs = attr;
     cfg.numAttrs = na;
-    if (cluster) cudaLaunchKernelEx(&cfg, attn_decode_kernel<kAttnClusterThreads, true>, p);
+    if (cluster && wide) cudaLaunchKernelEx(&cfg, attn_decode_kernel<kAttnClusterThreads, true>, p);
+    else if (cluster) cudaLaunchKernelEx(&cfg, attn_decode_kernel<kAttnThreads, true>, p);
     else cudaLaunchKernelEx(&cfg, attn_decode_kernel<kAttnThreads, false>, p);
 }
 size_t attn_decode_scratch_floats(int rows, int n_heads, int n_splits) {
