@@ -365,13 +365,17 @@ def main():
     ap.add_argument("--transport", default="p2p", choices=["p2p", "nccl"], help="hop transport for --gpus > 1")
     ap.add_argument("--streams", type=int, default=0, help="--gpus > 1: request streams in flight (default: one per GPU)")
     ap.add_argument("--rows", type=int, default=1, help="--gpus > 1: batch rows per stream; 8 streams x 4 rows = BASELINE configs[2]'s batch 32")
+    ap.add_argument("--splits", default="", help="--gpus > 1: layers per stage, e.g. 4,12,16 (BASELINE configs[4]); default: even")
+    ap.add_argument("--mixed", action="store_true", help="--gpus > 1: BASELINE configs[4]'s mixed stream: prompts of 32/512/2048 tokens, "
+                                                         "streams are retired and re-prefilled while the others decode")
+    ap.add_argument("--retire-every", type=int, default=8, help="--mixed: rounds between two retirements")
     args = ap.parse_args()
     PROMPT_LEN = args.prompt_len
     if args.impl == "reference":
         return run_reference(args)
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a GPU: the shard path has no CPU fallback (use --impl reference for the CPU baseline)")
-    if args.gpus == 1:
+    if args.gpus == 1 and not args.mixed:
         return run_single(args)
     from bench_chain import run_chain  # multi-GPU arm
     return run_chain(args, workload_config(args.gpus), METRIC, ClockSampler, peaks)

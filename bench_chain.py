@@ -79,6 +79,15 @@ def run_chain(args, config, metric, ClockSampler, peaks):
     rows = max(1, getattr(args, "rows", 1))          # batch rows per request stream (micro-batch)
     n_streams = getattr(args, "streams", 0) or world
     start, end = layer_range(rank, world, L)
+    splits = [int(v) for v in getattr(args, "splits", "").split(",") if v]
+    if splits:
+        if len(splits) != world or sum(splits) != L or min(splits) < 1:
+            raise SystemExit(f"--splits needs {world} positive layer counts that add up to {L}")
+        start = sum(splits[:rank])
+        end = start + splits[rank]
+    mixed = bool(getattr(args, "mixed", False))
+    if mixed:
+        return run_mixed(args, config, rank, world, local, device, ctrl, start, end, ClockSampler, peaks)
     tmp = tempfile.mkdtemp(prefix=f"b200shard_bench_r{rank}_")
     synthetic.write_model_dir(tmp, cfg)
     with _quiet():
@@ -187,6 +196,104 @@ def run_chain(args, config, metric, ClockSampler, peaks):
                          "frac": per_gpu_bytes / (stage_ms / 1000) / 1e9 / pk["hbm_gbs"], "traffic": None, "peak_source": pk["source"]},
             "hop": hop_lat, "hop_error_flag": int(err[0]),
             "prefill_tok_s": prefill_tok_s, "p50_token_ms": ms_per_step,
+        }
+        print(json.dumps(line), flush=True)
+    dist.barrier(group=ctrl)
+    stage.close()
+    dist.destroy_process_group()
+
+
+MIX_LENGTHS = (32, 512, 2048)
+
+
+def run_mixed(args, config, rank, world, local, device, ctrl, start, end, ClockSampler, peaks):
+    """BASELINE configs[4] / SURVEY.md 8(d) C5: uneven layer split, prompts of mixed length, prefill of new requests
+    interleaved with the ongoing decodes.  Streams are served round-robin; every `--retire-every` rounds the next stream
+    in rotation is retired at its turn (ChainStage.finish) and takes a fresh prompt of its length straight away."""
+    from llm_sharding_b200 import synthetic
+    from llm_sharding_b200.chain import ChainStage, LoopbackCommunicator
+    from llm_sharding_b200.node_worker import NodeWorker
+
+    K, W = args.steps, max(args.warmup, 3)
+    cfg = synthetic.LLAMA2_7B
+    rows = max(1, args.rows)
+    n_streams = args.streams or 2 * world
+    every = max(1, args.retire_every)
+    lens = [MIX_LENGTHS[i % len(MIX_LENGTHS)] for i in range(n_streams)]
+    max_prompt = max(lens)
+    tmp = tempfile.mkdtemp(prefix=f"b200shard_bench_r{rank}_")
+    synthetic.write_model_dir(tmp, cfg)
+    with _quiet():
+        worker = NodeWorker(f"tcp://*:{48900 + rank}", f"tcp://127.0.0.1:{48900 + (rank + 1) % world}", rank == 0, tmp,
+                            device=str(device), dtype=torch.bfloat16,
+                            communicator=LoopbackCommunicator(f"tcp://*:{48900 + rank}", f"tcp://127.0.0.1:{48900 + (rank + 1) % world}"),
+                            max_tokens=rows * max_prompt, max_batch=rows, max_slots=n_streams * rows,
+                            max_seq_len=max_prompt + K + W + 64,
+                            state_provider=synthetic.RandomStateProvider(cfg, str(device), seed=0))
+        worker.load_shards(start, end)
+    stage = ChainStage(worker, rank, world, n_streams, max_prompt, ctrl_group=ctrl, transport=args.transport, rows=rows)
+    g = torch.Generator().manual_seed(1234)
+    n_retire = K // every
+    def new_prompt(i):
+        t = torch.randint(3, cfg["vocab_size"], (rows * lens[i],), generator=g, dtype=torch.int64)
+        return t.to(device) if rank == 0 else None
+    first = [new_prompt(i) for i in range(n_streams)]
+    later = [new_prompt((j % n_streams)) for j in range(n_retire)]   # staged on the head's GPU before the clock starts
+
+    for i in range(n_streams):
+        stage.prefill(i, lens[i], first[i])
+    for _ in range(W):
+        for i in range(n_streams):
+            stage.decode(i)
+    torch.cuda.synchronize()
+    dist.barrier(group=ctrl)
+    eng = worker.shard.engine
+    eng.reset_counters()
+    counts = {"gen": 0, "prompt": 0, "retired": 0}
+
+    def body():
+        for r in range(K):
+            victim = (r // every) % n_streams if (r % every == every - 1 and r // every < n_retire) else -1
+            for i in range(n_streams):
+                if i == victim:
+                    stage.finish(i)
+                    stage.prefill(i, lens[i], later[r // every])
+                    counts["prompt"] += rows * lens[i]
+                    counts["retired"] += 1
+                else:
+                    stage.decode(i)
+                counts["gen"] += rows   # a decode yields a token, and so does the prefill that replaces it
+
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local) as clk:
+        e0.record()
+        body()
+        e1.record()
+        torch.cuda.synchronize()
+    t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX, group=ctrl)
+    total_ms = float(t[0])
+    cnt = eng.counters()
+    launches = torch.tensor([cnt["launches"]], dtype=torch.float64)
+    dist.all_reduce(launches, group=ctrl)
+    err = torch.tensor([stage.error()], dtype=torch.float64)
+    dist.all_reduce(err, op=dist.ReduceOp.MAX, group=ctrl)
+    layers = [None] * world
+    dist.all_gather_object(layers, (start, end), group=ctrl)
+    if rank == 0:
+        line = {
+            "metric": "llama2_7b_mixed_stream_tok_s", "value": counts["gen"] * 1000.0 / total_ms, "unit": "tok/s", "n_gpus": world,
+            "steps": K, "warmup": W, "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": "BASELINE.json configs[4]: Llama-2-7B bf16, uneven layer split, embedding holder = entry stage, "
+                                   "request streams with 32/512/2048-token prompts; streams are retired and re-prefilled in "
+                                   "rotation while the others decode; one step = one round over all streams",
+                       "layers_per_stage": layers, "streams": n_streams, "rows_per_stream": rows, "prompt_lengths": lens,
+                       "retire_every_rounds": every, "transport": args.transport,
+                       "l2": "inputs larger than L2: every stage streams its layers' weights once per stream per round"},
+            "clocks": clk.summary(), "gpu_launches": int(launches[0]),
+            "generated_tokens": counts["gen"], "prompt_tokens_in_timed_region": counts["prompt"], "requests_retired": counts["retired"],
+            "prompt_tok_s": counts["prompt"] * 1000.0 / total_ms, "hop_error_flag": int(err[0]),
         }
         print(json.dumps(line), flush=True)
     dist.barrier(group=ctrl)

@@ -157,15 +157,25 @@ class RingSchedule:
         self.seq_in = 0    # next message expected from the predecessor
         self.seq_out = 0   # next message sent to the successor
         self.prefilled = [False] * n_streams
+        self._owed = []    # streams whose token is on its way back to the head, in the order the tail produces them
 
     def _slot(self, seq: int) -> int:
         return seq % self.n_streams
+
+    def _consume_token_of(self, stream: int) -> None:
+        """The head's mailbox is a FIFO: a stream may take its token only when it is the oldest one outstanding, i.e.
+        streams must be continued (or finished) in the order their previous items were issued — round-robin does."""
+        if not self._owed or self._owed[0] != stream:
+            raise RuntimeError(f"[ERROR] stream {stream} continued out of order: the next token in the ring belongs to "
+                               f"stream {self._owed[0] if self._owed else None}")
+        self._owed.pop(0)
 
     def prefill(self, stream: int) -> dict:
         """Work item for the prompt of `stream`.  The head consumes nothing (the prompt comes from its own host)."""
         if self.prefilled[stream]:
             raise RuntimeError(f"[ERROR] stream {stream} already holds a request; clear it first")
         self.prefilled[stream] = True
+        self._owed.append(stream)
         item = {"kind": "prefill", "stream": stream, "kv_slot": stream, "wait": None, "send": None}
         if not self.is_head:
             item["wait"] = (self.seq_in, self._slot(self.seq_in))
@@ -179,14 +189,32 @@ class RingSchedule:
         tail sent back, utils/node_worker.py:515-520) consumes one message and produces one."""
         if not self.prefilled[stream]:
             raise RuntimeError(f"[ERROR] stream {stream} has no request to continue")
+        self._consume_token_of(stream)
+        self._owed.append(stream)
         item = {"kind": "decode", "stream": stream, "kv_slot": stream,
                 "wait": (self.seq_in, self._slot(self.seq_in)), "send": (self.seq_out, self._slot(self.seq_out))}
         self.seq_in += 1
         self.seq_out += 1
         return item
 
+    def finish(self, stream: int) -> dict:
+        """Work item that retires the request of `stream` (its stop rule fired, utils/node_worker.py:291-299): the head
+        consumes the last token the tail sent back — every message produced must be consumed or the two sides' counts
+        drift apart — and nothing is sent; the other stages only release the stream's KV slots.  The stream can then be
+        given a new prompt while the remaining streams keep decoding."""
+        if not self.prefilled[stream]:
+            raise RuntimeError(f"[ERROR] stream {stream} has no request to finish")
+        self._consume_token_of(stream)
+        self.prefilled[stream] = False
+        item = {"kind": "finish", "stream": stream, "kv_slot": stream, "wait": None, "send": None}
+        if self.is_head:
+            item["wait"] = (self.seq_in, self._slot(self.seq_in))
+            self.seq_in += 1
+        return item
+
     def clear(self) -> None:
         self.prefilled = [False] * self.n_streams
+        self._owed = []
 
 
 class _DevPtr:
@@ -227,7 +255,7 @@ class ChainStage:
             mine = (self.hop.export(), self.hop.dev_index)
             gathered = [None] * world
             dist.all_gather_object(gathered, mine, group=ctrl_group)
-            self.hop.connect(gathered[self.nxt][0], gathered[self.nxt][1], same_process=False)
+            self.hop.connect(gathered[self.nxt][0], gathered[self.nxt][1], same_process=(world == 1))
             dist.barrier(group=ctrl_group)
         else:
             # NCCL A/B transport.  Two communicators: hidden states travel forward on one, token ids return to the head
@@ -344,6 +372,21 @@ class ChainStage:
         round trip through pinned host memory before it is embedded (end-to-end mode)."""
         item = self.sched.decode(stream)
         self._run(item, 1, None, record, via_host and self.sched.is_head)
+
+    def finish(self, stream: int, record: bool = False) -> None:
+        """Retire the request of `stream` on this stage (same call on every stage, at the same point of the schedule):
+        the head takes the last token out of its mailbox, every stage returns the stream's KV pages to its pool
+        (stream-ordered, behind the kernels that still read them)."""
+        item = self.sched.finish(stream)
+        B = self.rows
+        if item["wait"] is not None:
+            self._wait(item, 8 * B)
+            if record:
+                src = (tensor_view(self._in_ptr(item), 8 * B, self.device) if self.hop is not None
+                       else self.inbuf[item["wait"][1]][:8 * B])
+                self.tokens.append(src.view(torch.int64).clone())
+        for slot in range(stream * B, stream * B + B):
+            self.kv.reset(slot)
 
     def error(self) -> int:
         return self.hop.error() if self.hop is not None else 0

@@ -48,6 +48,42 @@ def test_ring_schedule_slots_are_stable_per_stream():
         RingSchedule(0, 2, 2).decode(1)
 
 
+def test_finish_keeps_the_ring_counts_aligned_under_a_mixed_schedule():
+    """Streams are retired and given new prompts while the others keep decoding (BASELINE configs[4]): every message a
+    stage produces is consumed by its successor, in order, for the stream it was meant for, and the messages in flight
+    on one hop never share a mailbox slot."""
+    world, n_streams = 3, 3
+    scheds = [RingSchedule(r, world, n_streams) for r in range(world)]
+    queues = [[] for _ in range(world)]   # queues[r]: messages produced by stage r, not yet consumed by stage r+1
+
+    def run(kind, stream):
+        for r in range(world):
+            it = getattr(scheds[r], kind)(stream)
+            if it["wait"] is not None:
+                seq_slot, st = queues[(r - 1) % world].pop(0)
+                assert seq_slot == it["wait"] and st == stream, (kind, stream, r)
+            if it["send"] is not None:
+                q = queues[r]
+                q.append((it["send"], stream))
+                assert len({slot for (_, slot), _ in q}) == len(q) <= n_streams
+    for i in range(n_streams):
+        run("prefill", i)
+    # streams are served round-robin; at its turn a stream decodes, or finishes (and may take a new prompt)
+    plan = [("decode", 0), ("decode", 1), ("decode", 2),
+            ("decode", 0), ("finish", 1), ("prefill", 1), ("decode", 2),
+            ("finish", 0), ("decode", 1), ("finish", 2), ("prefill", 2),
+            ("decode", 1), ("decode", 2),
+            ("prefill", 0), ("decode", 1), ("decode", 2), ("decode", 0)]
+    for kind, stream in plan:
+        run(kind, stream)
+    # what is left in flight: exactly one token per live stream, waiting in the head's mailbox
+    assert [len(q) for q in queues] == [0, 0, 3]
+    with pytest.raises(RuntimeError):   # the oldest outstanding token belongs to stream 1, not 2
+        scheds[0].decode(2)
+    with pytest.raises(RuntimeError):
+        scheds[0].finish(0)
+
+
 def _free_port():
     with socket.socket() as s:
         s.bind(("127.0.0.1", 0))

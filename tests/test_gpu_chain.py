@@ -116,3 +116,63 @@ def test_two_gpu_ring_matches_single_process_chain(tmp_path):
     # the head records, per decode, the token that came back: round r, stream i -> token r of stream i
     by_stream = [[got[r * n_streams + i] for r in range(rounds)] for i in range(n_streams)]
     assert by_stream == expected
+
+
+def test_single_stage_ring_retires_and_restarts_streams(tmp_path):
+    """BASELINE configs[4]'s mixed prefill + decode stream, on the smallest ring there is (one stage that is head and
+    tail, so it runs on one GPU): a stream is retired (`finish`) and given a new, longer prompt while the other stream
+    keeps decoding; every request must produce the tokens it produces when it runs alone."""
+    import torch.distributed as dist
+    from gpu_utils import build_chain, close_chain, shard_dir
+    from llm_sharding_b200.chain import ChainStage, LoopbackCommunicator, generate
+    from llm_sharding_b200.node_worker import NodeWorker
+    from oracle import synth
+    cfg = synth.PRESETS["tiny"]
+    d = shard_dir(str(tmp_path), "tiny", 28)
+    reqs = {"a": (synth.prompt_ids(cfg, 910, 1, 20), 6), "b": (synth.prompt_ids(cfg, 911, 1, 9), 3),
+            "c": (synth.prompt_ids(cfg, 912, 1, 33), 3)}
+    expected = {}
+    workers = build_chain(str(tmp_path), "tiny", 28, [(0, 4)], max_tokens=64)
+    try:
+        for name, (ids, n) in reqs.items():
+            for w in workers:
+                w.clear_KV_cache()
+            toks, _ = generate(workers, ids, n)
+            expected[name] = [int(t) for t in toks[:, 0]]
+    finally:
+        close_chain(workers)
+    dist.init_process_group("gloo", rank=0, world_size=1, init_method=f"tcp://127.0.0.1:{_free_port()}")
+    try:
+        src, dst = "tcp://*:47390", "tcp://127.0.0.1:47390"
+        w = NodeWorker(src, dst, True, d, device="cuda:0", dtype=torch.bfloat16, communicator=LoopbackCommunicator(src, dst),
+                       max_tokens=64, max_batch=1, max_slots=2)
+        w.load_shards(0, cfg.num_hidden_layers)
+        stage = ChainStage(w, 0, 1, 2, 64, ctrl_group=None, transport="p2p", max_wait_us=10_000_000)
+        dev = lambda name: reqs[name][0][0].to("cuda:0")
+        stage.prefill(0, 20, dev("a"))
+        stage.prefill(1, 9, dev("b"))
+        order = []
+        for _ in range(2):
+            stage.decode(0, record=True); order.append("a")
+            stage.decode(1, record=True); order.append("b")
+        stage.decode(0, record=True); order.append("a")
+        stage.finish(1, record=True); order.append("b")        # request b is done after 3 tokens ...
+        stage.prefill(1, 33, dev("c"))                           # ... and its stream takes a longer prompt at once
+        for _ in range(2):
+            stage.decode(0, record=True); order.append("a")
+            stage.decode(1, record=True); order.append("c")
+        stage.finish(0, record=True); order.append("a")
+        stage.finish(1, record=True); order.append("c")
+        torch.cuda.synchronize()
+        assert stage.error() == 0
+        got = {k: [] for k in reqs}
+        for name, t in zip(order, stage.tokens):
+            got[name].append(int(t[0]))
+        assert got == expected
+        assert w.past_key_value.get_seq_length(0) == 0 and w.past_key_value.get_seq_length(1) == 0
+        with pytest.raises(RuntimeError):
+            stage.decode(0)
+        stage.close()
+        w.shard.engine.close()
+    finally:
+        dist.destroy_process_group()
