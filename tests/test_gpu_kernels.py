@@ -116,7 +116,11 @@ def attn_decode_reference(q, dense, n_heads, n_kv):
 
 
 @pytest.mark.parametrize("rows,n_heads,n_kv,T_list,n_splits", [
-    (1, 32, 32, [640], 10), (1, 4, 2, [1], 3), (3, 8, 8, [65, 128, 7], 4), (2, 32, 8, [1000, 513], 16), (4, 2, 2, [64, 64, 64, 64], 1)])
+    (1, 32, 32, [640], 10), (1, 4, 2, [1], 3), (3, 8, 8, [65, 128, 7], 4), (2, 32, 8, [1000, 513], 16), (4, 2, 2, [64, 64, 64, 64], 1),
+    # n_splits == 8 is served by the cluster variant (partials over distributed shared memory): one row = 256-thread CTAs,
+    # several rows = 128-thread CTAs; a single key leaves 7 of the 8 CTAs of a cluster with nothing but the barrier
+    (1, 32, 32, [640], 8), (1, 4, 2, [1], 8), (3, 8, 8, [65, 128, 7], 8), (2, 32, 8, [3000, 1537], 8), (1, 8, 2, [2500], 8),
+    (8, 4, 4, [5, 9, 1, 130, 64, 65, 2, 300], 8)])
 def test_attn_decode_split_k(lib, rows, n_heads, n_kv, T_list, n_splits):
     from llm_sharding_b200 import _lib
     g = torch.Generator(device="cuda").manual_seed(rows * 100 + n_heads)

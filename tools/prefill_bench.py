@@ -14,6 +14,8 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--layers", type=int, default=4)
     ap.add_argument("--causal", type=int, default=0)
+    ap.add_argument("--cases", default="1x512,1x2048,4x2048,1x8192", help="comma-separated BxS list")
+    ap.add_argument("--iters", type=int, default=4, help="timed calls per case (>= 3: the median of all but the first is reported)")
     a = ap.parse_args()
     from llm_sharding_b200 import synthetic
     from llm_sharding_b200.engine import Shard, read_model_config
@@ -24,11 +26,11 @@ def main():
     sh = Shard(read_model_config(d), a.layers, torch.device("cuda:0"), max_tokens=16384, max_batch=16)
     for l in range(a.layers):
         sh.set_layer(l, prov(f"block_{l}.pth"))
-    for B, S in ((1, 512), (1, 2048), (4, 2048), (1, 8192)):
+    for B, S in [tuple(int(v) for v in c.split("x")) for c in a.cases.split(",")]:
         x = (torch.randn(B, S, 4096, device="cuda") * 0.1).bfloat16()
         kv = sh.new_kv(max_slots=B, max_seq_len=S + 64)
         times = []
-        for it in range(4):
+        for it in range(a.iters):
             kv.reset(-1)
             torch.cuda.synchronize()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -37,7 +39,7 @@ def main():
             e1.record()
             torch.cuda.synchronize()
             times.append(e0.elapsed_time(e1))
-        ms = sorted(times[1:])[1]
+        ms = sorted(times[1:])[(len(times) - 1) // 2] if len(times) > 1 else times[0]
         flops = a.layers * (2 * 202375168 * B * S + 4 * B * S * S * 4096 * (0.5 if a.causal else 1.0))
         print(f"B={B} S={S}: {ms / a.layers * 1000:8.1f} us/layer  {B * S / ms * 1000 / 1e3 * (32 / a.layers) / 32:8.1f} k tok/s per 32-layer-equivalent x(32/{a.layers})"
               f"  {flops / ms / 1e9:7.1f} TFLOP/s", flush=True)
