@@ -193,6 +193,11 @@ B200_API int b200_gemm_f16(const void* d_a, const void* d_w, int M, int N, int K
 /* out[M,N] (fp32) = X[M,K] (fp32) * W[N,K]^T (fp16), M <= 8: the weight-streaming decode kernels (M == 1: CUDA cores,
  * fp32 activations; 2 <= M <= 8: mma.sync tensor cores, activations rounded to fp16) */
 B200_API int b200_gemv_f16(const float* d_x, const void* d_w, int M, int N, int K, float* d_out, void* stream);
+/* out[M,N] (fp32) = X[M,K] (fp16) * W[N,K]^T (fp16), M <= 32: the weight-streaming tensor-core GEMM of batched decode
+ * (tcgen05, weight tile as the 128-row operand, split-K over a cluster of `split` = 1, 2, 4 or 8 CTAs reduced through
+ * distributed shared memory; split = 0 lets the library choose).  Needs K % 8 == 0 and K >= 64.  Stands where the
+ * reference's nn.Linear calls (transformers modeling_llama.py:182-184,262-264,287-288) run for a 9..32-row batch. */
+B200_API int b200_gemm_stream_f16(const void* d_x, const void* d_w, int M, int N, int K, int split, float* d_out, void* stream);
 
 #ifdef __cplusplus
 }

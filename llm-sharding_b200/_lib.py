@@ -72,6 +72,7 @@ PROTOTYPES = {
     "b200_gemm_bf16": (_I, [_P, _P, _I, _I, _I, _P, _P]),
     "b200_gemm_f16": (_I, [_P, _P, _I, _I, _I, _P, _P]),
     "b200_gemv_f16": (_I, [_P, _P, _I, _I, _I, _P, _P]),
+    "b200_gemm_stream_f16": (_I, [_P, _P, _I, _I, _I, _I, _P, _P]),
 }
 
 _lib = None

@@ -134,10 +134,12 @@ extern "C" B200_API int b200_shard_create(const b200_shard_config_t* c, int devi
     r |= dev_alloc(A, &s->qrot_lo, MT * s->nq);
     r |= dev_alloc(A, &s->attn_b, MT * s->nq);
     r |= dev_alloc(A, &s->act_b, MT * I);
-    r |= dev_alloc(A, &s->q_f, (size_t)kMaxGemvRows * s->nq);
-    r |= dev_alloc(A, &s->attn_f, (size_t)kMaxGemvRows * s->nq);
+    r |= dev_alloc(A, &s->q_f, (size_t)kMaxStreamRows * s->nq);
+    r |= dev_alloc(A, &s->attn_f, (size_t)kMaxStreamRows * s->nq);
     r |= dev_alloc(A, &s->act_f, (size_t)kMaxGemvRows * I);
-    r |= dev_alloc(A, &s->attn_part, attn_decode_scratch_floats(kMaxGemvRows, c->n_heads, kMaxSplits));
+    // partials for rows x splits <= 8 x 16 per head, followed by one arrival ticket per (row, head) for up to 32 rows
+    const size_t part_floats = (size_t)kMaxGemvRows * c->n_heads * kMaxSplits * 130 + (size_t)kMaxStreamRows * c->n_heads;
+    r |= dev_alloc(A, &s->attn_part, part_floats);
     r |= dev_alloc(A, &s->lastrow, (size_t)c->max_batch * H);
     r |= dev_alloc(A, &s->lastrow_b, (size_t)c->max_batch * H);
     r |= dev_alloc(A, &s->logits, (size_t)c->max_batch * V);
@@ -149,7 +151,7 @@ extern "C" B200_API int b200_shard_create(const b200_shard_config_t* c, int devi
     r |= dev_alloc(A, &s->tm.sin, MT * 64);
     if (r != 0) { b200_shard_destroy(s); return B200_ENOMEM; }
     // arrival tickets of decode attention start at zero (the kernel re-zeroes them itself afterwards)
-    CU_TRY(cudaMemset(s->attn_part, 0, attn_decode_scratch_floats(kMaxGemvRows, c->n_heads, kMaxSplits) * sizeof(float)));
+    CU_TRY(cudaMemset(s->attn_part, 0, part_floats * sizeof(float)));
     *out = s;
     return 0;
 }
@@ -310,15 +312,38 @@ static int attn_splits(const b200_shard* s, const b200_kv* kv, int M) {
     // latency-bound kernel; measured sweet spot on B200 (32 heads): 16 splits for one row, 8 for 2..8 rows
     int ns = (M == 1) ? (4 * s->num_sms + s->cfg.n_heads - 1) / s->cfg.n_heads : 8;
     if (attn_decode_cluster_splits() > 0) ns = attn_decode_cluster_splits();  // one cluster per (row, head), partials over DSMEM
-    if (forced > 0) ns = forced;
+    if (M > kMaxGemvRows) {
+        // batched decode: rows x heads already gives hundreds of CTAs; split only as far as ~4 CTAs per SM needs,
+        // and never beyond what the scratch for the partials (sized for 8 rows x 16 splits) holds
+        ns = (4 * s->num_sms + M * s->cfg.n_heads - 1) / (M * s->cfg.n_heads);
+        const int cap = (kMaxGemvRows * kMaxSplits) / M;
+        if (ns > cap) ns = cap;
+        if (ns >= 8) ns = attn_decode_cluster_splits() > 0 ? 8 : ns;
+    }
+    if (forced > 0 && M <= kMaxGemvRows) ns = forced;
     const int ns_cap = (kv->dev.max_pages_per_slot * kv->dev.page_size + kMaxChunkKeys - 1) / kMaxChunkKeys;
     if (ns < ns_cap) ns = ns_cap;
     return ns < 1 ? 1 : (ns > kMaxSplits ? kMaxSplits : ns);
 }
 
+static bool stream_gemm_enabled() {  // B200SHARD_STREAM_GEMM=0: 9..32-row decode takes the 128 x 128 tile GEMMs instead (A/B)
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("B200SHARD_STREAM_GEMM");
+        v = (e != nullptr && e[0] == '0') ? 0 : 1;
+    }
+    return v == 1;
+}
+
 static int gemv_row_limit(const b200_shard* s) {
     const int kmax = s->cfg.intermediate_size > s->cfg.hidden_size ? s->cfg.intermediate_size : s->cfg.hidden_size;
-    int lim = kMaxGemvRows;
+    static int cap = -1;  // B200SHARD_GEMV_ROWS: rows up to which the CUDA-core / mma.sync GEMVs are used (A/B against the tcgen05 path)
+    if (cap < 0) {
+        const char* e = getenv("B200SHARD_GEMV_ROWS");
+        cap = e ? atoi(e) : kGemvRowsDefault;
+        if (cap < 1 || cap > kMaxGemvRows) cap = kGemvRowsDefault;
+    }
+    int lim = cap;
     while (lim > 0 && gemv_smem_bytes(lim, kmax) > 220 * 1024) --lim;
     return lim;
 }
@@ -368,6 +393,7 @@ static int enqueue_forward(b200_shard_t* s, b200_kv_t* kv, const SlotList& sl, c
     launch_load_residual(reinterpret_cast<const __nv_bfloat16*>(in), s->x, (int64_t)M * H, st);
     s->n_launch += 3;
     const bool gemv_path = M <= gemv_row_limit(s);
+    const bool stream_path = !gemv_path && M <= kMaxStreamRows && stream_gemm_enabled() && H % 64 == 0 && I % 64 == 0;
     for (int l = 0; l < c.n_layers; ++l) {
         const LayerW& L = s->layers[l];
         __nv_bfloat16* kp = kv->k_pool + (int64_t)l * kv->layer_stride;
@@ -396,6 +422,34 @@ static int enqueue_forward(b200_shard_t* s, b200_kv_t* kv, const SlotList& sl, c
             d.W = L.wdown; d.x = s->act_f; d.N = H; d.K = I; d.out = s->x;
             launch_gemv(d, M, EPI_RESID, false, s->num_sms, st);
             s->n_launch += 5;
+        } else if (stream_path) {
+            // 4..32 token rows (batched decode, short prompts): still bound by reading the weights once, now on the tensor cores
+            // (gemm_stream_tc.cu); operands fp16, residual stream and q fp32, K/V rounded to bf16 once
+            launch_rmsnorm_bf16(s->x, L.norm1, c.rms_eps, M, H, s->xn, st, true);
+            StreamGemmParams g{};
+            g.W = L.wqkv; g.X = s->xn; g.M = M; g.N = s->qkv_rows; g.K = H;
+            g.q_out = s->q_f; g.k_pool = kp; g.v_pool = vp; g.kv_off = s->tm.kv_off; g.cos = s->tm.cos; g.sin = s->tm.sin;
+            g.n_heads = c.n_heads; g.n_kv = c.n_kv_heads; g.head_stride = head_stride;
+            if (launch_gemm_stream(g, EPI_QKV, s->num_sms, st) != 0) return fail(B200_ECUDA, "[ERROR] %s", gemm_stream_last_error());
+            AttnDecodeParams a{};
+            a.q = s->q_f; a.k_pool = kp; a.v_pool = vp; a.block_table = kv->dev.block_table; a.t_end = s->tm.t_end; a.call_base = s->tm.call_base;
+            a.slots = sl; a.S = S; a.n_heads = c.n_heads; a.n_kv = c.n_kv_heads; a.page_size = kv->dev.page_size;
+            a.max_pages_per_slot = kv->dev.max_pages_per_slot;
+            a.n_splits = attn_splits(s, kv, M);
+            a.part = s->attn_part; a.out = s->attn_f; a.out_h = reinterpret_cast<__half*>(s->attn_b);
+            a.tickets = reinterpret_cast<unsigned int*>(s->attn_part + (size_t)kMaxGemvRows * c.n_heads * kMaxSplits * 130);
+            launch_attn_decode(a, M, st);
+            StreamGemmParams o{};
+            o.W = L.wo; o.X = s->attn_b; o.M = M; o.N = H; o.K = s->nq; o.out = s->x;
+            if (launch_gemm_stream(o, EPI_RESID, s->num_sms, st) != 0) return fail(B200_ECUDA, "[ERROR] %s", gemm_stream_last_error());
+            launch_rmsnorm_bf16(s->x, L.norm2, c.rms_eps, M, H, s->xn, st, true);
+            StreamGemmParams gu{};
+            gu.W = L.wgu; gu.X = s->xn; gu.M = M; gu.N = 2 * I; gu.K = H; gu.act_h = reinterpret_cast<__half*>(s->act_b);
+            if (launch_gemm_stream(gu, EPI_SWIGLU, s->num_sms, st) != 0) return fail(B200_ECUDA, "[ERROR] %s", gemm_stream_last_error());
+            StreamGemmParams d{};
+            d.W = L.wdown; d.X = s->act_b; d.M = M; d.N = H; d.K = I; d.out = s->x;
+            if (launch_gemm_stream(d, EPI_RESID, s->num_sms, st) != 0) return fail(B200_ECUDA, "[ERROR] %s", gemm_stream_last_error());
+            s->n_launch += 7;
         } else {
             // activations feeding the tensor cores are fp16 (10 mantissa bits) against exact bf16 weights; q reaches
             // attention as a (hi, lo) bf16 pair; K/V are rounded to bf16 exactly once, inside the QKV epilogue
@@ -460,10 +514,16 @@ static int enqueue_tail(b200_shard_t* s, int B, int S, bool from_residual, int64
         }
     } else {
         launch_rmsnorm_bf16(s->lastrow, nullptr, 0.f, B, c.hidden_size, s->lastrow_b, st, true);
-        GemmParams g{};
-        g.A = s->lastrow_b; g.W = s->lm_head; g.M = B; g.N = c.vocab_size; g.K = c.hidden_size; g.out = s->logits;
-        g.epi = GEMM_STORE_F32; g.ab_f16 = 1;
-        if (launch_gemm(g, st) != 0) return fail(B200_ECUDA, "[ERROR] %s", gemm_error());
+        if (B <= kMaxStreamRows && stream_gemm_enabled() && c.hidden_size % 64 == 0) {
+            StreamGemmParams g{};
+            g.W = s->lm_head; g.X = s->lastrow_b; g.M = B; g.N = c.vocab_size; g.K = c.hidden_size; g.out = s->logits;
+            if (launch_gemm_stream(g, EPI_STORE, s->num_sms, st) != 0) return fail(B200_ECUDA, "[ERROR] %s", gemm_stream_last_error());
+        } else {
+            GemmParams g{};
+            g.A = s->lastrow_b; g.W = s->lm_head; g.M = B; g.N = c.vocab_size; g.K = c.hidden_size; g.out = s->logits;
+            g.epi = GEMM_STORE_F32; g.ab_f16 = 1;
+            if (launch_gemm(g, st) != 0) return fail(B200_ECUDA, "[ERROR] %s", gemm_error());
+        }
         s->n_launch += 1;
     }
     launch_argmax(s->logits, B, c.vocab_size, tok, margin, st);
@@ -863,6 +923,20 @@ extern "C" B200_API int b200_gemv_f16(const float* x, const void* w, int M, int 
     GemvParams g{};
     g.W = w; g.x = x; g.N = N; g.K = K; g.out = out;
     launch_gemv(g, M, EPI_STORE, false, sms, (cudaStream_t)stream);
+    CU_TRY(cudaGetLastError());
+    return 0;
+}
+
+extern "C" B200_API int b200_gemm_stream_f16(const void* x, const void* w, int M, int N, int K, int split, float* out, void* stream) {
+    if (x == nullptr || w == nullptr || out == nullptr) return fail(B200_EINVAL, "[ERROR] null argument");
+    if (split != 0 && split != 1 && split != 2 && split != 4 && split != 8) return fail(B200_EINVAL, "[ERROR] gemm_stream: split must be 0, 1, 2, 4 or 8");
+    if (split > 1 && (K + 63) / 64 < split) return fail(B200_EINVAL, "[ERROR] gemm_stream: K too short for this split");
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    StreamGemmParams g{};
+    g.W = w; g.X = x; g.M = M; g.N = N; g.K = K; g.split = split; g.out = out;
+    if (launch_gemm_stream(g, EPI_STORE, sms, (cudaStream_t)stream) != 0) return fail(B200_EINVAL, "[ERROR] %s", gemm_stream_last_error());
     CU_TRY(cudaGetLastError());
     return 0;
 }

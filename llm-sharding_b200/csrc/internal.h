@@ -91,6 +91,7 @@ struct AttnDecodeParams {
     int n_heads, n_kv, page_size, max_pages_per_slot, n_splits;
     float* part;               // scratch: [M][n_heads][n_splits][130] partials, then M*n_heads arrival tickets (zeroed)
     float* out;                // [M, n_heads*128] fp32
+    __half* out_h = nullptr;   // optional fp16 copy of the output (operand of the tensor-core o_proj for 9..32 rows)
     unsigned int* tickets;     // [M*n_heads] arrival counters, zero before the launch (nullptr: right behind the partials)
 };
 void launch_attn_decode(const AttnDecodeParams& p, int M, cudaStream_t st);
@@ -129,6 +130,29 @@ int launch_attn_prefill_tc(const AttnPrefillParams& p, int64_t pool_rows, cudaSt
 int tma_map_2d(void* map_out, const void* ptr, int rows, int cols, int box_rows);
 
 // tcgen05 GEMM: C[M,N] = A[M,K] * W[N,K]^T with fused epilogues
+// Weight-streaming tensor-core GEMM for 9..32 token rows (gemm_stream_tc.cu): operands fp16, epilogues = GemvEpi
+constexpr int kMaxStreamRows = 32;
+constexpr int kGemvRowsDefault = 3;  // measured crossover: 4 rows and more run faster on the tcgen05 streaming GEMM (105 vs 111 us per 7B layer)
+struct StreamGemmParams {
+    const void* W;            // [N,K] fp16 (paired layouts as for the GEMV)
+    const void* X;            // [M,K] fp16
+    int M, N, K;
+    int split = 0;            // cluster size of the split-K (1, 2, 4, 8); 0: chosen by the launcher
+    float* out = nullptr;     // EPI_STORE / EPI_RESID: fp32 [M,N]
+    __half* act_h = nullptr;  // EPI_SWIGLU: fp16 [M,N/2]
+    float* q_out = nullptr;   // EPI_QKV: fp32 [M, n_heads*128]
+    __nv_bfloat16* k_pool = nullptr;
+    __nv_bfloat16* v_pool = nullptr;
+    const int64_t* kv_off = nullptr;
+    const float* cos = nullptr;
+    const float* sin = nullptr;
+    int n_heads = 0, n_kv = 0;
+    int64_t head_stride = 0;
+};
+int launch_gemm_stream(const StreamGemmParams& p, int epi, int num_sms, cudaStream_t st);
+int gemm_stream_split(int N, int K, int num_sms);
+const char* gemm_stream_last_error();
+
 enum GemmEpi { GEMM_STORE_BF16 = 0, GEMM_RESID_F32 = 1, GEMM_SWIGLU_BF16 = 2, GEMM_STORE_F32 = 3, GEMM_QKV_ROPE = 4 };
 struct GemmParams {
     const void* A;           // [M,K] bf16, or fp16 when ab_f16

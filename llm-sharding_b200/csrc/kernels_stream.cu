@@ -133,6 +133,10 @@ __global__ void __launch_bounds__(256) rmsnorm_bf16_kernel(const float* __restri
                                                            const __nv_bfloat16* __restrict__ w, float eps, int n,
                                                            __nv_bfloat16* __restrict__ out) {
     __shared__ float red[33];
+    // programmatic dependent launch: x comes from the previous kernel; the next kernel (a weight-streaming GEMM in the
+    // batched-decode path) may start requesting its weights while this one runs
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     const float* xr = x + (size_t)blockIdx.x * n;
     __nv_bfloat16* orow = out + (size_t)blockIdx.x * n;
     const int n8 = n / 8;
@@ -170,8 +174,19 @@ __global__ void __launch_bounds__(256) rmsnorm_bf16_kernel(const float* __restri
 void launch_rmsnorm_bf16(const float* x, const __nv_bfloat16* norm_w, float eps, int rows, int n,
                          void* out, cudaStream_t st, bool f16_out) {
     if (rows <= 0) return;
-    if (f16_out) rmsnorm_bf16_kernel<true><<<rows, 256, 0, st>>>(x, norm_w, eps, n, reinterpret_cast<__nv_bfloat16*>(out));
-    else rmsnorm_bf16_kernel<false><<<rows, 256, 0, st>>>(x, norm_w, eps, n, reinterpret_cast<__nv_bfloat16*>(out));
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(rows);
+    cfg.blockDim = dim3(256);
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    const char* e = getenv("B200SHARD_PDL");
+    cfg.numAttrs = (e != nullptr && e[0] == '0') ? 0 : 1;
+    __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(out);
+    if (f16_out) cudaLaunchKernelEx(&cfg, rmsnorm_bf16_kernel<true>, x, norm_w, eps, n, o);
+    else cudaLaunchKernelEx(&cfg, rmsnorm_bf16_kernel<false>, x, norm_w, eps, n, o);
 }
 
 __global__ void __launch_bounds__(256) lastrow_norm_f32_kernel(const float* __restrict__ x,
@@ -460,6 +475,14 @@ __global__ void __launch_bounds__(NT) attn_decode_kernel(const AttnDecodeParams 
             d2 = fmaf(w, c_part[s][kHeadDim + 1], d2);
         }
         p.out[((size_t)m * p.n_heads + h) * kHeadDim + tid] = n2 / d2;
+        if (p.out_h != nullptr) p.out_h[((size_t)m * p.n_heads + h) * kHeadDim + tid] = __float2half_rn(n2 / d2);
+        return;
+    }
+    if (p.n_splits == 1) {  // the CTA saw every key of its (row, head): nothing to merge (many rows: one CTA per row and head)
+        if (tid < kHeadDim) {
+            p.out[((size_t)m * p.n_heads + h) * kHeadDim + tid] = num / den;
+            if (p.out_h != nullptr) p.out_h[((size_t)m * p.n_heads + h) * kHeadDim + tid] = __float2half_rn(num / den);
+        }
         return;
     }
     float* part = p.part + (((size_t)m * p.n_heads + h) * p.n_splits + split) * kPartStride;
@@ -490,6 +513,7 @@ __global__ void __launch_bounds__(NT) attn_decode_kernel(const AttnDecodeParams 
         d2 = fmaf(w, __ldcg(all + s * kPartStride + kHeadDim + 1), d2);
     }
     p.out[((size_t)m * p.n_heads + h) * kHeadDim + tid] = n2 / d2;
+    if (p.out_h != nullptr) p.out_h[((size_t)m * p.n_heads + h) * kHeadDim + tid] = __float2half_rn(n2 / d2);
 }
 
 static bool attn_cluster_enabled() {

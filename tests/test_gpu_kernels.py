@@ -147,3 +147,36 @@ def test_gemm_tcgen05_fp16_operands(lib, M, N, K):
     ref = (a.double() @ w.double().t()).float()
     assert not torch.isnan(out).any()
     assert rel_l2(out, ref) < 3e-5  # exact fp16 x fp16 products, fp32 accumulation
+
+
+@pytest.mark.parametrize("M,N,K,split", [
+    (9, 128, 64, 1), (16, 256, 512, 2), (17, 384, 1024, 4), (32, 4096, 4096, 8), (32, 4096, 11008, 8), (24, 12288, 4096, 0),
+    (32, 22016, 4096, 0), (12, 200, 320, 1), (32, 32000, 4096, 0), (1, 128, 4096, 8), (31, 4096, 11008, 0)])
+def test_gemm_stream_tensor_core(lib, M, N, K, split):
+    """The weight-streaming tcgen05 GEMM of batched decode (9..32 rows): weight tile as the 128-row operand, split-K over
+    a cluster reduced through distributed shared memory; ragged N (200) and K (320 = 5 k-steps) included."""
+    from llm_sharding_b200 import _lib
+    g = torch.Generator(device="cuda").manual_seed(M * 7 + N + K + split)
+    x = torch.randn(M, K, device="cuda", generator=g).half()
+    w = (torch.randn(N, K, device="cuda", generator=g) * 0.05).bfloat16().half()
+    out = torch.full((M, N), float("nan"), device="cuda")
+    for _ in range(2):  # twice: the second launch meets whatever the first left in shared memory / TMEM
+        _lib.check(lib.b200_gemm_stream_f16(x.data_ptr(), w.data_ptr(), M, N, K, split, out.data_ptr(), _st()))
+    torch.cuda.synchronize()
+    ref = (x.double() @ w.double().t()).float()
+    assert not torch.isnan(out).any()
+    assert rel_l2(out, ref) < 3e-5  # exact fp16 x fp16 products, fp32 accumulation
+    out2 = torch.empty_like(out)
+    _lib.check(lib.b200_gemm_stream_f16(x.data_ptr(), w.data_ptr(), M, N, K, split, out2.data_ptr(), _st()))
+    torch.cuda.synchronize()
+    assert torch.equal(out, out2)   # the split-K sum runs in rank order: bit-reproducible
+
+
+def test_gemm_stream_rejects_bad_arguments(lib):
+    from llm_sharding_b200 import _lib
+    x = torch.zeros(40, 64, device="cuda").half()
+    w = torch.zeros(128, 64, device="cuda").half()
+    out = torch.zeros(40, 128, device="cuda")
+    for args in ((33, 128, 64, 1), (4, 128, 60, 1), (4, 128, 32, 1), (4, 128, 64, 3), (4, 128, 64, 2)):
+        with pytest.raises(ValueError):
+            _lib.check(lib.b200_gemm_stream_f16(x.data_ptr(), w.data_ptr(), *args, out.data_ptr(), _st()))

@@ -70,7 +70,10 @@ def _oracle(preset, seed, splits, ids, n_new, causal=False):
     ("tiny", 101, [(0, 4)], 1, 1, 3, False),        # single-token prompt: GEMV path from the first call
     ("tiny", 102, [(0, 2), (2, 4)], 4, 1, 3, False),  # B=4 rows, all on the weight-streaming path
     ("tiny", 103, [(0, 4)], 6, 5, 4, False),        # B=6: prefill on the tcgen05 GEMM, decode on the tensor-core GEMV (2..8 rows)
-    ("tiny", 111, [(0, 2), (2, 4)], 9, 2, 3, False),  # B=9: decode too goes through the tcgen05 GEMM + tiled attention
+    ("tiny", 111, [(0, 2), (2, 4)], 9, 2, 3, False),  # B=9: decode on the weight-streaming tcgen05 GEMM (9..32 rows) + split-K attention
+    ("tiny", 112, [(0, 4)], 32, 3, 4, False),         # B=32: the widest batch of that path (BASELINE configs[2]'s batch 32 in one call)
+    ("gqa", 113, [(0, 2), (2, 4)], 17, 5, 3, True),   # 17 rows (32-column operand, 15 padded), GQA, causal
+    ("small", 114, [(0, 6)], 12, 70, 3, False),       # 12 rows (16-column operand) with the context crossing a page
     ("tiny", 104, [(0, 2), (2, 4)], 2, 70, 3, True),  # causal masking, prompt crossing a 64-token page
     ("tiny", 105, [(0, 4)], 1, 127, 4, False),      # decode steps cross the 128-token page boundary
     ("small", 106, [(0, 2), (2, 6)], 3, 33, 3, True),
