@@ -398,36 +398,62 @@ __global__ void __launch_bounds__(NT) attn_decode_kernel(const AttnDecodeParams 
     }
     float m_run = -INFINITY, l_run = 0.f;
     float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-    // trip count is uniform across the CTA (the shuffles below need every lane of the warp); validity is per key
+    auto load_key = [&](int u, int t) {
+        const int64_t off = kv_offset(t);
+        kk[u] = *reinterpret_cast<const uint4*>(p.k_pool + off);
+        vv[u] = *reinterpret_cast<const uint4*>(p.v_pool + off);
+    };
+    // the keys of the first window that could not be requested before the wait (this call's own tokens)
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+        const int t = t0 + grp + NG * u;
+        if (t >= t_old && t < t1) load_key(u, t);
+    }
+    // Keys are consumed in half-windows of HB = 4: the four dot products and their 16-lane reductions are independent
+    // (instruction-level parallelism for a kernel that runs at low occupancy), the softmax state is updated once per
+    // half-window (one rescale of the accumulator instead of four), and as soon as a half-window is consumed its
+    // registers are refilled with the keys of the next pass, so loads stay in flight while the other half is computed.
+    // Trip counts are uniform across the CTA (the shuffles need every lane of the warp); validity is per key.
+    constexpr int HB = 4;
     for (int tb0 = t0; tb0 < t1; tb0 += NG * U) {
         const int tb = tb0 + grp;
 #pragma unroll
-        for (int u = 0; u < U; ++u) {
-            const int t = tb + NG * u;
-            const bool have = (tb0 == t0) && (t < t_old);  // already requested before the wait
-            if (t < t1 && !have) {
-                const int64_t off = kv_offset(t);
-                kk[u] = *reinterpret_cast<const uint4*>(p.k_pool + off);
-                vv[u] = *reinterpret_cast<const uint4*>(p.v_pool + off);
-            }
-        }
+        for (int hb = 0; hb < U; hb += HB) {
+            float d[HB];
 #pragma unroll
-        for (int u = 0; u < U; ++u) {
-            float d = dot8(kk[u], q);
-            d += __shfl_xor_sync(0xffffffffu, d, 8);
-            d += __shfl_xor_sync(0xffffffffu, d, 4);
-            d += __shfl_xor_sync(0xffffffffu, d, 2);
-            d += __shfl_xor_sync(0xffffffffu, d, 1);
-            if (tb + NG * u < t1) {  // uniform within the half-warp; no shuffles inside
-                const float m_new = fmaxf(m_run, d);
-                const float alpha = exp2f(m_run - m_new), w = exp2f(d - m_new);
-                l_run = l_run * alpha + w;
-                const uint4 v = vv[u];
-                acc[0] = fmaf(w, bf_lo(v.x), acc[0] * alpha); acc[1] = fmaf(w, bf_hi(v.x), acc[1] * alpha);
-                acc[2] = fmaf(w, bf_lo(v.y), acc[2] * alpha); acc[3] = fmaf(w, bf_hi(v.y), acc[3] * alpha);
-                acc[4] = fmaf(w, bf_lo(v.z), acc[4] * alpha); acc[5] = fmaf(w, bf_hi(v.z), acc[5] * alpha);
-                acc[6] = fmaf(w, bf_lo(v.w), acc[6] * alpha); acc[7] = fmaf(w, bf_hi(v.w), acc[7] * alpha);
+            for (int i = 0; i < HB; ++i) d[i] = dot8(kk[hb + i], q);
+#pragma unroll
+            for (int o = 8; o > 0; o >>= 1)
+#pragma unroll
+                for (int i = 0; i < HB; ++i) d[i] += __shfl_xor_sync(0xffffffffu, d[i], o);
+            float bmax = -INFINITY;
+#pragma unroll
+            for (int i = 0; i < HB; ++i)
+                if (tb + NG * (hb + i) < t1) bmax = fmaxf(bmax, d[i]);
+            if (bmax > -INFINITY) {  // uniform within the half-warp; no shuffles inside
+                const float m_new = fmaxf(m_run, bmax);
+                const float alpha = exp2f(m_run - m_new);
+                l_run *= alpha;
+#pragma unroll
+                for (int e = 0; e < 8; ++e) acc[e] *= alpha;
+#pragma unroll
+                for (int i = 0; i < HB; ++i) {
+                    if (tb + NG * (hb + i) < t1) {
+                        const float w = exp2f(d[i] - m_new);
+                        l_run += w;
+                        const uint4 v = vv[hb + i];
+                        acc[0] = fmaf(w, bf_lo(v.x), acc[0]); acc[1] = fmaf(w, bf_hi(v.x), acc[1]);
+                        acc[2] = fmaf(w, bf_lo(v.y), acc[2]); acc[3] = fmaf(w, bf_hi(v.y), acc[3]);
+                        acc[4] = fmaf(w, bf_lo(v.z), acc[4]); acc[5] = fmaf(w, bf_hi(v.z), acc[5]);
+                        acc[6] = fmaf(w, bf_lo(v.w), acc[6]); acc[7] = fmaf(w, bf_hi(v.w), acc[7]);
+                    }
+                }
                 m_run = m_new;
+            }
+#pragma unroll
+            for (int i = 0; i < HB; ++i) {  // refill: the same positions of the next pass
+                const int t = tb + NG * (hb + i) + NG * U;
+                if (t < t1) load_key(hb + i, t);
             }
         }
     }
