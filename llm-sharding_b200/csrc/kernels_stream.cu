@@ -326,16 +326,35 @@ void launch_pack_gate_up(const void* src, int dtype, void* dst, int rows, int co
 constexpr int kAttnThreads = 128;
 constexpr int kPartStride = kHeadDim + 2;
 
-__device__ __forceinline__ float dot8(const uint4& k, const float (&q)[8]) {
-    float d = bf_lo(k.x) * q[0];
-    d = fmaf(bf_hi(k.x), q[1], d);
-    d = fmaf(bf_lo(k.y), q[2], d);
-    d = fmaf(bf_hi(k.y), q[3], d);
-    d = fmaf(bf_lo(k.z), q[4], d);
-    d = fmaf(bf_hi(k.z), q[5], d);
-    d = fmaf(bf_lo(k.w), q[6], d);
-    d = fmaf(bf_hi(k.w), q[7], d);
+// Blackwell's packed fp32 pipe: one instruction, two independent fp32 FMAs (same rounding as two scalar FMAs).  A bf16
+// pair unpacks straight into such a register pair: (v << 16, v & 0xffff0000).
+__device__ __forceinline__ uint64_t f32x2(float lo, float hi) {
+    uint64_t r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ uint64_t bf16x2_to_f32x2(uint32_t v) { return f32x2(bf_lo(v), bf_hi(v)); }
+__device__ __forceinline__ uint64_t fma2(uint64_t a, uint64_t b, uint64_t c) {
+    uint64_t d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
     return d;
+}
+__device__ __forceinline__ uint64_t mul2(uint64_t a, uint64_t b) {
+    uint64_t d;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+__device__ __forceinline__ float sum2(uint64_t v) {
+    float lo, hi;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+    return lo + hi;
+}
+__device__ __forceinline__ float dot8(const uint4& k, const uint64_t (&q2)[4]) {
+    uint64_t d = mul2(bf16x2_to_f32x2(k.x), q2[0]);
+    d = fma2(bf16x2_to_f32x2(k.y), q2[1], d);
+    d = fma2(bf16x2_to_f32x2(k.z), q2[2], d);
+    d = fma2(bf16x2_to_f32x2(k.w), q2[3], d);
+    return sum2(d);
 }
 
 // CLUSTER = true: the n_splits CTAs of one (m, h) form a thread-block cluster (n_splits == kAttnCluster); the partials
@@ -370,9 +389,14 @@ __global__ void __launch_bounds__(NT) attn_decode_kernel(const AttnDecodeParams 
     // completed before the predecessor could even start its own dependent part.
     const int t_old = (p.call_base != nullptr) ? min(t1, p.call_base[b]) : 0;
     constexpr int U = 8;  // keys in flight per half-warp
+    // power-of-two page sizes (the usual 64) index with a shift and a mask instead of two integer divisions per key
+    const int page_shift = (p.page_size & (p.page_size - 1)) == 0 ? 31 - __clz(p.page_size) : -1;
+    const int64_t lane_base = kvh * head_stride + l16 * 8;
     auto kv_offset = [&](int t) -> int64_t {
-        const int page = bt[t / p.page_size];
-        return page * page_stride + kvh * head_stride + (int64_t)(t % p.page_size) * kHeadDim + l16 * 8;
+        int pi, in_page;
+        if (page_shift >= 0) { pi = t >> page_shift; in_page = t & (p.page_size - 1); }
+        else { pi = t / p.page_size; in_page = t - pi * p.page_size; }
+        return bt[pi] * page_stride + lane_base + (int64_t)in_page * kHeadDim;
     };
     uint4 kk[U], vv[U];
 #pragma unroll
@@ -389,15 +413,15 @@ __global__ void __launch_bounds__(NT) attn_decode_kernel(const AttnDecodeParams 
     }
     asm volatile("griddepcontrol.wait;" ::: "memory");            // q and the new K/V come from the previous kernel
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-    float q[8];
+    uint64_t q[4];  // the lane's 8 query values, pre-scaled, as four fp32 pairs
     {
         const float4* qp = reinterpret_cast<const float4*>(p.q + ((size_t)m * p.n_heads + h) * kHeadDim + l16 * 8);
         const float4 a = qp[0], c = qp[1];
-        q[0] = a.x * scale_log2; q[1] = a.y * scale_log2; q[2] = a.z * scale_log2; q[3] = a.w * scale_log2;
-        q[4] = c.x * scale_log2; q[5] = c.y * scale_log2; q[6] = c.z * scale_log2; q[7] = c.w * scale_log2;
+        q[0] = f32x2(a.x * scale_log2, a.y * scale_log2); q[1] = f32x2(a.z * scale_log2, a.w * scale_log2);
+        q[2] = f32x2(c.x * scale_log2, c.y * scale_log2); q[3] = f32x2(c.z * scale_log2, c.w * scale_log2);
     }
     float m_run = -INFINITY, l_run = 0.f;
-    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    uint64_t acc2[4] = {0ull, 0ull, 0ull, 0ull};  // 8 fp32 accumulators as four pairs (bit pattern 0 = +0.0f)
     auto load_key = [&](int u, int t) {
         const int64_t off = kv_offset(t);
         kk[u] = *reinterpret_cast<const uint4*>(p.k_pool + off);
@@ -434,18 +458,20 @@ __global__ void __launch_bounds__(NT) attn_decode_kernel(const AttnDecodeParams 
                 const float m_new = fmaxf(m_run, bmax);
                 const float alpha = exp2f(m_run - m_new);
                 l_run *= alpha;
+                const uint64_t alpha2 = f32x2(alpha, alpha);
 #pragma unroll
-                for (int e = 0; e < 8; ++e) acc[e] *= alpha;
+                for (int e = 0; e < 4; ++e) acc2[e] = mul2(acc2[e], alpha2);
 #pragma unroll
                 for (int i = 0; i < HB; ++i) {
                     if (tb + NG * (hb + i) < t1) {
                         const float w = exp2f(d[i] - m_new);
                         l_run += w;
                         const uint4 v = vv[hb + i];
-                        acc[0] = fmaf(w, bf_lo(v.x), acc[0]); acc[1] = fmaf(w, bf_hi(v.x), acc[1]);
-                        acc[2] = fmaf(w, bf_lo(v.y), acc[2]); acc[3] = fmaf(w, bf_hi(v.y), acc[3]);
-                        acc[4] = fmaf(w, bf_lo(v.z), acc[4]); acc[5] = fmaf(w, bf_hi(v.z), acc[5]);
-                        acc[6] = fmaf(w, bf_lo(v.w), acc[6]); acc[7] = fmaf(w, bf_hi(v.w), acc[7]);
+                        const uint64_t w2 = f32x2(w, w);
+                        acc2[0] = fma2(w2, bf16x2_to_f32x2(v.x), acc2[0]);
+                        acc2[1] = fma2(w2, bf16x2_to_f32x2(v.y), acc2[1]);
+                        acc2[2] = fma2(w2, bf16x2_to_f32x2(v.z), acc2[2]);
+                        acc2[3] = fma2(w2, bf16x2_to_f32x2(v.w), acc2[3]);
                     }
                 }
                 m_run = m_new;
@@ -458,6 +484,9 @@ __global__ void __launch_bounds__(NT) attn_decode_kernel(const AttnDecodeParams 
         }
     }
     // ---- merge the half-warp partials of this CTA
+    float acc[8];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) asm("mov.b64 {%0, %1}, %2;" : "=f"(acc[2 * e]), "=f"(acc[2 * e + 1]) : "l"(acc2[e]));
 #pragma unroll
     for (int e = 0; e < 8; ++e) g_acc[grp][l16 * 8 + e] = acc[e];
     if (l16 == 0) { g_m[grp] = m_run; g_l[grp] = l_run; }
