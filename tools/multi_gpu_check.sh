@@ -15,10 +15,12 @@ if [ "$N" = "2" ]; then
   timeout 300 python -m pytest tests/test_gpu_chain.py -q -m gpu -x 2>&1 | grep -E "passed|failed|rror" | tail -3
   run bench_n2 2 --steps 128 --warmup 4
   run bench_n2_c4 2 --streams 8 --rows 2 --prompt-len 2048 --steps 16 --warmup 3
+  run bench_n2_c3_batch32 2 --streams 2 --rows 16 --prompt-len 128 --steps 128 --warmup 4
 fi
 if [ "$N" = "4" ]; then
   run bench_n3_c5_mixed 3 --splits 4,12,16 --mixed --steps 96 --warmup 4
   run bench_n4 4 --steps 128 --warmup 4
+  run bench_n4_c3_batch32 4 --streams 4 --rows 8 --prompt-len 128 --steps 128 --warmup 4
 fi
 if [ "$N" = "8" ]; then
   run bench_n8 8 --steps 128 --warmup 4
