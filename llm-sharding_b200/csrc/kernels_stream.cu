@@ -357,11 +357,99 @@ __device__ __forceinline__ float dot8(const uint4& k, const uint64_t (&q2)[4]) {
     return sum2(d);
 }
 
+constexpr int kAttnCluster = 8;
+constexpr int kAttnClusterThreads = 256;
+
+// Merge of the NG group partials of one CTA (g_acc / g_m / g_l, already published with __syncthreads) and of the n_splits
+// CTAs of one (row, head): over distributed shared memory inside a cluster, through global scratch + arrival ticket
+// otherwise, or not at all when the CTA saw every key.  Shared by the CUDA-core and the tensor-core kernels.
+template <int NG, bool CLUSTER>
+__device__ __forceinline__ void attn_decode_merge(const AttnDecodeParams& p, const float (*g_acc)[kHeadDim], const float* g_m,
+                                                  const float* g_l, float (*c_part)[kPartStride], int& s_last, int split, int h,
+                                                  int m, int tid) {
+    float num = 0.f, den = 0.f, mx = -INFINITY;
+    if (tid < kHeadDim) {
+#pragma unroll
+        for (int g = 0; g < NG; ++g) mx = fmaxf(mx, g_m[g]);
+#pragma unroll
+        for (int g = 0; g < NG; ++g) {
+            const float w = (g_m[g] == -INFINITY) ? 0.f : exp2f(g_m[g] - mx);
+            num = fmaf(w, g_acc[g][tid], num);
+            den = fmaf(w, g_l[g], den);
+        }
+    }
+    if (CLUSTER) {
+        uint32_t rank;
+        asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
+        if (tid < kHeadDim) {
+            uint32_t dst;
+            asm volatile("mapa.shared::cluster.u32 %0, %1, 0;" : "=r"(dst) : "r"((uint32_t)__cvta_generic_to_shared(&c_part[rank][0])));
+            asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(dst + 4u * (uint32_t)tid), "f"(num) : "memory");
+            if (tid == 0) {
+                asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(dst + 4u * kHeadDim), "f"(mx) : "memory");
+                asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(dst + 4u * (kHeadDim + 1)), "f"(den) : "memory");
+            }
+        }
+        // every thread of every CTA of the cluster arrives (empty splits included); rank 0 outlives all remote stores
+        asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+        asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+        if (rank != 0 || tid >= kHeadDim) return;
+        float gmx = -INFINITY;
+#pragma unroll
+        for (int s = 0; s < kAttnCluster; ++s) gmx = fmaxf(gmx, c_part[s][kHeadDim]);
+        float n2 = 0.f, d2 = 0.f;
+#pragma unroll
+        for (int s = 0; s < kAttnCluster; ++s) {
+            const float pm = c_part[s][kHeadDim];
+            const float w = (pm == -INFINITY) ? 0.f : exp2f(pm - gmx);
+            n2 = fmaf(w, c_part[s][tid], n2);
+            d2 = fmaf(w, c_part[s][kHeadDim + 1], d2);
+        }
+        p.out[((size_t)m * p.n_heads + h) * kHeadDim + tid] = n2 / d2;
+        if (p.out_h != nullptr) p.out_h[((size_t)m * p.n_heads + h) * kHeadDim + tid] = __float2half_rn(n2 / d2);
+        return;
+    }
+    if (p.n_splits == 1) {  // the CTA saw every key of its (row, head): nothing to merge (many rows: one CTA per row and head)
+        if (tid < kHeadDim) {
+            p.out[((size_t)m * p.n_heads + h) * kHeadDim + tid] = num / den;
+            if (p.out_h != nullptr) p.out_h[((size_t)m * p.n_heads + h) * kHeadDim + tid] = __float2half_rn(num / den);
+        }
+        return;
+    }
+    float* part = p.part + (((size_t)m * p.n_heads + h) * p.n_splits + split) * kPartStride;
+    if (tid < kHeadDim) {
+        part[tid] = num;
+        if (tid == 0) { part[kHeadDim] = mx; part[kHeadDim + 1] = den; }
+    }
+    // ---- the last CTA of this (m, h) to finish merges the splits
+    unsigned int* ticket = p.tickets + ((size_t)m * p.n_heads + h);
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) {
+        const unsigned int prev = atomicAdd(ticket, 1u);
+        s_last = (prev == (unsigned int)p.n_splits - 1u);
+        if (s_last) *ticket = 0u;  // ready for the next launch (graph replays included)
+    }
+    __syncthreads();
+    if (!s_last || tid >= kHeadDim) return;
+    __threadfence();
+    const float* all = p.part + ((size_t)m * p.n_heads + h) * p.n_splits * kPartStride;
+    float gmx = -INFINITY;
+    for (int s = 0; s < p.n_splits; ++s) gmx = fmaxf(gmx, __ldcg(all + s * kPartStride + kHeadDim));
+    float n2 = 0.f, d2 = 0.f;
+    for (int s = 0; s < p.n_splits; ++s) {
+        const float pm = __ldcg(all + s * kPartStride + kHeadDim);
+        const float w = (pm == -INFINITY) ? 0.f : exp2f(pm - gmx);
+        n2 = fmaf(w, __ldcg(all + s * kPartStride + tid), n2);
+        d2 = fmaf(w, __ldcg(all + s * kPartStride + kHeadDim + 1), d2);
+    }
+    p.out[((size_t)m * p.n_heads + h) * kHeadDim + tid] = n2 / d2;
+    if (p.out_h != nullptr) p.out_h[((size_t)m * p.n_heads + h) * kHeadDim + tid] = __float2half_rn(n2 / d2);
+}
+
 // CLUSTER = true: the n_splits CTAs of one (m, h) form a thread-block cluster (n_splits == kAttnCluster); the partials
 // travel to cluster rank 0 through distributed shared memory and one hardware cluster barrier replaces the global
 // scratch round trip (store, fence, atomic ticket, reload) — the longest links of this latency-bound kernel's chain.
-constexpr int kAttnCluster = 8;
-constexpr int kAttnClusterThreads = 256;
 
 template <int NT, bool CLUSTER>
 __global__ void __launch_bounds__(NT) attn_decode_kernel(const AttnDecodeParams p) {
@@ -491,84 +579,7 @@ __global__ void __launch_bounds__(NT) attn_decode_kernel(const AttnDecodeParams 
     for (int e = 0; e < 8; ++e) g_acc[grp][l16 * 8 + e] = acc[e];
     if (l16 == 0) { g_m[grp] = m_run; g_l[grp] = l_run; }
     __syncthreads();
-    float num = 0.f, den = 0.f, mx = -INFINITY;
-    if (tid < kHeadDim) {
-#pragma unroll
-        for (int g = 0; g < NG; ++g) mx = fmaxf(mx, g_m[g]);
-#pragma unroll
-        for (int g = 0; g < NG; ++g) {
-            const float w = (g_m[g] == -INFINITY) ? 0.f : exp2f(g_m[g] - mx);
-            num = fmaf(w, g_acc[g][tid], num);
-            den = fmaf(w, g_l[g], den);
-        }
-    }
-    if (CLUSTER) {
-        uint32_t rank;
-        asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
-        if (tid < kHeadDim) {
-            uint32_t dst;
-            asm volatile("mapa.shared::cluster.u32 %0, %1, 0;" : "=r"(dst) : "r"((uint32_t)__cvta_generic_to_shared(&c_part[rank][0])));
-            asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(dst + 4u * (uint32_t)tid), "f"(num) : "memory");
-            if (tid == 0) {
-                asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(dst + 4u * kHeadDim), "f"(mx) : "memory");
-                asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(dst + 4u * (kHeadDim + 1)), "f"(den) : "memory");
-            }
-        }
-        // every thread of every CTA of the cluster arrives (empty splits included); rank 0 outlives all remote stores
-        asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
-        asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
-        if (rank != 0 || tid >= kHeadDim) return;
-        float gmx = -INFINITY;
-#pragma unroll
-        for (int s = 0; s < kAttnCluster; ++s) gmx = fmaxf(gmx, c_part[s][kHeadDim]);
-        float n2 = 0.f, d2 = 0.f;
-#pragma unroll
-        for (int s = 0; s < kAttnCluster; ++s) {
-            const float pm = c_part[s][kHeadDim];
-            const float w = (pm == -INFINITY) ? 0.f : exp2f(pm - gmx);
-            n2 = fmaf(w, c_part[s][tid], n2);
-            d2 = fmaf(w, c_part[s][kHeadDim + 1], d2);
-        }
-        p.out[((size_t)m * p.n_heads + h) * kHeadDim + tid] = n2 / d2;
-        if (p.out_h != nullptr) p.out_h[((size_t)m * p.n_heads + h) * kHeadDim + tid] = __float2half_rn(n2 / d2);
-        return;
-    }
-    if (p.n_splits == 1) {  // the CTA saw every key of its (row, head): nothing to merge (many rows: one CTA per row and head)
-        if (tid < kHeadDim) {
-            p.out[((size_t)m * p.n_heads + h) * kHeadDim + tid] = num / den;
-            if (p.out_h != nullptr) p.out_h[((size_t)m * p.n_heads + h) * kHeadDim + tid] = __float2half_rn(num / den);
-        }
-        return;
-    }
-    float* part = p.part + (((size_t)m * p.n_heads + h) * p.n_splits + split) * kPartStride;
-    if (tid < kHeadDim) {
-        part[tid] = num;
-        if (tid == 0) { part[kHeadDim] = mx; part[kHeadDim + 1] = den; }
-    }
-    // ---- the last CTA of this (m, h) to finish merges the splits
-    unsigned int* ticket = p.tickets + ((size_t)m * p.n_heads + h);
-    __threadfence();
-    __syncthreads();
-    if (tid == 0) {
-        const unsigned int prev = atomicAdd(ticket, 1u);
-        s_last = (prev == (unsigned int)p.n_splits - 1u);
-        if (s_last) *ticket = 0u;  // ready for the next launch (graph replays included)
-    }
-    __syncthreads();
-    if (!s_last || tid >= kHeadDim) return;
-    __threadfence();
-    const float* all = p.part + ((size_t)m * p.n_heads + h) * p.n_splits * kPartStride;
-    float gmx = -INFINITY;
-    for (int s = 0; s < p.n_splits; ++s) gmx = fmaxf(gmx, __ldcg(all + s * kPartStride + kHeadDim));
-    float n2 = 0.f, d2 = 0.f;
-    for (int s = 0; s < p.n_splits; ++s) {
-        const float pm = __ldcg(all + s * kPartStride + kHeadDim);
-        const float w = (pm == -INFINITY) ? 0.f : exp2f(pm - gmx);
-        n2 = fmaf(w, __ldcg(all + s * kPartStride + tid), n2);
-        d2 = fmaf(w, __ldcg(all + s * kPartStride + kHeadDim + 1), d2);
-    }
-    p.out[((size_t)m * p.n_heads + h) * kHeadDim + tid] = n2 / d2;
-    if (p.out_h != nullptr) p.out_h[((size_t)m * p.n_heads + h) * kHeadDim + tid] = __float2half_rn(n2 / d2);
+    attn_decode_merge<NG, CLUSTER>(p, g_acc, g_m, g_l, c_part, s_last, split, h, m, tid);
 }
 
 static bool attn_cluster_enabled() {

@@ -85,8 +85,9 @@ def _paged_kv(rows, n_kv, T_list, page_size, g):
     """random K/V written into a shuffled page pool; returns pools, block table, dense copies"""
     max_pages = max((t + page_size - 1) // page_size for t in T_list)
     n_pages = rows * max_pages + 3
-    k_pool = torch.zeros(n_pages, n_kv, page_size, 128, device="cuda", dtype=torch.bfloat16)
-    v_pool = torch.zeros_like(k_pool)
+    # rows the sequences never wrote hold NaN: a kernel that lets them leak into a sum (0 x NaN inside an MMA) is caught
+    k_pool = torch.full((n_pages, n_kv, page_size, 128), float("nan"), device="cuda", dtype=torch.bfloat16)
+    v_pool = torch.full_like(k_pool, float("nan"))
     perm = torch.randperm(n_pages, generator=torch.Generator().manual_seed(7)).tolist()
     bt = torch.full((rows, max_pages), -1, dtype=torch.int32)
     dense = []

@@ -17,6 +17,7 @@ def main():
     ap.add_argument("--context", type=int, default=128)
     ap.add_argument("--rows", default="1,4,8,9,16,32")
     ap.add_argument("--steps", type=int, default=64)
+    ap.add_argument("--page-size", type=int, default=64)
     a = ap.parse_args()
     from llm_sharding_b200 import synthetic
     from llm_sharding_b200.engine import Shard, read_model_config
@@ -32,7 +33,7 @@ def main():
     H = cfg["hidden_size"]
     w_bytes = 202383360 * 2
     for B in rows_list:
-        kv = sh.new_kv(max_slots=B, max_seq_len=a.context + a.steps + 80)
+        kv = sh.new_kv(max_slots=B, page_size=a.page_size, max_seq_len=a.context + a.steps + 80)
         x = (torch.randn(B, a.context, H, device="cuda") * 0.1).bfloat16()
         sh.forward(x, kv, list(range(B)))
         step = (torch.randn(B, 1, H, device="cuda") * 0.1).bfloat16()
