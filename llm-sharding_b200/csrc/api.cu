@@ -323,7 +323,14 @@ static int attn_splits(const b200_shard* s, const b200_kv* kv, int M) {
     if (forced > 0 && M <= kMaxGemvRows) ns = forced;
     const int ns_cap = (kv->dev.max_pages_per_slot * kv->dev.page_size + kMaxChunkKeys - 1) / kMaxChunkKeys;
     if (ns < ns_cap) ns = ns_cap;
-    return ns < 1 ? 1 : (ns > kMaxSplits ? kMaxSplits : ns);
+    ns = ns < 1 ? 1 : (ns > kMaxSplits ? kMaxSplits : ns);
+    // long-context caches force a minimum split count: if that no longer fits the scratch, the cluster variant needs none
+    if ((int64_t)ns * M > kMaxGemvRows * kMaxSplits && ns <= 8 && attn_decode_cluster_splits() > 0) ns = attn_decode_cluster_splits();
+    return ns;
+}
+// does the split-K scratch (8 rows x 16 splits of partials per head) hold this call?  The cluster variant uses none.
+static bool attn_scratch_fits(int M, int ns) {
+    return (ns == attn_decode_cluster_splits() && ns > 0) || ns == 1 || (int64_t)ns * M <= kMaxGemvRows * kMaxSplits;
 }
 
 static bool stream_gemm_enabled() {  // B200SHARD_STREAM_GEMM=0: 9..32-row decode takes the 128 x 128 tile GEMMs instead (A/B)
@@ -393,7 +400,8 @@ static int enqueue_forward(b200_shard_t* s, b200_kv_t* kv, const SlotList& sl, c
     launch_load_residual(reinterpret_cast<const __nv_bfloat16*>(in), s->x, (int64_t)M * H, st);
     s->n_launch += 3;
     const bool gemv_path = M <= gemv_row_limit(s);
-    const bool stream_path = !gemv_path && M <= kMaxStreamRows && stream_gemm_enabled() && H % 64 == 0 && I % 64 == 0;
+    const bool stream_path = !gemv_path && M <= kMaxStreamRows && stream_gemm_enabled() && H % 64 == 0 && I % 64 == 0 &&
+                             attn_scratch_fits(M, attn_splits(s, kv, M));
     for (int l = 0; l < c.n_layers; ++l) {
         const LayerW& L = s->layers[l];
         __nv_bfloat16* kp = kv->k_pool + (int64_t)l * kv->layer_stride;
