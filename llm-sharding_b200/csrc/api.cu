@@ -321,12 +321,9 @@ static int attn_splits(const b200_shard* s, const b200_kv* kv, int M) {
         if (ns >= 8) ns = attn_decode_cluster_splits() > 0 ? 8 : ns;
     }
     if (forced > 0 && M <= kMaxGemvRows) ns = forced;
-    const int ns_cap = (kv->dev.max_pages_per_slot * kv->dev.page_size + kMaxChunkKeys - 1) / kMaxChunkKeys;
-    if (ns < ns_cap) ns = ns_cap;
-    ns = ns < 1 ? 1 : (ns > kMaxSplits ? kMaxSplits : ns);
-    // long-context caches force a minimum split count: if that no longer fits the scratch, the cluster variant needs none
-    if ((int64_t)ns * M > kMaxGemvRows * kMaxSplits && ns <= 8 && attn_decode_cluster_splits() > 0) ns = attn_decode_cluster_splits();
-    return ns;
+    // (the online-softmax kernel streams any number of keys per CTA: no minimum split count follows from the context length)
+    (void)kv;
+    return ns < 1 ? 1 : (ns > kMaxSplits ? kMaxSplits : ns);
 }
 // does the split-K scratch (8 rows x 16 splits of partials per head) hold this call?  The cluster variant uses none.
 static bool attn_scratch_fits(int M, int ns) {
