@@ -84,6 +84,56 @@ def test_finish_keeps_the_ring_counts_aligned_under_a_mixed_schedule():
         scheds[0].finish(0)
 
 
+@pytest.mark.parametrize("seed", range(8))
+def test_random_round_robin_schedules_keep_the_ring_consistent(seed):
+    """Property test: any schedule in which the live streams take turns in a fixed order — each turn being a decode, a
+    finish, or a finish followed at once by a new prefill, with idle streams re-entering at any time — keeps every
+    hop's FIFO, stream and mailbox-slot bookkeeping consistent on every stage, for several ring sizes."""
+    import random
+    rng = random.Random(seed)
+    world, n_streams = rng.choice([1, 2, 3, 5, 8]), rng.choice([1, 2, 3, 4, 7])
+    scheds = [RingSchedule(r, world, n_streams) for r in range(world)]
+    queues = [[] for _ in range(world)]
+
+    def run(kind, stream):
+        for r in range(world):
+            it = getattr(scheds[r], kind)(stream)
+            if it["wait"] is not None:
+                assert queues[(r - 1) % world], (kind, stream, r, "nothing to consume")
+                seq_slot, st = queues[(r - 1) % world].pop(0)
+                assert seq_slot == it["wait"] and st == stream, (kind, stream, r)
+            if it["send"] is not None:
+                q = queues[r]
+                q.append((it["send"], stream))
+                assert len({slot for (_, slot), _ in q}) == len(q) <= n_streams
+    order = []                      # live streams in the order their tokens come back
+    idle = list(range(n_streams))
+    for _ in range(200):
+        if idle and (not order or rng.random() < 0.3):
+            s_new = idle.pop(rng.randrange(len(idle)))
+            run("prefill", s_new)
+            order.append(s_new)
+            continue
+        s_cur = order.pop(0)        # the stream whose token is the oldest one outstanding
+        action = rng.random()
+        if action < 0.7:
+            run("decode", s_cur)
+            order.append(s_cur)
+        elif action < 0.85:
+            run("finish", s_cur)
+            idle.append(s_cur)
+        else:
+            run("finish", s_cur)
+            run("prefill", s_cur)
+            order.append(s_cur)
+        if len(order) > 1:          # any other live stream is refused: its token is not at the head of the FIFO
+            with pytest.raises(RuntimeError):
+                scheds[0].decode(order[-1]) if order[-1] != order[0] else scheds[0].finish(idle[0] if idle else n_streams + 5)
+    # every token still in flight sits in the head's mailbox (the tail -> head hop), one per live stream
+    assert [len(q) for q in queues[:-1]] == [0] * (world - 1)
+    assert len(queues[-1]) == len(order)
+
+
 def _free_port():
     with socket.socket() as s:
         s.bind(("127.0.0.1", 0))
