@@ -222,13 +222,33 @@ __global__ void __launch_bounds__(1024) argmax_kernel(const float* __restrict__ 
                                                       float* margin) {
     __shared__ float sv[32], s2[32];
     __shared__ int si[32];
+    asm volatile("griddepcontrol.wait;" ::: "memory");  // launched programmatically behind the lm_head kernel
     const float* row = logits + (size_t)blockIdx.x * V;
     float best = -INFINITY, second = -INFINITY;
     int bi = 0x7fffffff;
-    for (int i = threadIdx.x; i < V; i += blockDim.x) {
-        const float v = row[i];
+    auto take = [&](float v, int i) {  // a thread visits its indices in increasing order: '>' keeps the first maximum
         if (v > best) { second = best; best = v; bi = i; }
         else if (v > second) second = v;
+    };
+    if ((V & 3) == 0 && (reinterpret_cast<uintptr_t>(row) & 15) == 0) {
+        // one decode step waits on this kernel: 128-bit loads, eight in flight per thread, instead of a chain of scalar ones
+        const float4* row4 = reinterpret_cast<const float4*>(row);
+        const int n4 = V >> 2;
+        for (int i0 = threadIdx.x; i0 < n4; i0 += 8 * (int)blockDim.x) {
+            float4 v[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const int i = i0 + u * (int)blockDim.x;
+                v[u] = (i < n4) ? __ldcg(row4 + i) : make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+            }
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const int i = 4 * (i0 + u * (int)blockDim.x);
+                if (i < V) { take(v[u].x, i); take(v[u].y, i + 1); take(v[u].z, i + 2); take(v[u].w, i + 3); }
+            }
+        }
+    } else {
+        for (int i = threadIdx.x; i < V; i += blockDim.x) take(row[i], i);
     }
     auto merge = [](float& b, int& i, float& s, float ob, int oi, float os) {
         if (ob > b || (ob == b && oi < i)) { s = fmaxf(fmaxf(b, os), s); b = ob; i = oi; }
@@ -263,7 +283,17 @@ __global__ void __launch_bounds__(1024) argmax_kernel(const float* __restrict__ 
     }
 }
 void launch_argmax(const float* logits, int B, int V, int64_t* tok, float* margin, cudaStream_t st) {
-    argmax_kernel<<<B, 1024, 0, st>>>(logits, V, tok, margin);
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(B);
+    cfg.blockDim = dim3(1024);
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    const char* e = getenv("B200SHARD_PDL");
+    cfg.numAttrs = (e != nullptr && e[0] == '0') ? 0 : 1;
+    cudaLaunchKernelEx(&cfg, argmax_kernel, logits, V, tok, margin);
 }
 
 // embed_tokens(ids) (utils/node_worker.py:215,302): row gather, 128-bit copies.
