@@ -91,6 +91,12 @@ B200_API int b200_shard_destroy(b200_shard_t* s);
 B200_API int b200_kv_create(const b200_shard_t* s, int max_slots, int page_size, int n_pages, b200_kv_t** out);
 B200_API int b200_kv_reset(b200_kv_t* kv, int slot /* -1: every slot */, void* stream); /* clear_KV_cache, utils/node_worker.py:319-355 */
 B200_API int b200_kv_seq_len(const b200_kv_t* kv, int slot); /* past_key_value.get_seq_length(), utils/forwarding_utils.py:15-16 */
+/* Sticky device-side error of the page allocator: 0 = none, 1 = page pool exhausted, 2 = slot capacity exceeded.  The host
+ * checks capacity before every call, so this fires only when device state ran ahead of the host mirror (a captured decode
+ * graph replayed more often than the pool allows).  Copies one int from the device (synchronises).  Stands where
+ * torch.cuda.OutOfMemoryError would surface inside DynamicCache.update (transformers cache_utils.py:102-121). */
+B200_API int b200_kv_error(b200_kv_t* kv);
+/* Also destroys every CUDA graph the shard captured against this cache (their nodes point into its pools). */
 B200_API int b200_kv_destroy(b200_kv_t* kv);
 
 /* ---- the hot path: LlamaShardPart.forward (utils/shard_loader.py:57-78) ---------------- */
@@ -133,7 +139,10 @@ B200_API int b200_shard_embed(b200_shard_t* s, const int64_t* d_ids, int n, void
 B200_API int b200_hop_create(int device, int n_ring_slots, int64_t slot_bytes, b200_hop_t** out);
 B200_API int b200_hop_export(b200_hop_t* h, void* h_handle_out /* B200_HOP_HANDLE_BYTES */);
 B200_API int b200_hop_connect(b200_hop_t* h, const void* h_peer_handle, int peer_device, int same_process);
-/* d_payload -> peer mailbox ring slot (seq % n_ring_slots); `seq` must increase by 1 per message. */
+/* d_payload -> peer mailbox ring slot (seq % the PEER's n_ring_slots — the ring geometry travels inside the exported
+ * handle); `seq` must increase by 1 per message.  The ring has no back-pressure: at most n_ring_slots messages may be
+ * un-consumed at any time (the chain runtime guarantees it by giving every request stream its own slot; a token only
+ * re-enters a slot after the previous message of that stream came back around the ring). */
 B200_API int b200_hop_send(b200_hop_t* h, const void* d_payload, int64_t bytes, uint64_t seq, void* stream);
 /* wait (on the GPU) for message `seq` in the local mailbox, copy it to d_out; max_wait_us bounds the spin */
 B200_API int b200_hop_recv(b200_hop_t* h, void* d_out, int64_t bytes, uint64_t seq, int64_t max_wait_us, void* stream);

@@ -45,6 +45,7 @@ PROTOTYPES = {
     "b200_kv_create": (_I, [_P, _I, _I, _I, C.POINTER(_P)]),
     "b200_kv_reset": (_I, [_P, _I, _P]),
     "b200_kv_seq_len": (_I, [_P, _I]),
+    "b200_kv_error": (_I, [_P]),
     "b200_kv_destroy": (_I, [_P]),
     "b200_shard_forward": (_I, [_P, _P, C.POINTER(C.c_int32), _P, _I, _I, _I, _P, _P]),
     "b200_shard_lm_head_argmax": (_I, [_P, _P, _I, _I, _P, _P, _P]),

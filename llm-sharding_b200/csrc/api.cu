@@ -43,13 +43,21 @@ struct LayerW {
     bool set = false;
 };
 
+// A captured graph has the KV pools, block table and length arrays of one b200_kv baked in.  The key therefore names
+// the cache by a process-wide generation number handed out by b200_kv_create — never by its host address, which the heap
+// may hand to the next b200_kv — and b200_kv_destroy drops every graph of that generation.
 struct GraphKey {
-    int B, causal, with_argmax;
+    int B, causal, with_argmax, pad_;
     const void *in, *out, *tok, *margin, *tok_in;
-    const b200_kv* kv;
+    uint64_t kv_gen;
     int32_t slots[kMaxBatch];
     bool operator<(const GraphKey& o) const { return memcmp(this, &o, sizeof(GraphKey)) < 0; }
 };
+struct GraphEntry {
+    cudaGraphExec_t exec = nullptr;
+    uint64_t last_use = 0;
+};
+constexpr size_t kMaxCachedGraphs = 64;  // least-recently-used graphs beyond this are destroyed (callers that pass fresh pointers every step)
 
 struct b200_shard {
     b200_shard_config_t cfg;
@@ -67,12 +75,24 @@ struct b200_shard {
     InvFreq inv{};
     uint64_t n_launch = 0, n_bytes = 0, n_flops = 0, n_calls = 0;
     bool graphs = false;
-    std::map<GraphKey, cudaGraphExec_t> graph_cache;
+    std::map<GraphKey, GraphEntry> graph_cache;
+    uint64_t graph_clock = 0;
     std::vector<void*> allocs;
 };
+static void drop_graphs(b200_shard* s, uint64_t kv_gen /* 0: all */) {
+    for (auto it = s->graph_cache.begin(); it != s->graph_cache.end();) {
+        if (kv_gen == 0 || it->first.kv_gen == kv_gen) {
+            cudaGraphExecDestroy(it->second.exec);
+            it = s->graph_cache.erase(it);
+        } else {
+            ++it;
+        }
+    }
+}
 
 struct b200_kv {
-    const b200_shard* shard = nullptr;
+    b200_shard* shard = nullptr;
+    uint64_t gen = 0;  // unique per b200_kv_create (graph-cache key)
     KvDev dev{};
     __nv_bfloat16 *k_pool = nullptr, *v_pool = nullptr;
     int64_t layer_stride = 0;  // elements per layer in a pool
@@ -160,7 +180,7 @@ extern "C" B200_API int b200_shard_destroy(b200_shard_t* s) {
     if (s == nullptr) return 0;
     cudaSetDevice(s->device);
     cudaDeviceSynchronize();
-    for (auto& kv : s->graph_cache) cudaGraphExecDestroy(kv.second);
+    drop_graphs(s, 0);
     for (void* p : s->allocs) cudaFree(p);
     for (auto& l : s->layers) if (l.slab) cudaFree(l.slab);
     delete s;
@@ -242,8 +262,10 @@ extern "C" B200_API int b200_kv_create(const b200_shard_t* s, int max_slots, int
     if (max_slots < 1 || page_size < 64 || page_size % 64 != 0 || n_pages < 1)
         return fail(B200_EINVAL, "[ERROR] need max_slots >= 1, page_size a multiple of 64, n_pages >= 1");
     CU_TRY(cudaSetDevice(s->device));
+    static uint64_t next_gen = 0;
     b200_kv* kv = new b200_kv();
-    kv->shard = s;
+    kv->shard = const_cast<b200_shard*>(s);
+    kv->gen = __atomic_add_fetch(&next_gen, 1, __ATOMIC_RELAXED);
     KvDev& d = kv->dev;
     d.max_slots = max_slots;
     d.page_size = page_size;
@@ -278,6 +300,7 @@ extern "C" B200_API int b200_kv_destroy(b200_kv_t* kv) {
     if (kv == nullptr) return 0;
     cudaSetDevice(kv->shard->device);
     cudaDeviceSynchronize();
+    drop_graphs(kv->shard, kv->gen);  // their nodes point into the pools freed below
     for (void* p : kv->allocs) cudaFree(p);
     delete kv;
     return 0;
@@ -299,6 +322,16 @@ extern "C" B200_API int b200_kv_reset(b200_kv_t* kv, int slot, void* stream) {
 extern "C" B200_API int b200_kv_seq_len(const b200_kv_t* kv, int slot) {
     if (kv == nullptr || slot < 0 || slot >= kv->dev.max_slots) return fail(B200_EINVAL, "[ERROR] kv slot out of range");
     return kv->h_len[slot];
+}
+
+extern "C" B200_API int b200_kv_error(b200_kv_t* kv) {
+    if (kv == nullptr) return fail(B200_EINVAL, "[ERROR] null kv");
+    int v = 0;
+    CU_TRY(cudaSetDevice(kv->shard->device));
+    CU_TRY(cudaMemcpy(&v, kv->dev.error, sizeof(int), cudaMemcpyDeviceToHost));  // synchronises with the kernels that may set it
+    if (v == 1) g_err = "[ERROR] KV page pool exhausted on the device (a captured graph was replayed past the pool's capacity)";
+    if (v == 2) g_err = "[ERROR] KV slot capacity exceeded on the device";
+    return v;
 }
 
 // ------------------------------------------------------------------------------------- forward
@@ -577,7 +610,7 @@ static int forward_impl(b200_shard_t* s, b200_kv_t* kv, const int32_t* h_slots, 
         GraphKey key;
         memset(&key, 0, sizeof(key));
         key.B = B; key.causal = causal; key.with_argmax = with_tail ? 1 : 0;
-        key.in = in; key.out = out; key.tok = tok; key.margin = margin; key.kv = kv; key.tok_in = tok_in;
+        key.in = in; key.out = out; key.tok = tok; key.margin = margin; key.kv_gen = kv->gen; key.tok_in = tok_in;
         for (int b = 0; b < B; ++b) key.slots[b] = sl.v[b];
         auto it = s->graph_cache.find(key);
         if (it == s->graph_cache.end()) {
@@ -602,9 +635,21 @@ static int forward_impl(b200_shard_t* s, b200_kv_t* kv, const int32_t* h_slots, 
             cudaGraphDestroy(graph);
             cudaStreamDestroy(cs);
             if (ce != cudaSuccess) return fail(B200_ECUDA, "[ERROR] cudaGraphInstantiate failed: %s", cudaGetErrorString(ce));
-            it = s->graph_cache.emplace(key, exec).first;
+            if (s->graph_cache.size() >= kMaxCachedGraphs) {  // evict the least recently used graph
+                auto victim = s->graph_cache.begin();
+                for (auto j = s->graph_cache.begin(); j != s->graph_cache.end(); ++j)
+                    if (j->second.last_use < victim->second.last_use) victim = j;
+                // a replay of the victim may still be running on some stream; destroying an exec waits for nothing, so drain first
+                cudaDeviceSynchronize();
+                cudaGraphExecDestroy(victim->second.exec);
+                s->graph_cache.erase(victim);
+            }
+            GraphEntry ge;
+            ge.exec = exec;
+            it = s->graph_cache.emplace(key, ge).first;
         }
-        CU_TRY(cudaGraphLaunch(it->second, st));
+        it->second.last_use = ++s->graph_clock;
+        CU_TRY(cudaGraphLaunch(it->second.exec, st));
         s->n_launch += 3 + (uint64_t)s->cfg.n_layers * (B <= gemv_row_limit(s) ? 5 : 7) + (out ? 1 : 0) + (with_tail ? (B <= gemv_row_limit(s) ? 2 : 4) : 0) + (tok_in ? 1 : 0);
         done = true;
     }
@@ -734,8 +779,7 @@ extern "C" B200_API int b200_shard_set_rope_inv_freq(b200_shard_t* s, const floa
     if (s == nullptr || h_inv_freq == nullptr) return fail(B200_EINVAL, "[ERROR] null argument");
     if (n != 64) return fail(B200_EINVAL, "[ERROR] inv_freq must have head_dim/2 = 64 entries (got %d)", n);
     for (int j = 0; j < 64; ++j) s->inv.v[j] = h_inv_freq[j];
-    for (auto& g : s->graph_cache) cudaGraphExecDestroy(g.second);  // captured graphs hold the old table by value
-    s->graph_cache.clear();
+    drop_graphs(s, 0);  // captured graphs hold the old table by value
     return 0;
 }
 extern "C" B200_API int b200_shard_set_graphs(b200_shard_t* s, int enabled) {
@@ -759,12 +803,16 @@ struct b200_hop {
 struct HopHandle {  // exactly B200_HOP_HANDLE_BYTES
     cudaIpcMemHandle_t ipc;  // 64 bytes, valid across processes
     char* raw;               // valid inside the exporting process
-    uint64_t has_ipc;
+    uint64_t geom;           // bit 0: ipc handle valid; bits 8..31: ring slots; bits 32..63: slot bytes / 256
 };
+static uint64_t hop_pack_geom(bool has_ipc, int n_slots, int64_t slot_bytes) {
+    return (has_ipc ? 1ull : 0ull) | ((uint64_t)(n_slots & 0xffffff) << 8) | ((uint64_t)(slot_bytes / 256) << 32);
+}
 static_assert(sizeof(HopHandle) == B200_HOP_HANDLE_BYTES, "handle size");
 
 extern "C" B200_API int b200_hop_create(int device, int n_ring_slots, int64_t slot_bytes, b200_hop_t** out) {
-    if (out == nullptr || n_ring_slots < 1 || slot_bytes < 16) return fail(B200_EINVAL, "[ERROR] bad hop arguments");
+    if (out == nullptr || n_ring_slots < 1 || n_ring_slots > 0xffffff || slot_bytes < 16 || slot_bytes > (1ll << 39))
+        return fail(B200_EINVAL, "[ERROR] bad hop arguments");
     CU_TRY(cudaSetDevice(device));
     b200_hop* h = new b200_hop();
     h->device = device;
@@ -773,9 +821,11 @@ extern "C" B200_API int b200_hop_create(int device, int n_ring_slots, int64_t sl
     const size_t total = (size_t)h->n_slots * h->slot_bytes + (size_t)h->n_slots * 8 + 256;
     cudaError_t e = cudaMalloc(&h->local, total);
     if (e != cudaSuccess) { cudaGetLastError(); delete h; return fail(B200_ENOMEM, "[ERROR] CUDA out of memory for the hop mailbox"); }
-    cudaMemset(h->local, 0, total);
-    cudaMalloc(&h->counter, 256);
-    cudaMemset(h->counter, 0, 256);
+    e = cudaMalloc(&h->counter, 256);
+    if (e != cudaSuccess) { cudaGetLastError(); cudaFree(h->local); delete h; return fail(B200_ENOMEM, "[ERROR] CUDA out of memory for the hop counters"); }
+    e = cudaMemset(h->local, 0, total);
+    if (e == cudaSuccess) e = cudaMemset(h->counter, 0, 256);
+    if (e != cudaSuccess) { cudaGetLastError(); cudaFree(h->local); cudaFree(h->counter); delete h; return fail(B200_ECUDA, "[ERROR] CUDA: %s (hop mailbox init)", cudaGetErrorString(e)); }
     h->err = reinterpret_cast<int*>(reinterpret_cast<char*>(h->counter) + 128);
     CU_TRY(cudaDeviceSynchronize());
     *out = h;
@@ -787,7 +837,7 @@ extern "C" B200_API int b200_hop_export(b200_hop_t* h, void* handle_out) {
     HopHandle hh;
     memset(&hh, 0, sizeof(hh));
     cudaError_t e = cudaIpcGetMemHandle(&hh.ipc, h->local);
-    hh.has_ipc = (e == cudaSuccess) ? 1 : 0;
+    hh.geom = hop_pack_geom(e == cudaSuccess, h->n_slots, h->slot_bytes);
     if (e != cudaSuccess) cudaGetLastError();  // still usable inside one process through `raw`
     hh.raw = h->local;
     memcpy(handle_out, &hh, sizeof(hh));
@@ -796,7 +846,17 @@ extern "C" B200_API int b200_hop_export(b200_hop_t* h, void* handle_out) {
 extern "C" B200_API int b200_hop_connect(b200_hop_t* h, const void* peer_handle, int peer_device, int same_process) {
     if (h == nullptr || peer_handle == nullptr) return fail(B200_EINVAL, "[ERROR] null argument");
     CU_TRY(cudaSetDevice(h->device));
-    if (h->peer != nullptr && h->peer_ipc) { cudaIpcCloseMemHandle(h->peer); h->peer = nullptr; }
+    if (h->peer != nullptr && h->peer_ipc) { cudaIpcCloseMemHandle(h->peer); }
+    h->peer = nullptr;
+    {   // the peer's ring geometry travels in the handle: slot and flag addresses are computed from ITS sizes
+        HopHandle g;
+        memcpy(&g, peer_handle, sizeof(g));
+        const int pn = (int)((g.geom >> 8) & 0xffffff);
+        const int64_t pb = (int64_t)(g.geom >> 32) * 256;
+        if (pn < 1 || pb < 256) return fail(B200_EINVAL, "[ERROR] malformed hop handle (ring geometry missing)");
+        h->n_slots_peer = pn;
+        h->slot_bytes_peer = pb;
+    }
     if (same_process) {
         HopHandle hh;
         memcpy(&hh, peer_handle, sizeof(hh));
@@ -814,7 +874,7 @@ extern "C" B200_API int b200_hop_connect(b200_hop_t* h, const void* peer_handle,
     } else {
         HopHandle hh;
         memcpy(&hh, peer_handle, sizeof(hh));
-        if (!hh.has_ipc) return fail(B200_ECUDA, "[ERROR] the peer could not export a CUDA IPC handle");
+        if (!(hh.geom & 1ull)) return fail(B200_ECUDA, "[ERROR] the peer could not export a CUDA IPC handle");
         void* p = nullptr;
         CU_TRY(cudaIpcOpenMemHandle(&p, hh.ipc, cudaIpcMemLazyEnablePeerAccess));
         h->peer = reinterpret_cast<char*>(p);
@@ -824,18 +884,18 @@ extern "C" B200_API int b200_hop_connect(b200_hop_t* h, const void* peer_handle,
 }
 extern "C" B200_API int b200_hop_send(b200_hop_t* h, const void* payload, int64_t bytes, uint64_t seq, void* stream) {
     if (h == nullptr || h->peer == nullptr) return fail(B200_ESTATE, "[ERROR] hop has no connected peer");
-    if (bytes < 0 || bytes > h->slot_bytes) return fail(B200_EINVAL, "[ERROR] hop payload of %lld bytes exceeds the slot (%lld)", (long long)bytes, (long long)h->slot_bytes);
+    if (bytes < 0 || bytes > h->slot_bytes_peer) return fail(B200_EINVAL, "[ERROR] hop payload of %lld bytes exceeds the peer's slot (%lld)", (long long)bytes, (long long)h->slot_bytes_peer);
     CU_TRY(cudaSetDevice(h->device));
-    const int slot = (int)(seq % (uint64_t)h->n_slots);
-    char* pslot = h->peer + (size_t)slot * h->slot_bytes;
-    uint64_t* pflag = reinterpret_cast<uint64_t*>(h->peer + (size_t)h->n_slots * h->slot_bytes) + slot;
+    const int slot = (int)(seq % (uint64_t)h->n_slots_peer);
+    char* pslot = h->peer + (size_t)slot * h->slot_bytes_peer;
+    uint64_t* pflag = reinterpret_cast<uint64_t*>(h->peer + (size_t)h->n_slots_peer * h->slot_bytes_peer) + slot;
     launch_hop_send(payload, bytes, pslot, pflag, seq, h->counter, (cudaStream_t)stream);
     CU_TRY(cudaGetLastError());
     return 0;
 }
 extern "C" B200_API void* b200_hop_peer_slot(b200_hop_t* h, uint64_t seq) {
     if (h == nullptr || h->peer == nullptr) return nullptr;
-    return h->peer + (size_t)(seq % (uint64_t)h->n_slots) * h->slot_bytes;
+    return h->peer + (size_t)(seq % (uint64_t)h->n_slots_peer) * h->slot_bytes_peer;
 }
 extern "C" B200_API void* b200_hop_local_slot(b200_hop_t* h, uint64_t seq) {
     if (h == nullptr) return nullptr;

@@ -9,7 +9,6 @@ namespace b200 {
 
 constexpr int kHeadDim = 128;      // the only head size this library is built for
 constexpr int kHalfDim = 64;
-constexpr int kMaxGemvM = 4;       // token rows handled by the weight-streaming SIMT path
 
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll

@@ -68,7 +68,11 @@ gemm_stream_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_co
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int S = p.split;
     uint32_t rank = 0;
-    if (S > 1) asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
+    if (S > 1) {
+        asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
+        // distributed shared memory may be written only once the owning CTA runs: arrive now, wait before the first remote store
+        asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
+    }
     const int tile = blockIdx.x / S;
     const int ks_total = (p.K + kSwK - 1) / kSwK;
     const int k0 = (int)((int64_t)ks_total * rank / S), k1 = (int)((int64_t)ks_total * (rank + 1) / S);
@@ -143,7 +147,10 @@ gemm_stream_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_co
         const int j = t & 63, half = t >> 6;
         const uint32_t owner = (uint32_t)(j / P), jl = (uint32_t)(j % P);
         uint32_t dst = red_u32;
-        if (S > 1) asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(dst) : "r"(red_u32), "r"(owner));
+        if (S > 1) {
+            asm volatile("barrier.cluster.wait.aligned;" ::: "memory");  // pairs with the arrive at kernel entry
+            asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(dst) : "r"(red_u32), "r"(owner));
+        }
         dst += 4u * ((rank * 2u + (uint32_t)half) * MP * P + jl);
 #pragma unroll
         for (int m = 0; m < MP; ++m)
@@ -152,6 +159,7 @@ gemm_stream_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_co
     }
     // every thread of every CTA of the cluster meets here: the partials are in place
     if (S > 1) {
+        if (warp < 2) asm volatile("barrier.cluster.wait.aligned;" ::: "memory");  // the producer / issuer warps complete the entry barrier here
         asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
         asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
     } else {

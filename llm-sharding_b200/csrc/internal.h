@@ -98,19 +98,6 @@ void launch_attn_decode(const AttnDecodeParams& p, int M, cudaStream_t st);
 size_t attn_decode_scratch_floats(int rows, int n_heads, int n_splits);
 int attn_decode_cluster_splits();  // split count served by the cluster variant (0: disabled by B200SHARD_ATTN_CLUSTER=0)
 
-struct RopeAppendParams {
-    const __nv_bfloat16* qkv;  // [M, (n_heads+2*n_kv)*128]
-    __nv_bfloat16* q_out;      // [M, n_heads*128]
-    __nv_bfloat16* k_pool;
-    __nv_bfloat16* v_pool;
-    const int64_t* kv_off;
-    const float* cos;
-    const float* sin;
-    int n_heads, n_kv;
-    int64_t head_stride;
-};
-void launch_rope_append(const RopeAppendParams& p, int M, cudaStream_t st);
-
 struct AttnPrefillParams {
     const __nv_bfloat16* q;    // [B*S, n_heads*128] bf16 (rope applied): high part
     const __nv_bfloat16* q_lo; // bf16(q - q_hi) or nullptr: second MMA pass over K so q keeps ~16 mantissa bits

@@ -8,6 +8,7 @@
 
 #include <mutex>
 
+#include "../../include/b200shard.h"
 #include "common.cuh"
 #include "internal.h"
 
@@ -411,6 +412,9 @@ __device__ __forceinline__ void attn_decode_merge(const AttnDecodeParams& p, con
     if (CLUSTER) {
         uint32_t rank;
         asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
+        // completes the arrive issued at kernel entry: every CTA of the cluster (rank 0 above all) has started, so its
+        // shared memory exists and may be written from here
+        asm volatile("barrier.cluster.wait.aligned;" ::: "memory");
         if (tid < kHeadDim) {
             uint32_t dst;
             asm volatile("mapa.shared::cluster.u32 %0, %1, 0;" : "=r"(dst) : "r"((uint32_t)__cvta_generic_to_shared(&c_part[rank][0])));
@@ -488,6 +492,9 @@ __global__ void __launch_bounds__(NT) attn_decode_kernel(const AttnDecodeParams 
     __shared__ float g_m[NG], g_l[NG];
     __shared__ int s_last;
     __shared__ float c_part[CLUSTER ? kAttnCluster : 1][kPartStride];  // rank 0's copy gathers the cluster's partials
+    // distributed shared memory may only be touched once the target CTA is known to be running: arrive now (non-blocking),
+    // wait right before the remote stores in attn_decode_merge — by then the wait is free
+    if (CLUSTER) asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
     const int split = blockIdx.x, h = blockIdx.y, m = blockIdx.z;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int l16 = lane & 15, grp = warp * 2 + (lane >> 4);  // NG half-warps, 16 lanes x 8 dims each
@@ -717,14 +724,14 @@ static cudaError_t static_scratch_for_current_device(float** out) {
 
 }  // namespace b200
 
-extern "C" __attribute__((visibility("default"))) int b200_attn_decode_static(
+extern "C" B200_API int b200_attn_decode_static(
     const float* q, const void* k_pool, const void* v_pool, const int32_t* block_table, const int32_t* t_end, int rows,
     int n_heads, int n_kv_heads, int page_size, int max_pages_per_row, int n_splits, float* out, void* stream) {
     using namespace b200;
     char msg[256];
     if (q == nullptr || k_pool == nullptr || v_pool == nullptr || block_table == nullptr || t_end == nullptr || out == nullptr) {
         set_last_error("[ERROR] null argument");
-        return -1;
+        return B200_EINVAL;
     }
     if (rows < 1 || rows > kMaxBatch || n_heads < 1 || n_kv_heads < 1 || n_heads % n_kv_heads != 0 || page_size < 64 ||
         page_size % 64 != 0 || max_pages_per_row < 1 || n_splits < 1 || n_splits > kMaxSplits ||
@@ -732,21 +739,21 @@ extern "C" __attribute__((visibility("default"))) int b200_attn_decode_static(
         snprintf(msg, sizeof(msg), "[ERROR] attn_decode_static: need 1 <= rows <= %d, n_heads %% n_kv_heads == 0, page_size %% 64 == 0, "
                  "1 <= n_splits <= %d and at most %d keys per split", kMaxBatch, kMaxSplits, kMaxChunkKeys);
         set_last_error(msg);
-        return -1;
+        return B200_EINVAL;
     }
     const int64_t partials = (int64_t)rows * n_heads * n_splits;
     if (partials > kStaticPartials) {
         snprintf(msg, sizeof(msg), "[ERROR] attn_decode_static: rows*n_heads*n_splits = %lld exceeds the built-in scratch (%d partials, "
                  "%zu bytes); use b200_attn_decode with caller-provided scratch", (long long)partials, kStaticPartials, kStaticScratchBytes);
         set_last_error(msg);
-        return -1;
+        return B200_EINVAL;
     }
     float* scratch = nullptr;
     cudaError_t e = static_scratch_for_current_device(&scratch);
     if (e != cudaSuccess) {
         snprintf(msg, sizeof(msg), "[ERROR] CUDA: could not resolve the built-in scratch array on this device: %s", cudaGetErrorString(e));
         set_last_error(msg);
-        return -3;
+        return B200_ECUDA;
     }
     AttnDecodeParams a{};
     a.q = q; a.k_pool = reinterpret_cast<const __nv_bfloat16*>(k_pool); a.v_pool = reinterpret_cast<const __nv_bfloat16*>(v_pool);
@@ -762,52 +769,7 @@ extern "C" __attribute__((visibility("default"))) int b200_attn_decode_static(
     if (e != cudaSuccess) {
         snprintf(msg, sizeof(msg), "[ERROR] CUDA: %s (attn_decode_static launch)", cudaGetErrorString(e));
         set_last_error(msg);
-        return -3;
+        return B200_ECUDA;
     }
-    return 0;
+    return B200_OK;
 }
-
-namespace b200 {
-
-// =========================================================================== RoPE + KV append (GEMM path)
-// apply_rotary_pos_emb (modeling_llama.py:146-168) on the fused QKV GEMM output, then
-// DynamicCache.update (cache_utils.py:102-121) as a paged write instead of a re-allocating cat.
-// One CTA per token; thread handles 8 consecutive dims of the first half and the matching 8 of the second.
-__global__ void __launch_bounds__(256) rope_append_kernel(const RopeAppendParams p) {
-    const int m = blockIdx.x;
-    const int n_all = p.n_heads + 2 * p.n_kv;
-    const __nv_bfloat16* row = p.qkv + (size_t)m * n_all * kHeadDim;
-    const float* cs = p.cos + (size_t)m * kHalfDim;
-    const float* sn = p.sin + (size_t)m * kHalfDim;
-    const int64_t off = p.kv_off[m];
-    for (int w = threadIdx.x; w < n_all * 8; w += blockDim.x) {
-        const int head = w >> 3, j0 = (w & 7) * 8;
-        const uint4 lo4 = *reinterpret_cast<const uint4*>(row + head * kHeadDim + j0);
-        const uint4 hi4 = *reinterpret_cast<const uint4*>(row + head * kHeadDim + kHalfDim + j0);
-        float a[8] = {bf_lo(lo4.x), bf_hi(lo4.x), bf_lo(lo4.y), bf_hi(lo4.y), bf_lo(lo4.z), bf_hi(lo4.z), bf_lo(lo4.w), bf_hi(lo4.w)};
-        float b[8] = {bf_lo(hi4.x), bf_hi(hi4.x), bf_lo(hi4.y), bf_hi(hi4.y), bf_lo(hi4.z), bf_hi(hi4.z), bf_lo(hi4.w), bf_hi(hi4.w)};
-        uint4 olo = lo4, ohi = hi4;
-        if (head < p.n_heads + p.n_kv) {
-            float lo[8], hi[8];
-#pragma unroll
-            for (int e = 0; e < 8; ++e) {
-                const float c = cs[j0 + e], s = sn[j0 + e];
-                lo[e] = a[e] * c - b[e] * s;
-                hi[e] = b[e] * c + a[e] * s;
-            }
-            olo = make_uint4(pack_bf16(lo[0], lo[1]), pack_bf16(lo[2], lo[3]), pack_bf16(lo[4], lo[5]), pack_bf16(lo[6], lo[7]));
-            ohi = make_uint4(pack_bf16(hi[0], hi[1]), pack_bf16(hi[2], hi[3]), pack_bf16(hi[4], hi[5]), pack_bf16(hi[6], hi[7]));
-        }
-        __nv_bfloat16* dst;
-        if (head < p.n_heads) dst = p.q_out + ((size_t)m * p.n_heads + head) * kHeadDim;
-        else if (head < p.n_heads + p.n_kv) dst = p.k_pool + off + (int64_t)(head - p.n_heads) * p.head_stride;
-        else dst = p.v_pool + off + (int64_t)(head - p.n_heads - p.n_kv) * p.head_stride;
-        *reinterpret_cast<uint4*>(dst + j0) = olo;
-        *reinterpret_cast<uint4*>(dst + kHalfDim + j0) = ohi;
-    }
-}
-void launch_rope_append(const RopeAppendParams& p, int M, cudaStream_t st) {
-    if (M > 0) rope_append_kernel<<<M, 256, 0, st>>>(p);
-}
-
-}  // namespace b200

@@ -83,7 +83,9 @@ class Communicator:
             os.makedirs(os.path.dirname(data_path), exist_ok=True)
             with open(data_path, "wb") as f:
                 f.write(raw)
-        return torch.load(io.BytesIO(raw), weights_only=False)
+        # weights_only: the socket is bound to a network address and the messages are dicts of tensors / ints / None / str
+        # (or a bare tensor) — nothing that needs the unpickler to run code (the reference's torch.load(path) default)
+        return torch.load(io.BytesIO(raw), weights_only=True)
 
     def close(self) -> None:
         self.recv_socket.close(0)

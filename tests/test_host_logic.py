@@ -121,3 +121,36 @@ def test_profiler_latency_fit_recovers_models():
         NodeProfiler._fit_latency_models([1, 2], [1.0, 2.0])
     with pytest.raises(ValueError):
         NodeProfiler._fit_latency_models([1, 2, 3], [1.0, 2.0])
+
+
+def test_communicator_does_not_unpickle_code():
+    """The ZeroMQ PULL socket is bound to a network address: a pickle that would execute code must be refused, while the
+    three message kinds of the reference still pass."""
+    import io
+    import pickle
+    import zmq
+    from llm_sharding_b200.node_worker import Communicator
+    a = Communicator("tcp://127.0.0.1:45990", "tcp://127.0.0.1:45990")
+    try:
+        msgs = [{"hidden_states": torch.ones(1, 2, 4, dtype=torch.bfloat16), "batch_size": 1, "seq_len": 2},
+                {"hidden_states": torch.ones(1, 1, 4), "cos": None, "sin": None, "pos_offset": 3, "slot": [0]},
+                torch.tensor([5], dtype=torch.int64),
+                {"command": "clear_KV_cache", "origin_node": {"src_addr": "x", "dst_addr": "y", "shards_start": 0, "shards_end": 2}}]
+        for m in msgs:
+            a.transfer_data(m)
+            got = a.receive_data()
+            if isinstance(m, torch.Tensor):
+                assert torch.equal(got, m)
+            else:
+                assert set(got) == set(m)
+
+        class Evil:
+            def __reduce__(self):
+                return (eval, ("1+1",))
+        buf = io.BytesIO()
+        torch.save({"x": Evil()}, buf)
+        a.send_socket.send(buf.getvalue())
+        with pytest.raises(pickle.UnpicklingError):
+            a.receive_data()
+    finally:
+        a.close()
