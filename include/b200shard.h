@@ -194,6 +194,17 @@ B200_API int b200_attn_decode_static(const float* d_q, const void* d_k_pool, con
                                      const int32_t* d_block_table, const int32_t* d_t_end, int rows, int n_heads,
                                      int n_kv_heads, int page_size, int max_pages_per_row, int n_splits, float* d_out,
                                      void* stream);
+/* Prefill attention alone (eager_attention_forward, transformers modeling_llama.py:199-221, for S query tokens per row on
+ * top of d_base_len[b] cached ones): the tcgen05 / TMA kernel b200_shard_forward launches for more than 32 token rows.
+ * Queries arrive as the (hi, lo) bf16 pair the QKV epilogue produces (hi = bf16(q), lo = bf16(q - hi)), [B*S, n_heads*128];
+ * K/V of all base_len[b] + S positions must already be in the pools (layout [page][kv_head][page_size][128] bf16,
+ * n_pool_pages pages), reached through d_block_table[b][*].  causal = 0: every query sees all base_len + S keys (what the
+ * reference does, utils/node_worker.py:253-258); causal = 1: query s sees keys 0 .. base_len + s.  d_out [B*S, n_heads*128]
+ * bf16 (out_f16 = 0) or fp16 (1). */
+B200_API int b200_attn_prefill(const void* d_q_hi, const void* d_q_lo, const void* d_k_pool, const void* d_v_pool,
+                               const int32_t* d_block_table, const int32_t* d_base_len, int B, int S, int n_heads,
+                               int n_kv_heads, int page_size, int max_pages_per_row, int n_pool_pages, int causal,
+                               int out_f16, void* d_out, void* stream);
 /* out[M,N] (fp32) = A[M,K] (bf16) * W[N,K]^T (bf16): the tcgen05/TMA GEMM used for prefill */
 B200_API int b200_gemm_bf16(const void* d_a, const void* d_w, int M, int N, int K, float* d_out, void* stream);
 /* same kernel with fp16 operands (A[M,K] and W[N,K] both fp16): what the shard path runs — it holds the bf16 model

@@ -961,6 +961,29 @@ extern "C" B200_API int b200_attn_decode(const float* q, const void* k_pool, con
     CU_TRY(cudaGetLastError());
     return 0;
 }
+extern "C" B200_API int b200_attn_prefill(const void* q_hi, const void* q_lo, const void* k_pool, const void* v_pool,
+                                          const int32_t* block_table, const int32_t* base_len, int B, int S, int n_heads,
+                                          int n_kv_heads, int page_size, int max_pages_per_row, int n_pool_pages, int causal,
+                                          int out_f16, void* out, void* stream) {
+    if (q_hi == nullptr || q_lo == nullptr || k_pool == nullptr || v_pool == nullptr || block_table == nullptr ||
+        base_len == nullptr || out == nullptr)
+        return fail(B200_EINVAL, "[ERROR] null argument");
+    if (B < 1 || B > kMaxBatch || S < 1 || n_heads < 1 || n_kv_heads < 1 || n_heads % n_kv_heads != 0 || page_size < 64 ||
+        page_size % 64 != 0 || max_pages_per_row < 1 || n_pool_pages < 1)
+        return fail(B200_EINVAL, "[ERROR] attn_prefill: need 1 <= B <= %d, S >= 1, n_heads %% n_kv_heads == 0, page_size %% 64 == 0", kMaxBatch);
+    AttnPrefillParams a{};
+    a.q = reinterpret_cast<const __nv_bfloat16*>(q_hi); a.q_lo = reinterpret_cast<const __nv_bfloat16*>(q_lo);
+    a.out_f16 = out_f16 ? 1 : 0;
+    a.k_pool = reinterpret_cast<const __nv_bfloat16*>(k_pool); a.v_pool = reinterpret_cast<const __nv_bfloat16*>(v_pool);
+    a.block_table = block_table; a.call_base = base_len;
+    for (int i = 0; i < B; ++i) a.slots.v[i] = i;
+    a.B = B; a.S = S; a.causal = causal ? 1 : 0; a.n_heads = n_heads; a.n_kv = n_kv_heads; a.page_size = page_size;
+    a.max_pages_per_slot = max_pages_per_row; a.out = out;
+    if (launch_attn_prefill_tc(a, (int64_t)n_pool_pages * n_kv_heads * page_size, (cudaStream_t)stream) != 0)
+        return fail(B200_ECUDA, "[ERROR] %s", gemm_error());
+    CU_TRY(cudaGetLastError());
+    return 0;
+}
 extern "C" B200_API int b200_gemm_bf16(const void* a, const void* w, int M, int N, int K, float* out, void* stream) {
     if (a == nullptr || w == nullptr || out == nullptr) return fail(B200_EINVAL, "[ERROR] null argument");
     GemmParams g{};

@@ -67,7 +67,14 @@ PRESETS = {
                              rope_scaling={"rope_type": "llama3", "factor": 8.0, "low_freq_factor": 1.0,
                                            "high_freq_factor": 4.0, "original_max_position_embeddings": 64}),
     "llama2_7b": SynthConfig("llama2_7b", 32000, 4096, 11008, 32, 32, 32),
+    # Llama-2-7B LAYER dimensions (what bench.py and BASELINE configs[3] run) with three layers and a small vocabulary, so
+    # that the CPU oracle finishes 512..4096-token prompts in seconds: reaches the CTA-pair GEMM epilogues and the
+    # steady state of the prefill-attention pipeline (>= 3 key tiles) that the small presets never touch
+    "l7b3": SynthConfig("l7b3", 8192, 4096, 11008, 3, 32, 32),
+    # same with grouped-query attention (Llama-3-8B-like head layout: 32 query heads on 8 K/V heads)
+    "l7b3_gqa": SynthConfig("l7b3_gqa", 8192, 4096, 11008, 3, 32, 8),
 }
+_BIG_CACHE: dict = {}   # (cfg.name, seed, layer) -> state dict, for the few-layer 7B-dimension presets only
 
 
 def _rng(seed: int, *tag: int) -> np.random.Generator:
@@ -92,6 +99,18 @@ def norm_weight(seed: int, tag: tuple, n: int) -> torch.Tensor:
 
 def layer_state(cfg: SynthConfig, seed: int, layer: int) -> dict:
     """bf16 tensors for absolute layer index ``layer`` keyed like ``block_i.pth``."""
+    cacheable = cfg.hidden_size >= 4096 and cfg.num_hidden_layers <= 4   # generated twice per test (oracle + GPU chain)
+    if cacheable and (cfg.name, seed, layer) in _BIG_CACHE:
+        return dict(_BIG_CACHE[(cfg.name, seed, layer)])
+    state = _layer_state(cfg, seed, layer)
+    if cacheable:
+        if len(_BIG_CACHE) >= 6:
+            _BIG_CACHE.clear()
+        _BIG_CACHE[(cfg.name, seed, layer)] = state
+    return dict(state)
+
+
+def _layer_state(cfg: SynthConfig, seed: int, layer: int) -> dict:
     H, I, d = cfg.hidden_size, cfg.intermediate_size, cfg.head_dim
     nq, nkv = cfg.num_attention_heads * d, cfg.num_key_value_heads * d
     s = cfg.init_std
@@ -169,6 +188,32 @@ def write_tokenizer(path: str, vocab_size: int) -> None:
     fast = PreTrainedTokenizerFast(tokenizer_object=tok, unk_token="<unk>", bos_token="<s>",
                                    eos_token="</s>", pad_token="<unk>")
     fast.save_pretrained(path)
+
+
+def state_provider(cfg: SynthConfig, seed: int):
+    """``file name -> state_dict`` straight from the generators (no .pth round trip): what the NodeWorker mirror accepts
+    through ``state_provider=`` for the 7B-dimension presets, whose shard files would be gigabytes."""
+    def provide(name: str) -> dict:
+        if name.startswith("block_"):
+            return layer_state(cfg, seed, int(name[len("block_"):-len(".pth")]))
+        if name == "embedding.pth":
+            return embedding_state(cfg, seed)
+        if name == "final_norm.pth":
+            return final_norm_state(cfg, seed)
+        if name == "lm_head.pth":
+            return lm_head_state(cfg, seed)
+        raise FileNotFoundError(name)
+    return provide
+
+
+def write_model_dir(path: str, cfg: SynthConfig) -> str:
+    """config.json + tokenizer + an empty embedding.pth placeholder (for use with ``state_provider``)."""
+    os.makedirs(path, exist_ok=True)
+    with open(os.path.join(path, "config.json"), "w") as f:
+        json.dump(hf_config_dict(cfg), f, indent=1)
+    write_tokenizer(path, cfg.vocab_size)
+    open(os.path.join(path, "embedding.pth"), "wb").close()
+    return path
 
 
 def write_shards(path: str, cfg: SynthConfig, seed: int, dtype: torch.dtype = torch.float32,

@@ -24,7 +24,13 @@ def build_chain(tmp_root, preset, seed, splits, max_batch=1, max_tokens=512, cau
                 max_seq_len=None, device="cuda:0"):
     from llm_sharding_b200.chain import LoopbackCommunicator
     from llm_sharding_b200.node_worker import NodeWorker
-    d = shard_dir(tmp_root, preset, seed)
+    cfg = synth.PRESETS[preset]
+    provider = None
+    if cfg.hidden_size >= 4096:   # 7B-dimension presets: weights straight from the generators, no gigabyte .pth files
+        d = synth.write_model_dir(os.path.join(tmp_root, f"{preset}_cfg"), cfg)
+        provider = synth.state_provider(cfg, seed)
+    else:
+        d = shard_dir(tmp_root, preset, seed)
     n = len(splits)
     ports = [next(_port) for _ in range(n)]
     workers = []
@@ -32,7 +38,7 @@ def build_chain(tmp_root, preset, seed, splits, max_batch=1, max_tokens=512, cau
         src, dst = f"tcp://*:{ports[i]}", f"tcp://127.0.0.1:{ports[(i + 1) % n]}"
         w = NodeWorker(src, dst, i == 0, d, device=device, dtype=torch.bfloat16,
                        communicator=LoopbackCommunicator(src, dst), max_tokens=max_tokens, max_batch=max_batch,
-                       causal=causal, use_graphs=use_graphs, max_seq_len=max_seq_len)
+                       causal=causal, use_graphs=use_graphs, max_seq_len=max_seq_len, state_provider=provider)
         w.load_shards(s, e)
         workers.append(w)
     return workers
