@@ -114,6 +114,7 @@ def cpu_decode_baseline(steps, warmup, time_budget_s, prompt_len=PROMPT_LEN):
     layer is 809 MB fp32, far beyond the LLC, so the DRAM-streaming behaviour is the real one)."""
     from oracle import llama_oracle as lo  # allowed here: the cpu_baseline / --impl reference legs
 
+    torch.set_num_threads(host_threads())
     torch.manual_seed(0)
     H, I, V, L, nh = 4096, 11008, 32000, 32, 32
     distinct = []
@@ -165,20 +166,71 @@ def cpu_decode_baseline(steps, warmup, time_budget_s, prompt_len=PROMPT_LEN):
             "prefill_tok_s": prompt_len / prefill_s}
 
 
+def reference_chain_baseline(n_gpus, steps, warmup, time_budget_s, with_c1):
+    """The reference's OWN NodeWorker chain (its files, unmodified, behind the transformers-5.5 shim) on the host cores:
+    `kind: "reference"`.  Returns None when the reference files are not on this machine (then the port is used)."""
+    from oracle import ref_chain_bench as rb  # allowed here: the cpu_baseline / --impl reference legs
+    if not rb.available():
+        return None
+    try:
+        import psutil
+        if psutil.virtual_memory().available < 40e9:   # 32 fp32 layers = 26 GB resident
+            return None
+    except ImportError:
+        pass
+    n_stages = max(2, n_gpus)
+    r = rb.run_workload(n_stages, PROMPT_LEN, steps, warmup, time_budget_s, with_c1)
+    m = r["main"]
+    if not m["steps_timed"]:
+        return None
+    sample = (f"the reference's own NodeWorker chain (utils/node_worker.py + utils/shard_loader.py, unmodified, transformers 5.5 compat shim), "
+              f"CPU fp32, Llama-2-7B architecture random init (32 layers = 4 distinct weight files + symlinks, 26 GB resident), "
+              f"{n_stages} NodeWorkers in one process over loopback ZeroMQ + torch.save/load files (its Communicator), batch 1, "
+              f"{PROMPT_LEN}-token prompt, {m['steps_timed']} decode passes timed after {warmup} warm-up; prefill {m['prefill_s']:.2f}s "
+              f"({m['prefill_tok_s']:.1f} tok/s); hop {m['hop_ms']:.2f} ms per message; set-up {r['setup_write_s'] + r['setup_load_s']:.0f}s untimed")
+    out = {"value": m["decode_tok_s"], "unit": "tok/s", "cores": r["threads"], "kind": "reference", "sample": sample,
+           "steps_timed": m["steps_timed"], "ms_per_step": m["ms_per_token"], "p50_token_ms": m["p50_token_ms"],
+           "prefill_tok_s": m["prefill_tok_s"], "hop_ms": m["hop_ms"], "omp_num_threads_env": r["omp_num_threads_env"],
+           "n_stages": n_stages}
+    if "c1" in r:
+        out["c1"] = dict(r["c1"], workload="BASELINE.json configs[0] exactly: 2 NodeWorkers (layers 0-16 / 16-32) on localhost, CPU fp32, "
+                                           "batch 1, 32-token prompt -> 16 greedy tokens" if n_stages == 2 else
+                                           f"configs[0]'s request (32-token prompt -> 16 greedy tokens) on the {n_stages}-worker chain")
+    return out
+
+
+def host_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
 def run_reference(args):
     rank, world, _ = dist_env()
     if rank != 0:
         return
-    base = cpu_decode_baseline(args.steps, max(1, min(args.warmup, 3)), time_budget_s=150.0, prompt_len=PROMPT_LEN)
+    torch.set_num_threads(host_threads())   # torchrun exports OMP_NUM_THREADS=1: the CPU arm uses every host core it can
+    W = max(1, min(args.warmup, 3))
+    base = None
+    try:
+        base = reference_chain_baseline(args.gpus, min(args.steps, 64), W, time_budget_s=90.0, with_c1=True)
+    except Exception as e:  # fall back to the port, say why
+        print(f"[bench] reference chain unavailable ({e!r}); timing the oracle port instead", file=sys.stderr, flush=True)
+    if base is None:
+        base = cpu_decode_baseline(args.steps, W, time_budget_s=150.0, prompt_len=PROMPT_LEN)
     line = {
         "impl": "reference", "metric": METRIC, "value": base["value"], "unit": "tok/s", "n_gpus": args.gpus,
-        "steps": base["steps_timed"], "warmup": max(1, min(args.warmup, 3)), "ms_per_step": base["ms_per_step"],
+        "steps": base["steps_timed"], "warmup": W, "ms_per_step": base["ms_per_step"],
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": workload_config(args.gpus),
         "cpu_baseline": {k: base[k] for k in ("value", "unit", "cores", "kind", "sample")},
         "e2e": {"value": base["value"], "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "prefill_tok_s": base["prefill_tok_s"], "p50_token_ms": base["p50_token_ms"], "gpu_launches": 0,
     }
+    for k in ("hop_ms", "c1", "omp_num_threads_env", "n_stages"):
+        if k in base:
+            line[k] = base[k]
     print(json.dumps(line), flush=True)
 
 
@@ -188,12 +240,16 @@ def workload_config(n_gpus):
                             "greedy decode with KV cache; one step = one decode token",
                 "prompt_len": PROMPT_LEN, "new_tokens": NEW_TOKENS, "batch": 1, "layers_per_gpu": 32,
                 "attention": "non-causal prefill (reference parity, SURVEY.md F4); decode unaffected",
+                "arithmetic": "model dtype bf16: weights held as fp16 (exact for bf16 values in fp16's normal range), tensor-core operands "
+                              "fp16 x fp16, accumulation / residual stream / softmax fp32, K/V cache and hop messages bf16",
                 "l2": "inputs larger than L2: 13.2 GB of weights streamed per step vs 126 MB L2"}
     return {"workload": f"Llama-2-7B bf16 layer-sharded {n_gpus}-way (BASELINE.json configs[2] family): {32 // n_gpus} layers per B200, "
                         f"{n_gpus} independent batch-1 request streams in flight, 512-token prompts, greedy decode; "
                         "one step = one decode token for every stream",
             "prompt_len": PROMPT_LEN, "new_tokens": NEW_TOKENS, "batch": 1, "streams": n_gpus, "layers_per_gpu": 32 // n_gpus,
             "hop": "in-kernel NVLink peer stores + flag",
+            "arithmetic": "model dtype bf16: weights held as fp16 (exact for bf16 values in fp16's normal range), tensor-core operands "
+                          "fp16 x fp16, accumulation / residual stream / softmax fp32, K/V cache and hop messages bf16",
             "l2": "inputs larger than L2: every GPU streams its layers' weights once per stream per step"}
 
 
@@ -206,13 +262,19 @@ def run_single(args):
     dev = torch.device("cuda:0")
     torch.cuda.set_device(dev)
     K, W = args.steps, max(args.warmup, 3)
+    parity = None
+    if not args.no_parity:   # the same public API on a model small enough for the CPU oracle, before anything is timed
+        import __graft_entry__ as entry
+        with quiet():
+            parity = entry.smoke_check()
     cfg = synthetic.LLAMA2_7B
     tmp = tempfile.mkdtemp(prefix="b200shard_bench_")
     synthetic.write_model_dir(tmp, cfg)
     with quiet():
         worker = NodeWorker("tcp://*:48800", "tcp://127.0.0.1:48800", True, tmp, device="cuda:0", dtype=torch.bfloat16,
                             communicator=LoopbackCommunicator("tcp://*:48800", "tcp://127.0.0.1:48800"),
-                            max_tokens=PROMPT_LEN, max_batch=1, max_seq_len=PROMPT_LEN + 2 * (K + W) + 64,
+                            max_tokens=max(PROMPT_LEN, 0 if args.no_extras else 4 * 2048), max_batch=1 if args.no_extras else 4,
+                            max_seq_len=max(PROMPT_LEN + 2 * (K + W) + 64, 0 if args.no_extras else 2048 + 64),
                             state_provider=synthetic.RandomStateProvider(cfg, "cuda:0", seed=0))
         worker.load_shards(0, cfg["num_hidden_layers"])
     eng, kv = worker.shard.engine, worker.past_key_value
@@ -236,7 +298,45 @@ def run_single(args):
         if it >= 2:
             prefill_ms.append(e0.elapsed_time(e1))
     prefill_ms.sort()
-    prefill_tok_s = PROMPT_LEN / (prefill_ms[len(prefill_ms) // 2] / 1000)
+    prefill_med_ms = prefill_ms[len(prefill_ms) // 2]
+    prefill_tok_s = PROMPT_LEN / (prefill_med_ms / 1000)
+
+    def prefill_flops(B, S):
+        # 2 x params per token per layer + 4 S T H per sequence per layer (non-causal), lm_head on the last row only
+        H, I, L, V = cfg["hidden_size"], cfg["intermediate_size"], cfg["num_hidden_layers"], cfg["vocab_size"]
+        return B * (S * L * 2 * (4 * H * H + 3 * H * I) + L * 4 * S * S * H + 2 * H * V)
+
+    pk0 = peaks()
+    roofline_prefill = {"bound": "tensor", "workload": f"1 x {PROMPT_LEN}-token prompt through NodeWorker (host ids in, first token out)",
+                        "flops": prefill_flops(1, PROMPT_LEN), "ms": prefill_med_ms,
+                        "achieved": prefill_flops(1, PROMPT_LEN) / (prefill_med_ms / 1000) / 1e12, "peak": pk0["bf16_tflops"],
+                        "unit": "TFLOP/s", "frac": prefill_flops(1, PROMPT_LEN) / (prefill_med_ms / 1000) / 1e12 / pk0["bf16_tflops"],
+                        "peak_source": pk0["source"]}
+    prefill_4x2048 = None
+    if not args.no_extras:   # the tensor-bound regime proper: 4 x 2048 tokens in one call
+        ids4 = torch.randint(3, cfg["vocab_size"], (4, 2048), generator=g, dtype=torch.int64).pin_memory()
+        ms4 = []
+        for it in range(1 + 3):
+            with quiet():
+                worker.clear_KV_cache()
+            torch.cuda.synchronize()
+            e0, e1 = ev(), ev()
+            e0.record()
+            with quiet():
+                tok4 = worker.pass_through_shard(worker.receive_user_request(input_ids=ids4))
+            e1.record()
+            torch.cuda.synchronize()
+            if it >= 1:
+                ms4.append(e0.elapsed_time(e1))
+        ms4.sort()
+        f4 = prefill_flops(4, 2048)
+        prefill_4x2048 = {"bound": "tensor", "workload": "4 x 2048-token prompts in one call through NodeWorker", "flops": f4,
+                          "ms": ms4[1], "tok_s": 4 * 2048 * 1000.0 / ms4[1], "achieved": f4 / (ms4[1] / 1000) / 1e12,
+                          "peak": pk0["bf16_tflops"], "unit": "TFLOP/s", "frac": f4 / (ms4[1] / 1000) / 1e12 / pk0["bf16_tflops"]}
+        with quiet():
+            worker.clear_KV_cache()
+            msg = worker.receive_user_request(input_ids=ids_host)
+            tok = worker.pass_through_shard(msg)
 
     # ---- decode, device resident: token buffer fed back on the GPU, one CUDA-graph replay per step
     tokbuf = tok.clone()
@@ -336,7 +436,13 @@ def run_single(args):
     cpu = None
     if not args.no_cpu_baseline:
         try:
-            cpu = cpu_decode_baseline(steps=16, warmup=1, time_budget_s=25.0, prompt_len=PROMPT_LEN)
+            cpu = None
+            try:
+                cpu = reference_chain_baseline(1, steps=16, warmup=1, time_budget_s=25.0, with_c1=False)
+            except Exception as e:
+                print(f"[bench] reference chain unavailable ({e!r}); timing the oracle port instead", file=sys.stderr, flush=True)
+            if cpu is None:
+                cpu = cpu_decode_baseline(steps=16, warmup=1, time_budget_s=25.0, prompt_len=PROMPT_LEN)
             cpu = {k: cpu[k] for k in ("value", "unit", "cores", "kind", "sample")}
         except Exception as e:  # the baseline is reported, never required
             cpu = {"value": None, "unit": "tok/s", "cores": 0, "kind": "port", "sample": f"failed: {e!r}"}
@@ -349,6 +455,7 @@ def run_single(args):
         "roofline": roofline, "step_roofline": step_roofline, "cpu_baseline": cpu,
         "prefill_tok_s": prefill_tok_s, "p50_token_ms": 1000 * per_step[len(per_step) // 2],
         "p50_token_ms_device": ms_per_step, "kernel_us": kernel_us,
+        "roofline_prefill": roofline_prefill, "prefill_4x2048": prefill_4x2048, "parity": parity,
     }
     print(json.dumps(line), flush=True)
 
@@ -369,6 +476,8 @@ def main():
     ap.add_argument("--mixed", action="store_true", help="--gpus > 1: BASELINE configs[4]'s mixed stream: prompts of 32/512/2048 tokens, "
                                                          "streams are retired and re-prefilled while the others decode")
     ap.add_argument("--retire-every", type=int, default=8, help="--mixed: rounds between two retirements")
+    ap.add_argument("--no-parity", action="store_true", help="--gpus > 1: skip the oracle parity check of the ring that precedes the timed region")
+    ap.add_argument("--no-extras", action="store_true", help="skip the extra blocks (c3_batch32 / c4_prefill at --gpus > 1, prefill_4x2048 at 1)")
     args = ap.parse_args()
     PROMPT_LEN = args.prompt_len
     if args.impl == "reference":

@@ -58,6 +58,79 @@ def hop_pingpong(rank, world, device, ctrl, n=200, payload=8192):
     return result
 
 
+PARITY_PRESET, PARITY_SEED, PARITY_PROMPT_SEEDS = "ring8", 11, (700, 701)   # seed scanned for fp32 top-1 margins >= 0.1
+PARITY_HIDDEN_TOL, PARITY_TIE_TOL = 2e-2, 0.02
+
+
+def ring_parity(rank, world, device, ctrl, splits, transport, tmp_root):
+    """Token / hidden-state parity of the SAME ChainStage ring the timed region uses, at the same N: an 8-layer synthetic
+    Llama (oracle/synth.py preset ring8) is split over the N stages, two request streams go round the ring (24-token
+    prompts, 5 more tokens each), and every stage compares the hidden state that ARRIVES in its mailbox with the CPU
+    oracle's state leaving the previous shard (<= 2e-2 relative L2); rank 0 compares the greedy tokens that come back
+    (identical wherever the oracle's top-1 margin is above bf16 noise).  The oracle is the checker only."""
+    from llm_sharding_b200.chain import ChainStage, LoopbackCommunicator
+    from llm_sharding_b200.node_worker import NodeWorker
+    from oracle import synth
+    from oracle.llama_oracle import OracleWorker, run_chain as oracle_chain
+
+    cfg = synth.PRESETS[PARITY_PRESET]
+    P, R, n_streams = 24, 5, 2
+    d = os.path.join(tmp_root, f"parity_{'_'.join(str(e - s) for s, e in splits)}_r{rank}")
+    synth.write_model_dir(d, cfg)
+    start, end = splits[rank]
+    with _quiet():
+        w = NodeWorker(f"tcp://*:{49100 + rank}", f"tcp://127.0.0.1:{49100 + (rank + 1) % world}", rank == 0, d,
+                       device=str(device), dtype=torch.bfloat16,
+                       communicator=LoopbackCommunicator(f"tcp://*:{49100 + rank}", f"tcp://127.0.0.1:{49100 + (rank + 1) % world}"),
+                       max_tokens=P, max_batch=1, max_slots=n_streams, max_seq_len=128,
+                       state_provider=synth.state_provider(cfg, PARITY_SEED))
+        w.load_shards(start, end)
+    stage = ChainStage(w, rank, world, n_streams, P, ctrl_group=ctrl, transport=transport)
+    stage.record_inbound = True
+    prompts = [synth.prompt_ids(cfg, ps, 1, P) for ps in PARITY_PROMPT_SEEDS]
+    for i in range(n_streams):
+        stage.prefill(i, P, prompts[i][0].to(device) if rank == 0 else None)
+    for _ in range(R):
+        for i in range(n_streams):
+            stage.decode(i, record=True)
+    for i in range(n_streams):
+        stage.finish(i, record=True)
+    torch.cuda.synchronize()
+    # the oracle chain with the same split (tiny model: well under a second per stream on one core)
+    worst, ok, n_tok = 0.0, True, 0
+    detail = []
+    for i in range(n_streams):
+        ows = [OracleWorker(cfg, PARITY_SEED, s, e, k == 0) for k, (s, e) in enumerate(splits)]
+        o_tok, o_states, o_margin = oracle_chain(ows, prompts[i], R + 1)
+        if rank > 0:
+            mine = [t for (st, S, t) in stage.inbound if st == i]
+            for p, h in enumerate(mine):
+                ref = o_states[p][rank - 1]
+                rel = float((h.float().cpu().double() - ref.double()).norm() / ref.double().norm())
+                worst = max(worst, rel)
+        else:
+            got = [int(t[0]) for k, t in enumerate(stage.tokens)]
+            # recording order: R rounds over the streams (decode), then one finish per stream
+            mine = [got[r * n_streams + i] for r in range(R)] + [got[R * n_streams + i]]
+            for p in range(R + 1):
+                n_tok += 1
+                if mine[p] != int(o_tok[p, 0]):
+                    if float(o_margin[p, 0]) >= PARITY_TIE_TOL:
+                        ok = False
+                    detail.append((i, p, mine[p], int(o_tok[p, 0]), float(o_margin[p, 0])))
+                    break   # no teacher forcing inside the ring: later tokens of this stream are not comparable
+    ok = ok and worst <= PARITY_HIDDEN_TOL and stage.error() == 0
+    t = torch.tensor([worst, 0.0 if ok else 1.0, float(n_tok)], dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX, group=ctrl)
+    dist.barrier(group=ctrl)
+    stage.close()
+    w.past_key_value = None
+    w.shard.engine.close()
+    return {"checked": True, "ok": float(t[1]) == 0.0, "worst_rel_l2": float(t[0]), "n": world,
+            "layers_per_stage": [e - s for s, e in splits], "tokens_compared": int(t[2]), "token_mismatches": detail,
+            "against": "CPU oracle (oracle/llama_oracle.py OracleWorker chain, fp32), preset ring8"}
+
+
 def run_chain(args, config, metric, ClockSampler, peaks):
     from llm_sharding_b200 import synthetic
     from llm_sharding_b200.chain import ChainStage, LoopbackCommunicator, layer_range
@@ -90,12 +163,29 @@ def run_chain(args, config, metric, ClockSampler, peaks):
         return run_mixed(args, config, rank, world, local, device, ctrl, start, end, ClockSampler, peaks)
     tmp = tempfile.mkdtemp(prefix=f"b200shard_bench_r{rank}_")
     synthetic.write_model_dir(tmp, cfg)
+    # ---- parity first: the same ring code at the same N against the CPU oracle (even split; at N = 4 an uneven one too)
+    parity = None
+    if not getattr(args, "no_parity", False):
+        checks = [[layer_range(r, world, 8) for r in range(world)]] if world <= 8 else []
+        if world == 4:
+            checks.append([(0, 1), (1, 4), (4, 6), (6, 8)])
+        results = [ring_parity(rank, world, device, ctrl, sp, transport, tmp) for sp in checks]
+        if results:
+            parity = dict(results[0], ok=all(r["ok"] for r in results), worst_rel_l2=max(r["worst_rel_l2"] for r in results),
+                          tokens_compared=sum(r["tokens_compared"] for r in results),
+                          layers_per_stage=[r["layers_per_stage"] for r in results],
+                          token_mismatches=[m for r in results for m in r["token_mismatches"]])
+    # named configurations measured after the default run on the same worker (BASELINE.json configs[2] and [3])
+    extras = not getattr(args, "no_extras", False) and not splits and rows == 1 and n_streams == world and 32 % world == 0
+    c3_rows, c3_prompt, c3_steps = 32 // world if extras else 0, 128, 128
+    c4_streams, c4_prompt = (16, 2048) if extras else (0, 0)
     with _quiet():
         worker = NodeWorker(f"tcp://*:{48900 + rank}", f"tcp://127.0.0.1:{48900 + (rank + 1) % world}", rank == 0, tmp,
                             device=str(device), dtype=torch.bfloat16,
                             communicator=LoopbackCommunicator(f"tcp://*:{48900 + rank}", f"tcp://127.0.0.1:{48900 + (rank + 1) % world}"),
-                            max_tokens=rows * PROMPT_LEN, max_batch=rows, max_slots=n_streams * rows,
-                            max_seq_len=PROMPT_LEN + 2 * (K + W) + 64,
+                            max_tokens=max(rows * PROMPT_LEN, c3_rows * c3_prompt, c4_prompt), max_batch=max(rows, c3_rows),
+                            max_slots=max(n_streams * rows, world * c3_rows, c4_streams),
+                            max_seq_len=max(PROMPT_LEN + 2 * (K + W) + 64, c3_prompt + 2 * (c3_steps + W) + 64, c4_prompt + 64),
                             state_provider=synthetic.RandomStateProvider(cfg, str(device), seed=0))
         worker.load_shards(start, end)
     hop_lat = None
@@ -178,6 +268,81 @@ def run_chain(args, config, metric, ClockSampler, peaks):
     err = torch.tensor([stage.error()], dtype=torch.float64)
     dist.all_reduce(err, op=dist.ReduceOp.MAX, group=ctrl)
 
+    # ---- the named configurations of BASELINE.json on the same worker and the same ring code
+    c3 = c4 = None
+    if extras:
+        clear_all()
+        stage.close()
+        pk = peaks()
+
+        def ring(n_str, r, prompt_len):
+            st = ChainStage(worker, rank, world, n_str, prompt_len, ctrl_group=ctrl, transport=transport, rows=r)
+            gp = torch.Generator().manual_seed(4321)
+            pr = [torch.randint(3, cfg["vocab_size"], (r * prompt_len,), generator=gp, dtype=torch.int64).to(device) for _ in range(n_str)]
+            return st, pr
+
+        def reset(st):
+            torch.cuda.synchronize()
+            dist.barrier(group=ctrl)
+            worker.past_key_value.reset(-1)
+            st.sched.clear()
+            torch.cuda.synchronize()
+            dist.barrier(group=ctrl)
+
+        # configs[2]: micro-batched batch-32 decode = N streams x 32/N rows, 128-token context, 128 decode rounds
+        st3, pr3 = ring(world, c3_rows, c3_prompt)
+        for i in range(world):
+            st3.prefill(i, c3_prompt, pr3[i] if rank == 0 else None)
+        for _ in range(W):
+            for i in range(world):
+                st3.decode(i)
+        torch.cuda.synchronize()
+        eng.reset_counters()
+        c3_ms = timed(lambda: [st3.decode(i) for _ in range(c3_steps) for i in range(world)]) / c3_steps
+        c3_cnt = eng.counters()
+        c3_b = torch.tensor([c3_cnt["bytes"] / max(1, c3_cnt["calls"])], dtype=torch.float64)
+        dist.all_reduce(c3_b, op=dist.ReduceOp.MAX, group=ctrl)
+        reset(st3)
+        for i in range(world):
+            st3.prefill(i, c3_prompt, pr3[i] if rank == 0 else None)
+        for _ in range(W):
+            for i in range(world):
+                st3.decode(i, via_host=True)
+        c3_e2e_ms = timed(lambda: [st3.decode(i, via_host=True) for _ in range(c3_steps) for i in range(world)]) / c3_steps
+        c3_err = st3.error()
+        reset(st3)
+        st3.close()
+        stage_s = c3_ms / 1000 / world
+        c3 = {"workload": f"BASELINE.json configs[2]: batch 32 as {world} micro-batches of {c3_rows} rows in flight on the {world}-way "
+                          f"chain, {c3_prompt}-token context, {c3_steps} decode rounds timed",
+              "tok_s": 32 * 1000.0 / c3_ms, "ms_per_round": c3_ms, "e2e_tok_s": 32 * 1000.0 / c3_e2e_ms,
+              "stage_bytes_per_call": float(c3_b[0]), "stage_hbm_gbs": float(c3_b[0]) / stage_s / 1e9,
+              "stage_hbm_frac": float(c3_b[0]) / stage_s / 1e9 / pk["hbm_gbs"], "hop_error_flag": int(c3_err)}
+
+        # configs[3]: prefill-heavy, 16 x 2048-token prompts through the whole chain as 16 micro-batches of one prompt
+        st4, pr4 = ring(c4_streams, 1, c4_prompt)
+
+        def prefill16():
+            for i in range(c4_streams):
+                st4.prefill(i, c4_prompt, pr4[i] if rank == 0 else None)
+        prefill16()
+        reset(st4)
+        c4_ms = timed(prefill16)
+        c4_err = st4.error()
+        reset(st4)
+        st4.close()
+        S4, L4, H4 = c4_prompt, cfg["num_hidden_layers"], cfg["hidden_size"]
+        layer_params = 4 * H4 * H4 + 3 * H4 * cfg["intermediate_size"]
+        flops = c4_streams * (S4 * L4 * 2 * layer_params + L4 * 4 * S4 * S4 * H4) + c4_streams * 2 * H4 * cfg["vocab_size"]
+        c4 = {"workload": f"BASELINE.json configs[3]: {c4_streams} x {c4_prompt}-token prompts through the {world}-way chain "
+                          f"({c4_streams} micro-batches of 1 prompt, non-causal attention as the reference), first token of each produced",
+              "tok_s": c4_streams * S4 * 1000.0 / c4_ms, "ms": c4_ms, "flops": flops,
+              "tflops_whole_job": flops / (c4_ms / 1000) / 1e12,
+              "frac_of_tensor_peak": flops / (c4_ms / 1000) / 1e12 / (world * pk["bf16_tflops"]),
+              "peak_tflops_per_gpu": pk["bf16_tflops"],
+              "pipeline_fill_bound": c4_streams / (c4_streams + world - 1), "hop_error_flag": int(c4_err)}
+        stage = None
+
     if rank == 0:
         pk = peaks()
         per_gpu_bytes = float(bmax[0]) / max(1, cnt["calls"])  # algorithmic bytes of one stage call (largest stage)
@@ -196,11 +361,15 @@ def run_chain(args, config, metric, ClockSampler, peaks):
                          "frac": per_gpu_bytes / (stage_ms / 1000) / 1e9 / pk["hbm_gbs"], "traffic": None, "peak_source": pk["source"]},
             "hop": hop_lat, "hop_error_flag": int(err[0]),
             "prefill_tok_s": prefill_tok_s, "p50_token_ms": ms_per_step,
+            "parity": parity, "c3_batch32": c3, "c4_prefill": c4,
         }
         print(json.dumps(line), flush=True)
     dist.barrier(group=ctrl)
-    stage.close()
+    if stage is not None:
+        stage.close()
     dist.destroy_process_group()
+    if parity is not None and not parity["ok"]:
+        raise SystemExit(3)   # a ring whose output differs from the oracle's has no valid throughput number
 
 
 MIX_LENGTHS = (32, 512, 2048)

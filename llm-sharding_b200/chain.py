@@ -213,6 +213,11 @@ class RingSchedule:
         return item
 
     def clear(self) -> None:
+        """Drop every request (all stages call this at the same point, after draining their streams).  Tokens the tail
+        already sent back and the head never consumed are skipped, so that both ends of every hop keep the same count:
+        otherwise the head's next wait would be satisfied by a stale flag of a dropped request."""
+        if self.is_head:
+            self.seq_in += len(self._owed)
         self.prefilled = [False] * self.n_streams
         self._owed = []
 
@@ -283,6 +288,8 @@ class ChainStage:
             dist.barrier(group=ctrl_group)
         self.tokens = []       # head: device int64[1] tensors, one per recorded decode
         self.host_tokens = []  # head, via_host mode: python ints
+        self.record_inbound = False  # non-head stages: keep a copy of every hidden state that arrives (parity checks)
+        self.inbound = []            # (stream, S, bf16 tensor [rows, S, H])
 
     # -- raw-pointer plumbing
     def _st(self):
@@ -326,6 +333,10 @@ class ChainStage:
         out_bytes = tok_bytes if sch.is_tail else hid_bytes
         self._wait(item, in_bytes)
         out_ptr = self._out_ptr(item)
+        if self.record_inbound and not sch.is_head:
+            src = (tensor_view(self._in_ptr(item), hid_bytes, self.device) if self.hop is not None
+                   else self.inbuf[item["wait"][1]][:hid_bytes])
+            self.inbound.append((item["stream"], S, src.view(torch.bfloat16).view(B, S, self.H).clone()))
         if sch.is_head:
             if tok_in_ptr is None:
                 tok_in_ptr = self._in_ptr(item)

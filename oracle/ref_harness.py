@@ -1,8 +1,13 @@
 """TEST INFRASTRUCTURE — drives the REAL reference (``/root/reference``) in-process.
 
-Only usable in the build container (the GPU box has no ``/root/reference``): it is how
+In the build container the reference is imported from ``/root/reference``: that is how
 ``tests/golden/*.npz`` are produced (``oracle/make_golden.py``) and how the restatement in
-``llama_oracle.py`` is validated.  The reference's files are imported unmodified; two
+``llama_oracle.py`` is validated.  The GPU box has no ``/root/reference``; there the same six
+files are found under ``baseline/_ref/utils/`` — a git-ignored, verbatim copy made by
+``__graft_entry__.build()`` (an output directory like a compiled ``.so``: never committed,
+never edited) — and are used ONLY by ``bench.py``'s CPU-baseline legs
+(``oracle/ref_chain_bench.py``), never by the ``-m gpu`` tests or ``smoke()``.
+The reference's files are imported unmodified; two
 compat points are patched from outside because this image has transformers 5.5.0 while
 the reference pins 4.53.2:
 
@@ -25,7 +30,8 @@ import sys
 
 import torch
 
-REFERENCE_ROOT = "/root/reference"
+_HERE = os.path.dirname(os.path.abspath(__file__))
+REFERENCE_ROOT = "/root/reference" if os.path.isfile("/root/reference/utils/node_worker.py") else os.path.join(os.path.dirname(_HERE), "baseline", "_ref")
 _shim_applied = False
 
 

@@ -48,6 +48,26 @@ def test_ring_schedule_slots_are_stable_per_stream():
         RingSchedule(0, 2, 2).decode(1)
 
 
+def test_clear_keeps_both_ends_of_the_token_hop_counting_alike():
+    """bench_chain.py prefills, clears (no token was consumed) and prefills again: afterwards the head must wait for the
+    very message the tail sends next, not for one whose flag a dropped request already published."""
+    world, n_streams = 3, 2
+    scheds = [RingSchedule(r, world, n_streams) for r in range(world)]
+    for _ in range(2):
+        for i in range(n_streams):
+            for s in scheds:
+                s.prefill(i)
+        for s in scheds:
+            s.clear()
+    tail_sends = []
+    for i in range(n_streams):
+        for s in scheds:
+            it = s.prefill(i)
+        tail_sends.append(it["send"])
+    for i in range(n_streams):
+        assert scheds[0].decode(i)["wait"] == tail_sends[i]
+
+
 def test_finish_keeps_the_ring_counts_aligned_under_a_mixed_schedule():
     """Streams are retired and given new prompts while the others keep decoding (BASELINE configs[4]): every message a
     stage produces is consumed by its successor, in order, for the stream it was meant for, and the messages in flight
