@@ -151,6 +151,20 @@ B200_API int b200_hop_recv(b200_hop_t* h, void* d_out, int64_t bytes, uint64_t s
  * consumer calls b200_hop_recv with d_out == NULL (wait only) and lets its first kernel read b200_hop_local_slot. */
 B200_API void* b200_hop_peer_slot(b200_hop_t* h, uint64_t seq);
 B200_API void* b200_hop_local_slot(b200_hop_t* h, uint64_t seq);
+/* Whole messages for a host-driven loop (NodeController.run_worker_loop, utils/node_worker.py:493-559, which receives,
+ * classifies and dispatches on the host): a header of at most B200_HOP_HEADER_BYTES describing the message (kind, shapes,
+ * dtype, pos_offset, slots: whatever the caller's wire format needs, opaque to the library) is stored at the start of
+ * the peer's ring slot by the same kernel that copies the payload behind it and releases the flag, so the tensor never
+ * leaves device memory and nothing is pickled (the reference's transfer_data does torch.save -> file -> socket,
+ * utils/node_worker.py:44-54).  slot_bytes of the receiver must hold header + payload. */
+#define B200_HOP_HEADER_BYTES 256
+B200_API int b200_hop_send_msg(b200_hop_t* h, const void* h_header, int header_bytes, const void* d_payload, int64_t bytes,
+                               uint64_t seq, void* stream);
+/* Non-blocking receive_data(no_block=True) (utils/node_worker.py:56-67): 1 and the header in h_header_out
+ * (B200_HOP_HEADER_BYTES) when message `seq` has arrived, 0 when it has not (zmq.Again in the reference), < 0 on error.
+ * The payload then sits at b200_hop_local_slot(h, seq) + B200_HOP_HEADER_BYTES in device memory.  Uses a private stream:
+ * never waits for work queued on the caller's streams. */
+B200_API int b200_hop_poll(b200_hop_t* h, uint64_t seq, void* h_header_out);
 B200_API int b200_hop_error(b200_hop_t* h); /* nonzero once a recv kernel timed out */
 B200_API int b200_hop_destroy(b200_hop_t* h);
 

@@ -18,6 +18,7 @@ LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "lib", "libb
 OK, EINVAL, ESTATE, ECUDA, ENOMEM, ETIMEOUT = 0, -1, -2, -3, -4, -5
 DT_BF16, DT_F32, DT_F16 = 0, 1, 2
 HOP_HANDLE_BYTES = 80
+HOP_HEADER_BYTES = 256
 
 TORCH_TO_DT = {torch.bfloat16: DT_BF16, torch.float32: DT_F32, torch.float16: DT_F16}
 
@@ -58,6 +59,8 @@ PROTOTYPES = {
     "b200_hop_connect": (_I, [_P, _P, _I, _I]),
     "b200_hop_send": (_I, [_P, _P, _I64, _U64, _P]),
     "b200_hop_recv": (_I, [_P, _P, _I64, _U64, _I64, _P]),
+    "b200_hop_send_msg": (_I, [_P, _P, _I, _P, _I64, _U64, _P]),
+    "b200_hop_poll": (_I, [_P, _U64, _P]),
     "b200_hop_peer_slot": (_P, [_P, _U64]),
     "b200_hop_local_slot": (_P, [_P, _U64]),
     "b200_hop_error": (_I, [_P]),

@@ -799,6 +799,8 @@ struct b200_hop {
     int* err = nullptr;
     int n_slots_peer = 0;
     int64_t slot_bytes_peer = 0;
+    cudaStream_t poll_stream = nullptr;  // host polls of the flag / header must not queue behind the compute stream
+    uint64_t* h_poll = nullptr;          // pinned: [0] flag, then the 256-byte header
 };
 struct HopHandle {  // exactly B200_HOP_HANDLE_BYTES
     cudaIpcMemHandle_t ipc;  // 64 bytes, valid across processes
@@ -913,6 +915,45 @@ extern "C" B200_API int b200_hop_recv(b200_hop_t* h, void* out, int64_t bytes, u
     CU_TRY(cudaGetLastError());
     return 0;
 }
+extern "C" B200_API int b200_hop_send_msg(b200_hop_t* h, const void* h_header, int header_bytes, const void* d_payload,
+                                          int64_t bytes, uint64_t seq, void* stream) {
+    if (h == nullptr || h->peer == nullptr) return fail(B200_ESTATE, "[ERROR] hop has no connected peer");
+    if (header_bytes < 0 || header_bytes > kHopHeaderBytes || (header_bytes > 0 && h_header == nullptr))
+        return fail(B200_EINVAL, "[ERROR] hop message header must be at most %d bytes", kHopHeaderBytes);
+    if (bytes < 0 || bytes + kHopHeaderBytes > h->slot_bytes_peer || (bytes > 0 && d_payload == nullptr))
+        return fail(B200_EINVAL, "[ERROR] hop message of %lld + %d bytes exceeds the peer's slot (%lld)", (long long)bytes,
+                    kHopHeaderBytes, (long long)h->slot_bytes_peer);
+    CU_TRY(cudaSetDevice(h->device));
+    HopHeader hdr;
+    memset(hdr.b, 0, sizeof(hdr.b));
+    if (header_bytes > 0) memcpy(hdr.b, h_header, (size_t)header_bytes);
+    const int slot = (int)(seq % (uint64_t)h->n_slots_peer);
+    char* pslot = h->peer + (size_t)slot * h->slot_bytes_peer;
+    uint64_t* pflag = reinterpret_cast<uint64_t*>(h->peer + (size_t)h->n_slots_peer * h->slot_bytes_peer) + slot;
+    launch_hop_send_msg(hdr, d_payload, bytes, pslot, pflag, seq, h->counter, (cudaStream_t)stream);
+    CU_TRY(cudaGetLastError());
+    return 0;
+}
+extern "C" B200_API int b200_hop_poll(b200_hop_t* h, uint64_t seq, void* h_header_out) {
+    if (h == nullptr) return fail(B200_EINVAL, "[ERROR] null argument");
+    CU_TRY(cudaSetDevice(h->device));
+    if (h->poll_stream == nullptr) {
+        CU_TRY(cudaStreamCreateWithFlags(&h->poll_stream, cudaStreamNonBlocking));
+        CU_TRY(cudaHostAlloc(reinterpret_cast<void**>(&h->h_poll), 8 + kHopHeaderBytes, cudaHostAllocDefault));
+    }
+    const int slot = (int)(seq % (uint64_t)h->n_slots);
+    const uint64_t* lflag = reinterpret_cast<const uint64_t*>(h->local + (size_t)h->n_slots * h->slot_bytes) + slot;
+    CU_TRY(cudaMemcpyAsync(h->h_poll, lflag, 8, cudaMemcpyDeviceToHost, h->poll_stream));
+    CU_TRY(cudaStreamSynchronize(h->poll_stream));
+    if (h->h_poll[0] < seq + 1) return 0;  // not there yet
+    if (h_header_out != nullptr) {
+        // the flag was released after the header and the payload: a copy ordered after the flag read sees both
+        CU_TRY(cudaMemcpyAsync(h->h_poll + 1, h->local + (size_t)slot * h->slot_bytes, kHopHeaderBytes, cudaMemcpyDeviceToHost, h->poll_stream));
+        CU_TRY(cudaStreamSynchronize(h->poll_stream));
+        memcpy(h_header_out, h->h_poll + 1, kHopHeaderBytes);
+    }
+    return 1;
+}
 extern "C" B200_API int b200_hop_error(b200_hop_t* h) {
     if (h == nullptr) return 0;
     int v = 0;
@@ -925,6 +966,8 @@ extern "C" B200_API int b200_hop_destroy(b200_hop_t* h) {
     cudaSetDevice(h->device);
     cudaDeviceSynchronize();
     if (h->peer != nullptr && h->peer_ipc) cudaIpcCloseMemHandle(h->peer);
+    if (h->poll_stream != nullptr) cudaStreamDestroy(h->poll_stream);
+    if (h->h_poll != nullptr) cudaFreeHost(h->h_poll);
     cudaFree(h->local);
     cudaFree(h->counter);
     delete h;

@@ -57,6 +57,30 @@ __global__ void __launch_bounds__(1024) hop_recv_kernel(uint4* __restrict__ dst,
         dst[i] = local_slot[i];
 }
 
+// Message = 256-byte header (built on the host, passed by value as a kernel parameter: no staging copy) + payload.
+// The header lands at the start of the peer's slot, the payload right behind it, then the flag is released.
+__global__ void __launch_bounds__(1024) hop_send_msg_kernel(const HopHeader hdr, const uint4* __restrict__ src, int64_t n16,
+                                                            uint4* peer_slot, uint64_t* peer_flag, uint64_t seq,
+                                                            unsigned int* counter) {
+    if (blockIdx.x == 0 && threadIdx.x < kHopHeaderBytes / 16) peer_slot[threadIdx.x] = reinterpret_cast<const uint4*>(hdr.b)[threadIdx.x];
+    uint4* dst = peer_slot + kHopHeaderBytes / 16;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += (int64_t)gridDim.x * blockDim.x) dst[i] = src[i];
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        bool last = true;
+        if (gridDim.x > 1) {
+            const unsigned int done = atomicAdd(counter, 1u) + 1u;
+            last = (done == gridDim.x);
+            if (last) {
+                *counter = 0u;
+                __threadfence_system();
+            }
+        }
+        if (last) st_release_sys(peer_flag, seq + 1);
+    }
+}
+
 static int hop_grid(int64_t n16) {
     int64_t g = (n16 + 1024 * 4 - 1) / (1024 * 4);
     if (g < 1) g = 1;
@@ -69,6 +93,12 @@ void launch_hop_send(const void* payload, int64_t bytes, void* peer_slot, uint64
     const int64_t n16 = (bytes + 15) / 16;
     hop_send_kernel<<<hop_grid(payload ? n16 : 0), payload ? 1024 : 32, 0, st>>>(reinterpret_cast<const uint4*>(payload), payload ? n16 : 0,
                                                     reinterpret_cast<uint4*>(peer_slot), peer_flag, seq, counter);
+}
+void launch_hop_send_msg(const HopHeader& hdr, const void* payload, int64_t bytes, void* peer_slot, uint64_t* peer_flag,
+                         uint64_t seq, unsigned int* counter, cudaStream_t st) {
+    const int64_t n16 = (bytes + 15) / 16;
+    hop_send_msg_kernel<<<hop_grid(n16), n16 > 0 ? 1024 : 32, 0, st>>>(hdr, reinterpret_cast<const uint4*>(payload), n16,
+                                                                       reinterpret_cast<uint4*>(peer_slot), peer_flag, seq, counter);
 }
 void launch_hop_recv(void* out, int64_t bytes, const void* local_slot, const uint64_t* local_flag, uint64_t seq,
                      int64_t max_wait_cycles, int* err, cudaStream_t st) {

@@ -168,6 +168,10 @@ const char* gemm_error();
 void set_last_error(const char* msg);
 
 // hop
+constexpr int kHopHeaderBytes = 256;
+struct HopHeader { unsigned char b[kHopHeaderBytes]; };
+void launch_hop_send_msg(const HopHeader& hdr, const void* payload, int64_t bytes, void* peer_slot, uint64_t* peer_flag,
+                         uint64_t seq, unsigned int* counter, cudaStream_t st);
 // payload == nullptr: the payload was already written in place; only publish the flag
 void launch_hop_send(const void* payload, int64_t bytes, void* peer_slot, uint64_t* peer_flag, uint64_t seq,
                      unsigned int* counter, cudaStream_t st);

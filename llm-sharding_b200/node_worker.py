@@ -97,15 +97,24 @@ class NodeWorker:
     CLEAR_KV_CACHE_ORIGIN_KEY = "origin_node"
 
     def __init__(self, src_addr: str, dst_addr: str, can_receive_user_request: bool, shards_path: str,
-                 device="cuda:0", dtype=torch.bfloat16, *, communicator=None, max_tokens: int = 4096,
+                 device="cuda:0", dtype=torch.bfloat16, *, communicator=None, transport: str = "zmq", max_tokens: int = 4096,
                  max_batch: int = 1, max_slots: int | None = None, max_seq_len: int | None = None,
                  causal: bool = False, use_graphs: bool = True, state_provider=None):
-        """Positional parameters as in the reference (utils/node_worker.py:75-76).  ``communicator``
-        lets the chain runtime inject a P2P transport; ``causal=False`` is the reference's
-        (non-causal prefill) behaviour."""
+        """Positional parameters as in the reference (utils/node_worker.py:75-76).  ``transport="p2p"``
+        replaces the ZeroMQ data path by the NVLink mailbox (``P2PCommunicator``, same interface; the nodes must share
+        one NVSwitch box), ``"zmq"`` is the reference's; ``communicator`` injects a ready-made one.  ``causal=False`` is
+        the reference's (non-causal prefill) behaviour."""
         from .engine import read_model_config
 
-        self.communicator = communicator if communicator is not None else Communicator(src_addr, dst_addr)
+        if communicator is None:
+            if transport == "p2p":
+                from .p2p_communicator import P2PCommunicator
+                communicator = P2PCommunicator(src_addr, dst_addr, device=device)
+            elif transport == "zmq":
+                communicator = Communicator(src_addr, dst_addr)
+            else:
+                raise ValueError(f"[ERROR] unknown transport {transport!r} (zmq or p2p)")
+        self.communicator = communicator
         self.can_receive_user_request = can_receive_user_request
         self.shards_path = shards_path
         self.device = torch.device(device)
@@ -379,6 +388,10 @@ class NodeController:
         print("[INFO] The new configuration node is ready.")
 
     def _forward_request(self, data: dict, data_path: str = "results/send_request.pt", keep_data: bool = False):
+        comm = self.node_worker.communicator
+        if hasattr(comm, "forward_request"):   # P2P transport: no pickle on any socket
+            comm.forward_request(data, self.first_node_addr, self.send_request_socket)
+            return None
         buf = io.BytesIO()
         torch.save(Communicator._to_wire(data), buf)
         self.send_request_socket.send(buf.getvalue())
