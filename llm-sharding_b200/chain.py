@@ -405,3 +405,155 @@ class ChainStage:
     def close(self) -> None:
         if self.hop is not None:
             self.hop.close()
+
+
+# ----------------------------------------------------------------------------------------------
+# Stop rules inside the ring: the reference's run_worker_loop / receive_next_token decide on the HEAD node when a request
+# is over (EOS, or len(generated_ids) > max_new_tokens, utils/node_worker.py:290-299) and then send a clear-cache
+# command around the ring (:357-382, :507-524).  With several requests in flight the same decisions are taken per
+# stream: RingPlanner (pure host logic, head only) turns "what the head has seen so far" into one action per stream and
+# round, RingServer broadcasts that plan over the control group and every stage enqueues the same work items.
+# ----------------------------------------------------------------------------------------------
+ACT_IDLE, ACT_DECODE, ACT_FINISH, ACT_STOP = 0, -1, -2, -9   # a positive action is a prefill of that many prompt tokens
+
+
+class RingPlanner:
+    """Per-stream request state on the head.  `max_new_tokens` is the reference's rule: exactly that many tokens are
+    produced and the last one is not fed back; it is applied without looking at any token, so no work
+    is wasted.  The EOS rule needs token values, which reach the head's host a little after the ring has moved on: a
+    request that hit EOS is retired at the first round that knows about it and its output is cut at the EOS token."""
+
+    def __init__(self, n_streams: int, rows: int = 1, eos_token_id: int | None = None):
+        self.n_streams, self.rows, self.eos = n_streams, rows, eos_token_id
+        self.pending = []                       # (request id, prompt_len, max_new_tokens)
+        self.active = [None] * n_streams        # per stream: id of the request it serves
+        self.reqs = {}                          # request id -> dict(req, issued, max_new, eos_seen, row_eos, tokens)
+        self.done = {}                          # request id -> list of per-step token lists
+        self._next_id = 0
+
+    def submit(self, prompt_len: int, max_new_tokens: int) -> int:
+        if prompt_len < 1 or max_new_tokens < 1:
+            raise ValueError("[ERROR] a request needs at least one prompt token and one new token")
+        rid = self._next_id
+        self._next_id += 1
+        self.pending.append((rid, prompt_len, max_new_tokens))
+        return rid
+
+    def observe(self, stream: int, request: int, tokens: list) -> None:
+        """A token (one id per row) of `request` reached the head's host."""
+        st = self.reqs.get(request)
+        if st is None or st["eos_seen"]:
+            return                                # produced after the EOS: dropped
+        st["tokens"].append(list(tokens))
+        if self.eos is not None:
+            for r, t in enumerate(tokens):
+                st["row_eos"][r] = st["row_eos"][r] or t == self.eos
+            if all(st["row_eos"]):
+                st["eos_seen"] = True
+
+    def plan(self) -> list:
+        """Actions of the next round, one per stream: [finish?, action] pairs flattened to 2 * n_streams ints."""
+        out = []
+        for i in range(self.n_streams):
+            a = self.reqs[self.active[i]] if self.active[i] is not None else None
+            fin, act = 0, ACT_IDLE
+            if a is not None:
+                if a["eos_seen"] or a["issued"] >= a["max_new"]:
+                    fin = 1
+                    self.done[a["req"]] = a["tokens"]
+                    self.active[i] = a = None
+                else:
+                    act = ACT_DECODE
+                    a["issued"] += 1
+            if a is None and self.pending:
+                rid, plen, mnt = self.pending.pop(0)
+                self.reqs[rid] = {"req": rid, "issued": 1, "max_new": mnt, "eos_seen": False, "tokens": [],
+                                  "row_eos": [False] * self.rows}
+                self.active[i] = rid
+                act = plen
+            out += [fin, act]
+        return out
+
+    def idle(self) -> bool:
+        return not self.pending and all(a is None for a in self.active)
+
+
+class RingServer:
+    """The generalised run_worker_loop of one stage: rounds of per-stream actions, planned on the head (rank 0) and
+    broadcast over the control group (`dist` gloo group; `None` for a one-stage ring).  The head needs the prompts
+    (`submit`), the other stages only their turn in `serve()`."""
+
+    def __init__(self, stage: ChainStage, ctrl_group=None, eos_token_id: int | None = None):
+        self.stage, self.ctrl = stage, ctrl_group
+        self.is_head = stage.sched.is_head
+        self.planner = RingPlanner(stage.n_streams, stage.rows, eos_token_id) if self.is_head else None
+        self.prompts = {}        # head: request id -> ids [rows, S] on this GPU
+        self._stream_req = [None] * stage.n_streams
+        self._records = []       # head: (stream, request, index into stage.tokens)
+        self._seen = 0
+
+    def submit(self, ids: torch.Tensor, max_new_tokens: int) -> int:
+        if not self.is_head:
+            raise RuntimeError("[ERROR] this node cannot receive user request.")
+        if ids.ndim != 2 or ids.shape[0] != self.stage.rows:
+            raise ValueError("[ERROR] input_ids must be a 2D tensor with shape [batch_size, seq_len].")
+        rid = self.planner.submit(ids.shape[1], max_new_tokens)
+        self.prompts[rid] = ids.to(device=self.stage.device, dtype=torch.long).contiguous()
+        return rid
+
+    def _drain_tokens(self, block: bool) -> None:
+        """Move the tokens whose copies have completed from the device to the planner (never blocks unless asked)."""
+        while self._seen < len(self._records):
+            stream, req, idx, ev = self._records[self._seen]
+            if not block and not ev.query():
+                return
+            ev.synchronize()
+            self.planner.observe(stream, req, self.stage.tokens[idx].tolist())
+            self._seen += 1
+
+    def _exchange(self, plan: list) -> list:
+        if self.ctrl is None or self.stage.world == 1:
+            return plan
+        t = torch.tensor(plan if self.is_head else [0] * (2 * self.stage.n_streams), dtype=torch.int64)
+        self.stage.dist.broadcast(t, src=0, group=self.ctrl)
+        return t.tolist()
+
+    def _record(self, stream: int) -> None:
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(self.stage.device))
+        self._records.append((stream, self._stream_req[stream], len(self.stage.tokens) - 1, ev))
+
+    def serve(self, max_rounds: int = 1 << 30) -> dict:
+        """Run rounds until every submitted request is finished (head's decision).  Returns, on the head,
+        {request id: int64 tensor [n_tokens, rows]}; {} elsewhere."""
+        st = self.stage
+        for _ in range(max_rounds):
+            if self.is_head:
+                self._drain_tokens(block=False)
+                plan = [ACT_STOP] * (2 * st.n_streams) if self.planner.idle() else self.planner.plan()
+            else:
+                plan = None
+            plan = self._exchange(plan)
+            if plan[1] == ACT_STOP:
+                break
+            for i in range(st.n_streams):
+                fin, act = plan[2 * i], plan[2 * i + 1]
+                if fin:
+                    st.finish(i, record=self.is_head)
+                    if self.is_head:
+                        self._record(i)
+                if act == ACT_DECODE:
+                    st.decode(i, record=self.is_head)
+                    if self.is_head:
+                        self._record(i)
+                elif act > 0:
+                    ids = None
+                    if self.is_head:
+                        rid = self.planner.active[i]
+                        self._stream_req[i] = rid
+                        ids = self.prompts.pop(rid).reshape(-1)
+                    st.prefill(i, act, ids)
+        if not self.is_head:
+            return {}
+        self._drain_tokens(block=True)
+        return {rid: torch.tensor(toks, dtype=torch.int64) for rid, toks in self.planner.done.items()}

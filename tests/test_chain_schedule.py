@@ -220,3 +220,130 @@ def test_ring_protocol_two_processes_gloo():
     assert [g[1] for g in gathered] == [(0, 16), (16, 32)]
     # the last message a stage handled has travelled (rounds * world + rank) hops around the ring
     assert [g[2] for g in gathered] == [rounds * world + r for r in range(world)]
+
+
+# ---------------------------------------------------------------------------------------------- stop rules in the ring
+class _FakeStage:
+    """Records the work items a RingServer enqueues; tokens are made up by `token_fn(stream, k)` on the head."""
+
+    def __init__(self, rank, world, n_streams, rows=1, token_fn=None):
+        from llm_sharding_b200.chain import RingSchedule
+        self.sched = RingSchedule(rank, world, n_streams)
+        self.rank, self.world, self.n_streams, self.rows = rank, world, n_streams, rows
+        self.device = torch.device("cpu")
+        self.dist = dist
+        self.tokens, self.log = [], []
+        self.token_fn = token_fn or (lambda stream, nth, k: 100 * stream + k)
+        self._count = [0] * n_streams
+        self._nth = [-1] * n_streams     # how many requests this stream has started, minus one
+
+    def _tok(self, stream):
+        k = self._count[stream]
+        self._count[stream] += 1
+        self.tokens.append(torch.tensor([self.token_fn(stream, self._nth[stream], k)] * self.rows))
+
+    def prefill(self, stream, prompt_len, ids=None):
+        self.sched.prefill(stream)
+        self._count[stream] = 0
+        self._nth[stream] += 1
+        self.log.append(("prefill", stream, prompt_len))
+
+    def decode(self, stream, record=False, via_host=False):
+        self.sched.decode(stream)
+        if record:
+            self._tok(stream)
+        self.log.append(("decode", stream))
+
+    def finish(self, stream, record=False):
+        self.sched.finish(stream)
+        if record:
+            self._tok(stream)
+        self.log.append(("finish", stream))
+
+
+class _NoEvent:
+    def record(self, *a): pass
+    def query(self): return True
+    def synchronize(self): pass
+
+
+def test_ring_server_applies_the_reference_stop_rules_per_stream(monkeypatch):
+    """max_new_tokens gives exactly that many tokens per request (utils/node_worker.py:291: the last token is not fed
+    back); an EOS ends the request early and cuts its output there; a freed stream takes the next queued prompt at once."""
+    from llm_sharding_b200 import chain
+    monkeypatch.setattr(torch.cuda, "Event", lambda *a, **k: _NoEvent())
+    monkeypatch.setattr(torch.cuda, "current_stream", lambda *a, **k: None)
+    EOS = 2
+    # the second request served by stream 1 (r2) emits EOS as its third token although it may produce six
+
+    def token_fn(stream, nth, k):
+        return EOS if (stream == 1 and nth == 1 and k == 2) else 10 * (stream + 1) + k + 1
+
+    stage = _FakeStage(0, 1, 2, token_fn=token_fn)
+    srv = chain.RingServer(stage, None, eos_token_id=EOS)
+    r0 = srv.submit(torch.zeros(1, 5, dtype=torch.long), 4)
+    r1 = srv.submit(torch.zeros(1, 9, dtype=torch.long), 2)
+    r2 = srv.submit(torch.zeros(1, 3, dtype=torch.long), 6)   # lands on whichever stream frees first (stream 1)
+    out = srv.serve()
+    assert [t for t in out[r0][:, 0].tolist()] == [11, 12, 13, 14]
+    assert [t for t in out[r1][:, 0].tolist()] == [21, 22]
+    assert out[r2][:, 0].tolist() == [21, 22, EOS]           # cut at the EOS although max_new_tokens was 6
+    kinds = [e[0] for e in stage.log]
+    assert kinds.count("prefill") == 3 and kinds.count("finish") == 3
+    # request r0: prefill + 3 decodes + finish = 4 tokens; nothing is decoded for a finished stream
+    assert [e for e in stage.log if e[1] == 0][:5] == [("prefill", 0, 5), ("decode", 0), ("decode", 0), ("decode", 0), ("finish", 0)]
+
+
+def test_ring_planner_eos_cuts_the_output_and_retires_the_stream():
+    from llm_sharding_b200.chain import ACT_DECODE, ACT_IDLE, RingPlanner
+    p = RingPlanner(1, rows=2, eos_token_id=2)
+    rid = p.submit(4, 10)
+    assert p.plan() == [0, 4]
+    p.observe(0, rid, [7, 2])            # one row hit EOS: the micro-batch goes on until every row has
+    assert p.plan() == [0, ACT_DECODE]
+    p.observe(0, rid, [2, 9])
+    assert p.plan() == [1, ACT_IDLE]     # retired at the first round that knows
+    p.observe(0, rid, [5, 5])            # a token that was already on its way: dropped
+    assert p.done[rid] == [[7, 2], [2, 9]] and p.idle()
+    with pytest.raises(ValueError):
+        p.submit(0, 3)
+
+
+def _server_proc(rank, world, port, q):
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from llm_sharding_b200 import chain
+        torch.cuda.Event = lambda *a, **k: _NoEvent()
+        torch.cuda.current_stream = lambda *a, **k: None
+        stage = _FakeStage(rank, world, 2)
+        srv = chain.RingServer(stage, dist.group.WORLD)
+        if rank == 0:
+            srv.submit(torch.zeros(1, 6, dtype=torch.long), 3)
+            srv.submit(torch.zeros(1, 2, dtype=torch.long), 5)
+            srv.submit(torch.zeros(1, 8, dtype=torch.long), 1)
+        out = srv.serve()
+        q.put((rank, stage.log, {k: v.tolist() for k, v in out.items()}))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_ring_server_plan_reaches_every_stage_gloo():
+    """world_size 2 on gloo: the head's per-round plan is broadcast and both stages enqueue the same work items."""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    procs = [ctx.Process(target=_server_proc, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = dict()
+    for _ in range(2):
+        rank, log, out = q.get(timeout=120)
+        got[rank] = (log, out)
+    for p in procs:
+        p.join(60)
+    assert all(p.exitcode == 0 for p in procs)
+    assert got[0][0] == got[1][0] and len(got[0][0]) > 0
+    assert {k: len(v) for k, v in got[0][1].items()} == {0: 3, 1: 5, 2: 1} and got[1][1] == {}
