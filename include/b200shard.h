@@ -12,9 +12,9 @@
  * Conventions: every function returns 0 on success or a negative B200_E* code (no C++
  * exception crosses the ABI); b200_last_error() gives the message for the calling thread.
  * Pointers named d_* are DEVICE pointers owned by the caller; h_* are host pointers.
- * `stream` is a cudaStream_t passed as void*.  All activations crossing the ABI are bf16
- * ("model dtype" of the reference's messages, utils/node_worker.py:252,267-271); token ids
- * are int64 like torch.long (utils/node_worker.py:208,264).
+ * `stream` is a cudaStream_t passed as void*.  Activations crossing the ABI are bf16 unless
+ * b200_shard_set_io_dtype chose fp16 / fp32 ("model dtype" of the reference's messages,
+ * utils/node_worker.py:252,267-271); token ids are int64 like torch.long (utils/node_worker.py:208,264).
  */
 #ifndef B200SHARD_H
 #define B200SHARD_H
@@ -82,6 +82,11 @@ B200_API int b200_shard_set_embedding(b200_shard_t* s, const void* d_weight, int
  * 1 / rope_theta^(2j/128) (compute_default_rope_parameters, modeling_llama.py:93-120); scaled variants such as the
  * Llama-3.x "llama3" rope_type (transformers modeling_rope_utils.py:550-626) are computed by the host and set here. */
 B200_API int b200_shard_set_rope_inv_freq(b200_shard_t* s, const float* h_inv_freq, int n);
+/* Element type of the hidden states that cross the ABI (d_hidden_in / d_hidden_out of the forward calls, b200_shard_embed's
+ * output, b200_shard_lm_head_argmax's input): B200_DT_BF16 (default), B200_DT_F16 or B200_DT_F32 — the dtype the node was
+ * started with (start_node.py:16-17 uses float16; utils/node_worker.py:252 casts incoming messages to it).  Only the
+ * boundary changes: inside, the residual stream stays fp32 and the operands stay as described in DESIGN.md. */
+B200_API int b200_shard_set_io_dtype(b200_shard_t* s, int dtype);
 /* `del self.shard` + empty_cache (utils/node_worker.py:139-147) */
 B200_API int b200_shard_destroy(b200_shard_t* s);
 

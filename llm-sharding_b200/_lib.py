@@ -70,6 +70,7 @@ PROTOTYPES = {
     "b200_shard_counters": (_I, [_P, C.POINTER(_U64)]),
     "b200_shard_reset_counters": (_I, [_P]),
     "b200_shard_set_graphs": (_I, [_P, _I]),
+    "b200_shard_set_io_dtype": (_I, [_P, _I]),
     "b200_rmsnorm": (_I, [_P, _P, C.c_float, _I, _I, _P, _P]),
     "b200_attn_decode": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P, _P]),
     "b200_attn_decode_static": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P]),

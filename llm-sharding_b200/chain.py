@@ -245,6 +245,8 @@ class ChainStage:
         self.w, self.rank, self.world, self.n_streams = worker, rank, world, n_streams
         self.sched = RingSchedule(rank, world, n_streams)
         self.eng, self.kv = worker.shard.engine, worker.past_key_value
+        if self.eng.io_dtype != torch.bfloat16:
+            raise ValueError("[ERROR] the ring's mailbox slots are laid out for bfloat16 hidden states; start the worker with dtype=torch.bfloat16")
         self.lib = self.eng.lib
         self.device = worker.device
         self.H = self.eng.hidden_size

@@ -75,6 +75,7 @@ struct b200_shard {
     InvFreq inv{};
     uint64_t n_launch = 0, n_bytes = 0, n_flops = 0, n_calls = 0;
     bool graphs = false;
+    int io_dtype = B200_DT_BF16;  // element type of hidden states crossing the ABI (the node's dtype, utils/node_worker.py:252)
     std::map<GraphKey, GraphEntry> graph_cache;
     uint64_t graph_clock = 0;
     std::vector<void*> allocs;
@@ -421,13 +422,13 @@ static int enqueue_forward(b200_shard_t* s, b200_kv_t* kv, const SlotList& sl, c
     const int M = B * S, H = c.hidden_size, I = c.intermediate_size;
     const int64_t head_stride = (int64_t)kv->dev.page_size * 128;
     if (tok_in != nullptr) {  // entry == head node: embed_tokens (utils/node_worker.py:215,302) straight into the workspace
-        launch_embed(s->embedding, tok_in, M, H, c.vocab_size, s->xn, st);
+        launch_embed(s->embedding, tok_in, M, H, c.vocab_size, s->xn, B200_DT_BF16, st);
         s->n_launch += 1;
         in = s->xn;
     }
     launch_kv_alloc(kv->dev, sl, B, S, s->tm.call_base, st);
     launch_prep(kv->dev, sl, B, S, causal, s->inv, c.n_kv_heads, s->tm, st);
-    launch_load_residual(reinterpret_cast<const __nv_bfloat16*>(in), s->x, (int64_t)M * H, st);
+    launch_load_residual(in, tok_in != nullptr ? B200_DT_BF16 : s->io_dtype, s->x, (int64_t)M * H, st);
     s->n_launch += 3;
     const bool gemv_path = M <= gemv_row_limit(s);
     const bool stream_path = !gemv_path && M <= kMaxStreamRows && stream_gemm_enabled() && H % 64 == 0 && I % 64 == 0 &&
@@ -463,7 +464,7 @@ static int enqueue_forward(b200_shard_t* s, b200_kv_t* kv, const SlotList& sl, c
         } else if (stream_path) {
             // 4..32 token rows (batched decode, short prompts): still bound by reading the weights once, now on the tensor cores
             // (gemm_stream_tc.cu); operands fp16, residual stream and q fp32, K/V rounded to bf16 once
-            launch_rmsnorm_bf16(s->x, L.norm1, c.rms_eps, M, H, s->xn, st, true);
+            launch_rmsnorm_bf16(s->x, L.norm1, c.rms_eps, M, H, s->xn, st, B200_DT_F16);
             StreamGemmParams g{};
             g.W = L.wqkv; g.X = s->xn; g.M = M; g.N = s->qkv_rows; g.K = H;
             g.q_out = s->q_f; g.k_pool = kp; g.v_pool = vp; g.kv_off = s->tm.kv_off; g.cos = s->tm.cos; g.sin = s->tm.sin;
@@ -480,7 +481,7 @@ static int enqueue_forward(b200_shard_t* s, b200_kv_t* kv, const SlotList& sl, c
             StreamGemmParams o{};
             o.W = L.wo; o.X = s->attn_b; o.M = M; o.N = H; o.K = s->nq; o.out = s->x;
             if (launch_gemm_stream(o, EPI_RESID, s->num_sms, st) != 0) return fail(B200_ECUDA, "[ERROR] %s", gemm_stream_last_error());
-            launch_rmsnorm_bf16(s->x, L.norm2, c.rms_eps, M, H, s->xn, st, true);
+            launch_rmsnorm_bf16(s->x, L.norm2, c.rms_eps, M, H, s->xn, st, B200_DT_F16);
             StreamGemmParams gu{};
             gu.W = L.wgu; gu.X = s->xn; gu.M = M; gu.N = 2 * I; gu.K = H; gu.act_h = reinterpret_cast<__half*>(s->act_b);
             if (launch_gemm_stream(gu, EPI_SWIGLU, s->num_sms, st) != 0) return fail(B200_ECUDA, "[ERROR] %s", gemm_stream_last_error());
@@ -491,7 +492,7 @@ static int enqueue_forward(b200_shard_t* s, b200_kv_t* kv, const SlotList& sl, c
         } else {
             // activations feeding the tensor cores are fp16 (10 mantissa bits) against exact bf16 weights; q reaches
             // attention as a (hi, lo) bf16 pair; K/V are rounded to bf16 exactly once, inside the QKV epilogue
-            launch_rmsnorm_bf16(s->x, L.norm1, c.rms_eps, M, H, s->xn, st, true);
+            launch_rmsnorm_bf16(s->x, L.norm1, c.rms_eps, M, H, s->xn, st, B200_DT_F16);
             GemmParams g{};
             g.A = s->xn; g.W = L.wqkv; g.M = M; g.N = s->qkv_rows; g.K = H; g.out = nullptr; g.epi = GEMM_QKV_ROPE; g.ab_f16 = 1;
             g.q_hi = s->qrot; g.q_lo = s->qrot_lo; g.k_pool = kp; g.v_pool = vp; g.kv_off = s->tm.kv_off;
@@ -512,7 +513,7 @@ static int enqueue_forward(b200_shard_t* s, b200_kv_t* kv, const SlotList& sl, c
             GemmParams o{};
             o.A = s->attn_b; o.W = L.wo; o.M = M; o.N = H; o.K = s->nq; o.out = s->x; o.epi = GEMM_RESID_F32; o.ab_f16 = 1;
             if (launch_gemm(o, st) != 0) return fail(B200_ECUDA, "[ERROR] %s", gemm_error());
-            launch_rmsnorm_bf16(s->x, L.norm2, c.rms_eps, M, H, s->xn, st, true);
+            launch_rmsnorm_bf16(s->x, L.norm2, c.rms_eps, M, H, s->xn, st, B200_DT_F16);
             GemmParams gu{};
             gu.A = s->xn; gu.W = L.wgu; gu.M = M; gu.N = 2 * I; gu.K = H; gu.out = s->act_b; gu.epi = GEMM_SWIGLU_BF16;
             gu.ab_f16 = 1; gu.out_f16 = 1;
@@ -524,8 +525,7 @@ static int enqueue_forward(b200_shard_t* s, b200_kv_t* kv, const SlotList& sl, c
         }
     }
     if (out != nullptr) {  // final RMSNorm when this is the tail shard (utils/shard_loader.py:76-77), else a plain cast
-        launch_rmsnorm_bf16(s->x, c.has_final_norm ? s->final_norm : nullptr, c.rms_eps, M, H,
-                            reinterpret_cast<__nv_bfloat16*>(out), st);
+        launch_rmsnorm_bf16(s->x, c.has_final_norm ? s->final_norm : nullptr, c.rms_eps, M, H, out, st, s->io_dtype);
         s->n_launch += 1;
     }
     if (with_tail && B > gemv_row_limit(s)) {  // batched tail goes through the GEMM; small batches fuse the norm into the GEMV
@@ -551,7 +551,7 @@ static int enqueue_tail(b200_shard_t* s, int B, int S, bool from_residual, int64
             launch_gemv(g, B, EPI_STORE, false, s->num_sms, st);
         }
     } else {
-        launch_rmsnorm_bf16(s->lastrow, nullptr, 0.f, B, c.hidden_size, s->lastrow_b, st, true);
+        launch_rmsnorm_bf16(s->lastrow, nullptr, 0.f, B, c.hidden_size, s->lastrow_b, st, B200_DT_F16);
         if (B <= kMaxStreamRows && stream_gemm_enabled() && c.hidden_size % 64 == 0) {
             StreamGemmParams g{};
             g.W = s->lm_head; g.X = s->lastrow_b; g.M = B; g.N = c.vocab_size; g.K = c.hidden_size; g.out = s->logits;
@@ -747,7 +747,7 @@ extern "C" B200_API int b200_shard_lm_head_argmax(b200_shard_t* s, const void* h
     if (B < 1 || B > s->cfg.max_batch || S < 1) return fail(B200_EINVAL, "[ERROR] bad batch / seq_len");
     CU_TRY(cudaSetDevice(s->device));
     cudaStream_t st = (cudaStream_t)stream;
-    launch_lastrow_bf16_to_f32(reinterpret_cast<const __nv_bfloat16*>(hidden), B, S, s->cfg.hidden_size, s->lastrow, st);
+    launch_lastrow_to_f32(hidden, s->io_dtype, B, S, s->cfg.hidden_size, s->lastrow, st);
     s->n_launch += 1;
     TRY(enqueue_tail(s, B, S, false, tok, margin, st));
     CU_TRY(cudaGetLastError());
@@ -759,7 +759,7 @@ extern "C" B200_API int b200_shard_embed(b200_shard_t* s, const int64_t* ids, in
     if (!s->cfg.has_embedding || s->embedding == nullptr)
         return fail(B200_ESTATE, "[ERROR] this node does not have embedding layer while receiving user request.");
     CU_TRY(cudaSetDevice(s->device));
-    launch_embed(s->embedding, ids, n, s->cfg.hidden_size, s->cfg.vocab_size, reinterpret_cast<__nv_bfloat16*>(out), (cudaStream_t)stream);
+    launch_embed(s->embedding, ids, n, s->cfg.hidden_size, s->cfg.vocab_size, out, s->io_dtype, (cudaStream_t)stream);
     CU_TRY(cudaGetLastError());
     s->n_launch += 1;
     return 0;
@@ -780,6 +780,13 @@ extern "C" B200_API int b200_shard_set_rope_inv_freq(b200_shard_t* s, const floa
     if (n != 64) return fail(B200_EINVAL, "[ERROR] inv_freq must have head_dim/2 = 64 entries (got %d)", n);
     for (int j = 0; j < 64; ++j) s->inv.v[j] = h_inv_freq[j];
     drop_graphs(s, 0);  // captured graphs hold the old table by value
+    return 0;
+}
+extern "C" B200_API int b200_shard_set_io_dtype(b200_shard_t* s, int dtype) {
+    if (s == nullptr) return fail(B200_EINVAL, "[ERROR] null shard");
+    if (dtype != B200_DT_BF16 && dtype != B200_DT_F32 && dtype != B200_DT_F16) return fail(B200_EINVAL, "[ERROR] unsupported message dtype %d", dtype);
+    if (dtype != s->io_dtype) drop_graphs(s, 0);  // captured graphs have the conversion kernels of the old dtype baked in
+    s->io_dtype = dtype;
     return 0;
 }
 extern "C" B200_API int b200_shard_set_graphs(b200_shard_t* s, int enabled) {

@@ -63,16 +63,17 @@ void launch_kv_init(const KvDev& kv, cudaStream_t st);
 void launch_prep(const KvDev& kv, const SlotList& slots, int B, int S, int causal, const InvFreq& inv, int n_kv,
                  const TokMeta& tm, cudaStream_t st);
 
-void launch_load_residual(const __nv_bfloat16* in, float* x, int64_t n, cudaStream_t st);
-// x fp32 [rows,n] -> bf16 (or fp16 when f16_out); norm_w == nullptr: plain convert
+// `in` in any message dtype (B200_DT_* code) -> fp32 residual stream
+void launch_load_residual(const void* in, int dtype, float* x, int64_t n, cudaStream_t st);
+// x fp32 [rows,n] -> out_dtype (B200_DT_* code: 0 bf16, 1 fp32, 2 fp16 saturating); norm_w == nullptr: plain convert
 void launch_rmsnorm_bf16(const float* x, const __nv_bfloat16* norm_w, float eps, int rows, int n,
-                         void* out, cudaStream_t st, bool f16_out = false);
+                         void* out, cudaStream_t st, int out_dtype = 0);
 // last-row gather + optional norm, fp32 out [B,n] (input rows b*S+S-1)
 void launch_lastrow_norm_f32(const float* x, const __nv_bfloat16* norm_w, float eps, int B, int S, int n,
                              float* out, cudaStream_t st);
-void launch_lastrow_bf16_to_f32(const __nv_bfloat16* h, int B, int S, int n, float* out, cudaStream_t st);
+void launch_lastrow_to_f32(const void* h, int dtype, int B, int S, int n, float* out, cudaStream_t st);
 void launch_argmax(const float* logits, int B, int V, int64_t* tok, float* margin, cudaStream_t st);
-void launch_embed(const __nv_bfloat16* table, const int64_t* ids, int n, int H, int V, __nv_bfloat16* out,
+void launch_embed(const __nv_bfloat16* table, const int64_t* ids, int n, int H, int V, void* out, int out_dtype,
                   cudaStream_t st);
 // src (.pth storage dtype) -> bf16, or -> fp16 (saturating) when f16_out
 void launch_convert_to_bf16(const void* src, int dtype, void* dst, int64_t n, cudaStream_t st, bool f16_out = false);

@@ -103,6 +103,11 @@ void launch_prep(const KvDev& kv, const SlotList& slots, int B, int S, int causa
 }
 
 // =========================================================================== small bandwidth kernels
+__device__ __forceinline__ float load_as_float(const void* src, int dtype, int64_t i) {
+    if (dtype == 0) return __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(src)[i]);
+    if (dtype == 1) return reinterpret_cast<const float*>(src)[i];
+    return __half2float(reinterpret_cast<const __half*>(src)[i]);
+}
 __global__ void load_residual_kernel(const __nv_bfloat16* __restrict__ in, float* __restrict__ x, int64_t n8) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
@@ -113,7 +118,21 @@ __global__ void load_residual_kernel(const __nv_bfloat16* __restrict__ in, float
         o[1] = make_float4(bf_lo(v.z), bf_hi(v.z), bf_lo(v.w), bf_hi(v.w));
     }
 }
-void launch_load_residual(const __nv_bfloat16* in, float* x, int64_t n, cudaStream_t st) {
+// same for fp16 / fp32 messages (the reference runs in whatever dtype the node was started with, start_node.py:16-17)
+__global__ void load_residual_any_kernel(const void* __restrict__ in, int dtype, float* __restrict__ x, int64_t n) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; i < n; i += stride)
+        x[i] = dtype == 1 ? reinterpret_cast<const float*>(in)[i] : __half2float(reinterpret_cast<const __half*>(in)[i]);
+}
+void launch_load_residual(const void* in_any, int dtype, float* x, int64_t n, cudaStream_t st) {
+    if (dtype != 0) {
+        int grid = (int)((n + 255) / 256);
+        if (grid > 148 * 16) grid = 148 * 16;
+        load_residual_any_kernel<<<grid < 1 ? 1 : grid, 256, 0, st>>>(in_any, dtype, x, n);
+        return;
+    }
+    const __nv_bfloat16* in = reinterpret_cast<const __nv_bfloat16*>(in_any);
     const int64_t n8 = n / 8;
     int grid = (int)((n8 + 255) / 256);
     if (grid > 148 * 8) grid = 148 * 8;
@@ -129,7 +148,7 @@ __device__ __forceinline__ uint32_t pack_f16_sat(float a, float b) {
     __half2 t = __floats2half2_rn(a, b);
     return *reinterpret_cast<uint32_t*>(&t);
 }
-template <bool F16OUT>
+template <int OUT>  // element type of `out`: 0 bf16, 1 fp32, 2 fp16 (saturating) — the B200_DT_* codes
 __global__ void __launch_bounds__(256) rmsnorm_bf16_kernel(const float* __restrict__ x,
                                                            const __nv_bfloat16* __restrict__ w, float eps, int n,
                                                            __nv_bfloat16* __restrict__ out) {
@@ -139,7 +158,7 @@ __global__ void __launch_bounds__(256) rmsnorm_bf16_kernel(const float* __restri
     asm volatile("griddepcontrol.wait;" ::: "memory");
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     const float* xr = x + (size_t)blockIdx.x * n;
-    __nv_bfloat16* orow = out + (size_t)blockIdx.x * n;
+    __nv_bfloat16* orow = out + (size_t)blockIdx.x * n * (OUT == 1 ? 2 : 1);
     const int n8 = n / 8;
     float rstd = 1.f;
     if (w != nullptr) {
@@ -162,7 +181,12 @@ __global__ void __launch_bounds__(256) rmsnorm_bf16_kernel(const float* __restri
             for (int e = 0; e < 8; ++e) v[e] = v[e] * rstd * wf[e];
         }
         uint4 o;
-        if (F16OUT) {
+        if (OUT == 1) {
+            float4* of = reinterpret_cast<float4*>(orow) + 2 * i;
+            of[0] = make_float4(v[0], v[1], v[2], v[3]);
+            of[1] = make_float4(v[4], v[5], v[6], v[7]);
+            continue;
+        } else if (OUT == 2) {
             o.x = pack_f16_sat(v[0], v[1]); o.y = pack_f16_sat(v[2], v[3]);
             o.z = pack_f16_sat(v[4], v[5]); o.w = pack_f16_sat(v[6], v[7]);
         } else {
@@ -173,7 +197,7 @@ __global__ void __launch_bounds__(256) rmsnorm_bf16_kernel(const float* __restri
     }
 }
 void launch_rmsnorm_bf16(const float* x, const __nv_bfloat16* norm_w, float eps, int rows, int n,
-                         void* out, cudaStream_t st, bool f16_out) {
+                         void* out, cudaStream_t st, int out_dtype) {
     if (rows <= 0) return;
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(rows);
@@ -186,8 +210,9 @@ void launch_rmsnorm_bf16(const float* x, const __nv_bfloat16* norm_w, float eps,
     const char* e = getenv("B200SHARD_PDL");
     cfg.numAttrs = (e != nullptr && e[0] == '0') ? 0 : 1;
     __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(out);
-    if (f16_out) cudaLaunchKernelEx(&cfg, rmsnorm_bf16_kernel<true>, x, norm_w, eps, n, o);
-    else cudaLaunchKernelEx(&cfg, rmsnorm_bf16_kernel<false>, x, norm_w, eps, n, o);
+    if (out_dtype == 2) cudaLaunchKernelEx(&cfg, rmsnorm_bf16_kernel<2>, x, norm_w, eps, n, o);
+    else if (out_dtype == 1) cudaLaunchKernelEx(&cfg, rmsnorm_bf16_kernel<1>, x, norm_w, eps, n, o);
+    else cudaLaunchKernelEx(&cfg, rmsnorm_bf16_kernel<0>, x, norm_w, eps, n, o);
 }
 
 __global__ void __launch_bounds__(256) lastrow_norm_f32_kernel(const float* __restrict__ x,
@@ -210,12 +235,12 @@ void launch_lastrow_norm_f32(const float* x, const __nv_bfloat16* norm_w, float 
     lastrow_norm_f32_kernel<<<B, 256, 0, st>>>(x, norm_w, eps, S, n, out);
 }
 
-__global__ void lastrow_bf16_to_f32_kernel(const __nv_bfloat16* __restrict__ h, int S, int n, float* __restrict__ out) {
-    const __nv_bfloat16* r = h + ((size_t)blockIdx.x * S + (S - 1)) * n;
-    for (int i = threadIdx.x; i < n; i += blockDim.x) out[(size_t)blockIdx.x * n + i] = __bfloat162float(r[i]);
+__global__ void lastrow_to_f32_kernel(const void* __restrict__ h, int dtype, int S, int n, float* __restrict__ out) {
+    const size_t r0 = ((size_t)blockIdx.x * S + (S - 1)) * n;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) out[(size_t)blockIdx.x * n + i] = load_as_float(h, dtype, (int64_t)(r0 + i));
 }
-void launch_lastrow_bf16_to_f32(const __nv_bfloat16* h, int B, int S, int n, float* out, cudaStream_t st) {
-    lastrow_bf16_to_f32_kernel<<<B, 256, 0, st>>>(h, S, n, out);
+void launch_lastrow_to_f32(const void* h, int dtype, int B, int S, int n, float* out, cudaStream_t st) {
+    lastrow_to_f32_kernel<<<B, 256, 0, st>>>(h, dtype, S, n, out);
 }
 
 // torch.argmax(logits[:, -1, :], dim=-1) (utils/node_worker.py:264): first index of the maximum.
@@ -298,6 +323,18 @@ void launch_argmax(const float* logits, int B, int V, int64_t* tok, float* margi
 }
 
 // embed_tokens(ids) (utils/node_worker.py:215,302): row gather, 128-bit copies.
+__global__ void embed_any_kernel(const __nv_bfloat16* __restrict__ table, const int64_t* __restrict__ ids, int H, int V,
+                                 void* __restrict__ out, int dtype) {
+    int64_t id = ids[blockIdx.x];
+    if (id < 0) id = 0;
+    if (id >= V) id = V - 1;
+    const __nv_bfloat16* src = table + (size_t)id * H;
+    for (int i = threadIdx.x; i < H; i += blockDim.x) {
+        const float v = __bfloat162float(src[i]);
+        if (dtype == 1) reinterpret_cast<float*>(out)[(size_t)blockIdx.x * H + i] = v;
+        else reinterpret_cast<__half*>(out)[(size_t)blockIdx.x * H + i] = __float2half_rn(fminf(fmaxf(v, -65504.f), 65504.f));
+    }
+}
 __global__ void embed_kernel(const __nv_bfloat16* __restrict__ table, const int64_t* __restrict__ ids, int H, int V,
                              __nv_bfloat16* __restrict__ out) {
     int64_t id = ids[blockIdx.x];
@@ -307,17 +344,14 @@ __global__ void embed_kernel(const __nv_bfloat16* __restrict__ table, const int6
     uint4* dst = reinterpret_cast<uint4*>(out + (size_t)blockIdx.x * H);
     for (int i = threadIdx.x; i < H / 8; i += blockDim.x) dst[i] = src[i];
 }
-void launch_embed(const __nv_bfloat16* table, const int64_t* ids, int n, int H, int V, __nv_bfloat16* out,
+void launch_embed(const __nv_bfloat16* table, const int64_t* ids, int n, int H, int V, void* out, int out_dtype,
                   cudaStream_t st) {
-    if (n > 0) embed_kernel<<<n, 128, 0, st>>>(table, ids, H, V, out);
+    if (n <= 0) return;
+    if (out_dtype == 0) embed_kernel<<<n, 128, 0, st>>>(table, ids, H, V, reinterpret_cast<__nv_bfloat16*>(out));
+    else embed_any_kernel<<<n, 128, 0, st>>>(table, ids, H, V, out, out_dtype);
 }
 
 // ---- weight ingest: .pth storage dtype -> bf16, and the paired gate/up layout
-__device__ __forceinline__ float load_as_float(const void* src, int dtype, int64_t i) {
-    if (dtype == 0) return __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(src)[i]);
-    if (dtype == 1) return reinterpret_cast<const float*>(src)[i];
-    return __half2float(reinterpret_cast<const __half*>(src)[i]);
-}
 __device__ __forceinline__ __half to_half_sat(float v) { return __float2half_rn(fminf(fmaxf(v, -65504.f), 65504.f)); }
 __global__ void convert_kernel(const void* src, int dtype, void* dst, int64_t n, bool f16_out) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;

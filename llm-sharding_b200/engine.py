@@ -60,7 +60,7 @@ def read_model_config(shards_path: str) -> dict:
 
 class Shard:
     def __init__(self, model_cfg: dict, n_layers: int, device: torch.device, *, has_final_norm=False, has_lm_head=False,
-                 has_embedding=False, max_tokens=4096, max_batch=1):
+                 has_embedding=False, max_tokens=4096, max_batch=1, io_dtype: torch.dtype = torch.bfloat16):
         _lib.require_cuda()
         self.lib = _lib.load()
         self.device = torch.device(device)
@@ -84,6 +84,10 @@ class Shard:
         # the table torch would compute (bit-identical to the reference's LlamaRotaryEmbedding.inv_freq), scaled or not
         inv = rope_inv_freq(model_cfg["head_dim"], model_cfg["rope_theta"], model_cfg.get("rope_scaling"))
         _lib.check(self.lib.b200_shard_set_rope_inv_freq(self.handle, inv.numpy().ctypes.data_as(C.POINTER(C.c_float)), inv.numel()))
+        if io_dtype not in _lib.TORCH_TO_DT:
+            raise ValueError(f"[ERROR] dtype={io_dtype} is not built (bfloat16, float16 and float32 messages are)")
+        self.io_dtype = io_dtype
+        _lib.check(self.lib.b200_shard_set_io_dtype(self.handle, _lib.TORCH_TO_DT[io_dtype]))
         self.graphs = False
         self._step_bufs: dict = {}   # B -> persistent (hidden_in, hidden_out, tok, margin) for single-token calls
 
@@ -128,7 +132,7 @@ class Shard:
 
     def forward(self, hidden: torch.Tensor, kv: "PagedKVCache", slots=None, causal: bool = False,
                 out: torch.Tensor | None = None) -> torch.Tensor:
-        """LlamaShardPart.forward: bf16 [B,S,H] -> bf16 [B,S,H]."""
+        """LlamaShardPart.forward: [B,S,H] -> [B,S,H] in the shard's message dtype (bf16 unless chosen otherwise)."""
         hidden = self._check_hidden(hidden)
         B, S, _ = hidden.shape
         if S == 1 and self.graphs and out is None:
@@ -148,8 +152,8 @@ class Shard:
     def _bufs(self, B: int):
         if B not in self._step_bufs:
             H = self.hidden_size
-            self._step_bufs[B] = (torch.empty(B, 1, H, dtype=torch.bfloat16, device=self.device),
-                                  torch.empty(B, 1, H, dtype=torch.bfloat16, device=self.device),
+            self._step_bufs[B] = (torch.empty(B, 1, H, dtype=self.io_dtype, device=self.device),
+                                  torch.empty(B, 1, H, dtype=self.io_dtype, device=self.device),
                                   torch.empty(B, dtype=torch.int64, device=self.device),
                                   torch.empty(B, dtype=torch.float32, device=self.device))
         return self._step_bufs[B]
@@ -201,16 +205,16 @@ class Shard:
         return tok, margin
 
     def embed(self, ids: torch.Tensor) -> torch.Tensor:
-        """embed_tokens(ids): int64 [...] -> bf16 [..., H]."""
+        """embed_tokens(ids): int64 [...] -> [..., H] in the message dtype."""
         ids = ids.to(device=self.device, dtype=torch.long).contiguous()
-        out = torch.empty(*ids.shape, self.hidden_size, dtype=torch.bfloat16, device=self.device)
+        out = torch.empty(*ids.shape, self.hidden_size, dtype=self.io_dtype, device=self.device)
         _lib.check(self.lib.b200_shard_embed(self.handle, ids.data_ptr(), ids.numel(), out.data_ptr(), self._stream()))
         return out
 
     def _check_hidden(self, hidden: torch.Tensor) -> torch.Tensor:
         if hidden.ndim != 3 or hidden.shape[-1] != self.hidden_size:
             raise ValueError(f"[ERROR] hidden_states must be [B, S, {self.hidden_size}], got {tuple(hidden.shape)}")
-        return hidden.to(device=self.device, dtype=torch.bfloat16).contiguous()
+        return hidden.to(device=self.device, dtype=self.io_dtype).contiguous()
 
     def counters(self) -> dict:
         arr = (C.c_uint64 * 4)()

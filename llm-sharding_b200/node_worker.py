@@ -97,7 +97,7 @@ class NodeWorker:
     CLEAR_KV_CACHE_ORIGIN_KEY = "origin_node"
 
     def __init__(self, src_addr: str, dst_addr: str, can_receive_user_request: bool, shards_path: str,
-                 device="cuda:0", dtype=torch.bfloat16, *, communicator=None, transport: str = "zmq", max_tokens: int = 4096,
+                 device="cuda:0", dtype=torch.bfloat16, *, communicator=None, transport: str | None = None, max_tokens: int = 4096,
                  max_batch: int = 1, max_slots: int | None = None, max_seq_len: int | None = None,
                  causal: bool = False, use_graphs: bool = True, state_provider=None):
         """Positional parameters as in the reference (utils/node_worker.py:75-76).  ``transport="p2p"``
@@ -107,6 +107,8 @@ class NodeWorker:
         from .engine import read_model_config
 
         if communicator is None:
+            # B200SHARD_TRANSPORT lets the reference's unchanged launch scripts (start_node.py, profiling.py) pick the NVLink path
+            transport = transport or os.environ.get("B200SHARD_TRANSPORT", "zmq")
             if transport == "p2p":
                 from .p2p_communicator import P2PCommunicator
                 communicator = P2PCommunicator(src_addr, dst_addr, device=device)

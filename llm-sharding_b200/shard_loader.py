@@ -16,7 +16,9 @@ class LlamaShardPart:
                  add_final_norm=False, final_norm_weight=None, *,
                  lm_head_weight: str | None = None, embedding_weight: str | None = None,
                  max_tokens: int = 4096, max_batch: int = 1, state_provider=None):
-        """Same positional parameters as the reference.  Keyword-only extras: ``lm_head_weight`` /
+        """Same positional parameters as the reference.  ``dtype`` is the dtype of the hidden states that enter and leave
+        (the reference's module dtype: messages are cast to it, utils/node_worker.py:252); the arithmetic inside is the
+        same for all three (fp32 residual stream, fp16 tensor-core operands, bf16 K/V).  Keyword-only extras: ``lm_head_weight`` /
         ``embedding_weight`` (file names) put the tail's ``lm_head`` and the entry node's embedding
         behind the same C handle; ``max_tokens`` / ``max_batch`` size the workspace; ``state_provider``
         (``file name -> state_dict``) replaces ``torch.load`` of the shard files (synthetic weights)."""
@@ -26,9 +28,8 @@ class LlamaShardPart:
         self.end = end
         self.device = torch.device(device)
         self.dtype = dtype
-        if dtype != torch.bfloat16:
-            raise ValueError("[ERROR] the B200 shard path computes in bfloat16 (fp32 accumulate); "
-                             f"dtype={dtype} is not built")
+        if dtype not in (torch.bfloat16, torch.float16, torch.float32):
+            raise ValueError(f"[ERROR] dtype={dtype} is not built (bfloat16, float16 and float32 are)")
         if len(self.shard_weights) != self.end - self.start:
             raise ValueError("[ERROR] String list: shard_weights length must be equal to (end - start)")
         if add_final_norm and final_norm_weight is None:
@@ -36,7 +37,7 @@ class LlamaShardPart:
         self.config = read_model_config(shards_path)
         self.engine = Shard(self.config, end - start, self.device, has_final_norm=bool(add_final_norm),
                             has_lm_head=lm_head_weight is not None, has_embedding=embedding_weight is not None,
-                            max_tokens=max_tokens, max_batch=max_batch)
+                            max_tokens=max_tokens, max_batch=max_batch, io_dtype=dtype)
         load = state_provider or (lambda fname: torch.load(os.path.join(shards_path, fname), map_location="cpu"))
         for rel_idx, fname in enumerate(self.shard_weights):  # shard-relative index, utils/shard_loader.py:36-45
             state = load(fname)
@@ -57,7 +58,7 @@ class LlamaShardPart:
         return self.engine.new_kv(max_slots, page_size, None, max_seq_len or self.config["max_position_embeddings"])
 
     def forward(self, hidden_states, attention_mask=None, past_key_value=None, rotary_emb=None, *, slots=None):
-        """hidden_states [B,S,H] -> [B,S,H] (bf16).
+        """hidden_states [B,S,H] -> [B,S,H] (in ``dtype``).
 
         ``past_key_value`` must be a ``PagedKVCache`` of this shard (the reference passes its
         ``DynamicCache``).  ``rotary_emb`` is accepted for signature parity and ignored: cos/sin

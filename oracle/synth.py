@@ -69,6 +69,9 @@ PRESETS = {
     "llama2_7b": SynthConfig("llama2_7b", 32000, 4096, 11008, 32, 32, 32),
     # eight small layers: one per GPU of an 8-way ring (the parity check bench_chain.py runs before its timed region)
     "ring8": SynthConfig("ring8", 1000, 256, 640, 8, 2, 2, max_position_embeddings=512),
+    # 28 small layers: the layer count the reference's go_through_every_shards hard-codes (0-7 / 7-14 / 14-21 / 21-28,
+    # utils/node_profiler.py:1207-1210, i.e. Llama-3.2-3B's)
+    "l28": SynthConfig("l28", 1000, 256, 640, 28, 2, 2, max_position_embeddings=512),
     # Llama-2-7B LAYER dimensions (what bench.py and BASELINE configs[3] run) with three layers and a small vocabulary, so
     # that the CPU oracle finishes 512..4096-token prompts in seconds: reaches the CTA-pair GEMM epilogues and the
     # steady state of the prefill-attention pipeline (>= 3 key tiles) that the small presets never touch

@@ -21,7 +21,7 @@ def shard_dir(tmp_root: str, preset: str, seed: int) -> str:
 
 
 def build_chain(tmp_root, preset, seed, splits, max_batch=1, max_tokens=512, causal=False, use_graphs=True,
-                max_seq_len=None, device="cuda:0"):
+                max_seq_len=None, device="cuda:0", dtype=torch.bfloat16):
     from llm_sharding_b200.chain import LoopbackCommunicator
     from llm_sharding_b200.node_worker import NodeWorker
     cfg = synth.PRESETS[preset]
@@ -36,7 +36,7 @@ def build_chain(tmp_root, preset, seed, splits, max_batch=1, max_tokens=512, cau
     workers = []
     for i, (s, e) in enumerate(splits):
         src, dst = f"tcp://*:{ports[i]}", f"tcp://127.0.0.1:{ports[(i + 1) % n]}"
-        w = NodeWorker(src, dst, i == 0, d, device=device, dtype=torch.bfloat16,
+        w = NodeWorker(src, dst, i == 0, d, device=device, dtype=dtype,
                        communicator=LoopbackCommunicator(src, dst), max_tokens=max_tokens, max_batch=max_batch,
                        causal=causal, use_graphs=use_graphs, max_seq_len=max_seq_len, state_provider=provider)
         w.load_shards(s, e)

@@ -96,6 +96,29 @@ def test_chain_matches_oracle_on_fresh_inputs(preset, seed, splits, B, S, n_new,
         close_chain(workers)
 
 
+@pytest.mark.parametrize("dtype", [torch.float16, torch.float32])
+def test_chain_in_the_other_message_dtypes(dtype, tmp_root):
+    """The reference launches its nodes in float16 (start_node.py:16-17) and casts every incoming message to the node's
+    dtype (utils/node_worker.py:252): hidden states may cross the boundary as fp16 or fp32 as well as bf16.  Same oracle,
+    same tolerance; the messages must come out in the dtype that was asked for."""
+    from llm_sharding_b200.chain import generate
+    preset, seed, splits, B, S, n_new = "small", 115, [(0, 2), (2, 6)], 2, 70, 3
+    cfg = synth.PRESETS[preset]
+    ids = synth.prompt_ids(cfg, seed, B, S)
+    o_tokens, o_states, o_margins = _oracle(preset, seed, splits, ids, n_new)
+    workers = build_chain(tmp_root, preset, seed, splits, max_batch=B, max_tokens=B * S, dtype=dtype)
+    try:
+        msg = workers[0].pass_through_shard(workers[0].receive_user_request(input_ids=ids))
+        assert msg["hidden_states"].dtype == dtype
+        for w in workers:
+            w.clear_KV_cache()
+        tokens, states = generate(workers, ids, n_new, record_states=True, teacher_tokens=o_tokens)
+        worst, mism = _compare(tokens, states, o_tokens, o_states, o_margins)
+        print(f"dtype {dtype}: worst hidden rel-L2 {worst:.2e}, near-tie flips {mism}")
+    finally:
+        close_chain(workers)
+
+
 def test_kv_reset_reuses_pages_and_reproduces(tmp_root):
     z, meta = load_golden("tiny_b1")
     workers = build_chain(tmp_root, meta["preset"], meta["seed"], [tuple(s) for s in meta["splits"]], max_tokens=64)
