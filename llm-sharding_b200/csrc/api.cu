@@ -70,6 +70,8 @@ struct b200_shard {
     __nv_bfloat16 *xn = nullptr, *qrot = nullptr, *qrot_lo = nullptr, *attn_b = nullptr, *act_b = nullptr;  // 16-bit staging (xn / attn_b / act_b hold fp16)
     float *q_f = nullptr, *attn_f = nullptr, *act_f = nullptr;  // GEMV path (<= 4 rows), fp32
     float *lastrow = nullptr, *logits = nullptr, *attn_part = nullptr;
+    float* sk_ws = nullptr;             // stream-K GEMM: partial-sum slots, one per SM
+    unsigned int* sk_flags = nullptr;   // and their flags (zero between launches)
     __nv_bfloat16* lastrow_b = nullptr;
     TokMeta tm{};
     InvFreq inv{};
@@ -161,6 +163,8 @@ extern "C" B200_API int b200_shard_create(const b200_shard_config_t* c, int devi
     // partials for rows x splits <= 8 x 16 per head, followed by one arrival ticket per (row, head) for up to 32 rows
     const size_t part_floats = (size_t)kMaxGemvRows * c->n_heads * kMaxSplits * 130 + (size_t)kMaxStreamRows * c->n_heads;
     r |= dev_alloc(A, &s->attn_part, part_floats);
+    r |= dev_alloc(A, &s->sk_ws, gemm_streamk_ws_floats(s->num_sms));
+    r |= dev_alloc(A, &s->sk_flags, (size_t)s->num_sms + 8);
     r |= dev_alloc(A, &s->lastrow, (size_t)c->max_batch * H);
     r |= dev_alloc(A, &s->lastrow_b, (size_t)c->max_batch * H);
     r |= dev_alloc(A, &s->logits, (size_t)c->max_batch * V);
@@ -173,6 +177,7 @@ extern "C" B200_API int b200_shard_create(const b200_shard_config_t* c, int devi
     if (r != 0) { b200_shard_destroy(s); return B200_ENOMEM; }
     // arrival tickets of decode attention start at zero (the kernel re-zeroes them itself afterwards)
     CU_TRY(cudaMemset(s->attn_part, 0, part_floats * sizeof(float)));
+    CU_TRY(cudaMemset(s->sk_flags, 0, ((size_t)s->num_sms + 8) * sizeof(unsigned int)));
     *out = s;
     return 0;
 }
@@ -468,7 +473,7 @@ static int enqueue_forward(b200_shard_t* s, b200_kv_t* kv, const SlotList& sl, c
             StreamGemmParams g{};
             g.W = L.wqkv; g.X = s->xn; g.M = M; g.N = s->qkv_rows; g.K = H;
             g.q_out = s->q_f; g.k_pool = kp; g.v_pool = vp; g.kv_off = s->tm.kv_off; g.cos = s->tm.cos; g.sin = s->tm.sin;
-            g.n_heads = c.n_heads; g.n_kv = c.n_kv_heads; g.head_stride = head_stride;
+            g.n_heads = c.n_heads; g.n_kv = c.n_kv_heads; g.head_stride = head_stride; g.ws = s->sk_ws; g.ws_flags = s->sk_flags;
             if (launch_gemm_stream(g, EPI_QKV, s->num_sms, st) != 0) return fail(B200_ECUDA, "[ERROR] %s", gemm_stream_last_error());
             AttnDecodeParams a{};
             a.q = s->q_f; a.k_pool = kp; a.v_pool = vp; a.block_table = kv->dev.block_table; a.t_end = s->tm.t_end; a.call_base = s->tm.call_base;
@@ -479,14 +484,14 @@ static int enqueue_forward(b200_shard_t* s, b200_kv_t* kv, const SlotList& sl, c
             a.tickets = reinterpret_cast<unsigned int*>(s->attn_part + (size_t)kMaxGemvRows * c.n_heads * kMaxSplits * 130);
             launch_attn_decode(a, M, st);
             StreamGemmParams o{};
-            o.W = L.wo; o.X = s->attn_b; o.M = M; o.N = H; o.K = s->nq; o.out = s->x;
+            o.W = L.wo; o.X = s->attn_b; o.M = M; o.N = H; o.K = s->nq; o.out = s->x; o.ws = s->sk_ws; o.ws_flags = s->sk_flags;
             if (launch_gemm_stream(o, EPI_RESID, s->num_sms, st) != 0) return fail(B200_ECUDA, "[ERROR] %s", gemm_stream_last_error());
             launch_rmsnorm_bf16(s->x, L.norm2, c.rms_eps, M, H, s->xn, st, B200_DT_F16);
             StreamGemmParams gu{};
-            gu.W = L.wgu; gu.X = s->xn; gu.M = M; gu.N = 2 * I; gu.K = H; gu.act_h = reinterpret_cast<__half*>(s->act_b);
+            gu.W = L.wgu; gu.X = s->xn; gu.M = M; gu.N = 2 * I; gu.K = H; gu.act_h = reinterpret_cast<__half*>(s->act_b); gu.ws = s->sk_ws; gu.ws_flags = s->sk_flags;
             if (launch_gemm_stream(gu, EPI_SWIGLU, s->num_sms, st) != 0) return fail(B200_ECUDA, "[ERROR] %s", gemm_stream_last_error());
             StreamGemmParams d{};
-            d.W = L.wdown; d.X = s->act_b; d.M = M; d.N = H; d.K = I; d.out = s->x;
+            d.W = L.wdown; d.X = s->act_b; d.M = M; d.N = H; d.K = I; d.out = s->x; d.ws = s->sk_ws; d.ws_flags = s->sk_flags;
             if (launch_gemm_stream(d, EPI_RESID, s->num_sms, st) != 0) return fail(B200_ECUDA, "[ERROR] %s", gemm_stream_last_error());
             s->n_launch += 7;
         } else {
@@ -554,7 +559,7 @@ static int enqueue_tail(b200_shard_t* s, int B, int S, bool from_residual, int64
         launch_rmsnorm_bf16(s->lastrow, nullptr, 0.f, B, c.hidden_size, s->lastrow_b, st, B200_DT_F16);
         if (B <= kMaxStreamRows && stream_gemm_enabled() && c.hidden_size % 64 == 0) {
             StreamGemmParams g{};
-            g.W = s->lm_head; g.X = s->lastrow_b; g.M = B; g.N = c.vocab_size; g.K = c.hidden_size; g.out = s->logits;
+            g.W = s->lm_head; g.X = s->lastrow_b; g.M = B; g.N = c.vocab_size; g.K = c.hidden_size; g.out = s->logits; g.ws = s->sk_ws; g.ws_flags = s->sk_flags;
             if (launch_gemm_stream(g, EPI_STORE, s->num_sms, st) != 0) return fail(B200_ECUDA, "[ERROR] %s", gemm_stream_last_error());
         } else {
             GemmParams g{};

@@ -261,7 +261,21 @@ static int launch_one(const CUtensorMap& mw, const CUtensorMap& mx, const Stream
     return 0;
 }
 
+static bool streamk_enabled() {  // B200SHARD_STREAMK=1: the persistent stream-K kernel of gemm_streamk_tc.cu (A/B against this file's)
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("B200SHARD_STREAMK");
+        v = (e != nullptr && e[0] == '1') ? 1 : 0;
+    }
+    return v == 1;
+}
+
 int launch_gemm_stream(const StreamGemmParams& p_in, int epi, int num_sms, cudaStream_t st) {
+    if (streamk_enabled() && p_in.split == 0) {
+        const int r = launch_gemm_streamk(p_in, epi, num_sms, st);
+        if (r != 0) snprintf(g_stream_err, sizeof(g_stream_err), "%s", gemm_streamk_last_error());
+        return r;
+    }
     StreamGemmParams p = p_in;
     if (p.M < 1 || p.M > kMaxStreamRows || p.K % 8 != 0 || p.K < kSwK || p.N < 1) {
         snprintf(g_stream_err, sizeof(g_stream_err), "gemm_stream: need 1 <= M <= %d, K %% 8 == 0, K >= 64 (M=%d N=%d K=%d)", kMaxStreamRows,

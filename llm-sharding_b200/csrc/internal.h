@@ -136,7 +136,13 @@ struct StreamGemmParams {
     const float* sin = nullptr;
     int n_heads = 0, n_kv = 0;
     int64_t head_stride = 0;
+    // stream-K kernel (gemm_streamk_tc.cu): partial-sum slots [grid][MP][128] floats and one flag per CTA (zero between launches)
+    float* ws = nullptr;
+    unsigned int* ws_flags = nullptr;
 };
+int launch_gemm_streamk(const StreamGemmParams& p, int epi, int num_sms, cudaStream_t st);
+const char* gemm_streamk_last_error();
+size_t gemm_streamk_ws_floats(int num_sms);
 int launch_gemm_stream(const StreamGemmParams& p, int epi, int num_sms, cudaStream_t st);
 int gemm_stream_split(int N, int K, int num_sms);
 const char* gemm_stream_last_error();
