@@ -56,6 +56,7 @@ struct GraphKey {
 struct GraphEntry {
     cudaGraphExec_t exec = nullptr;
     uint64_t last_use = 0;
+    uint64_t launches = 0;   // kernels inside (counted while capturing)
 };
 constexpr size_t kMaxCachedGraphs = 64;  // least-recently-used graphs beyond this are destroyed (callers that pass fresh pointers every step)
 
@@ -164,7 +165,7 @@ extern "C" B200_API int b200_shard_create(const b200_shard_config_t* c, int devi
     const size_t part_floats = (size_t)kMaxGemvRows * c->n_heads * kMaxSplits * 130 + (size_t)kMaxStreamRows * c->n_heads;
     r |= dev_alloc(A, &s->attn_part, part_floats);
     r |= dev_alloc(A, &s->sk_ws, gemm_streamk_ws_floats(s->num_sms));
-    r |= dev_alloc(A, &s->sk_flags, (size_t)s->num_sms + 8);
+    r |= dev_alloc(A, &s->sk_flags, (size_t)2 * s->num_sms + 8);
     r |= dev_alloc(A, &s->lastrow, (size_t)c->max_batch * H);
     r |= dev_alloc(A, &s->lastrow_b, (size_t)c->max_batch * H);
     r |= dev_alloc(A, &s->logits, (size_t)c->max_batch * V);
@@ -177,7 +178,7 @@ extern "C" B200_API int b200_shard_create(const b200_shard_config_t* c, int devi
     if (r != 0) { b200_shard_destroy(s); return B200_ENOMEM; }
     // arrival tickets of decode attention start at zero (the kernel re-zeroes them itself afterwards)
     CU_TRY(cudaMemset(s->attn_part, 0, part_floats * sizeof(float)));
-    CU_TRY(cudaMemset(s->sk_flags, 0, ((size_t)s->num_sms + 8) * sizeof(unsigned int)));
+    CU_TRY(cudaMemset(s->sk_flags, 0, ((size_t)2 * s->num_sms + 8) * sizeof(unsigned int)));
     *out = s;
     return 0;
 }
@@ -350,7 +351,9 @@ static int attn_splits(const b200_shard* s, const b200_kv* kv, int M) {
     }
     // latency-bound kernel; measured sweet spot on B200 (32 heads): 16 splits for one row, 8 for 2..8 rows
     int ns = (M == 1) ? (4 * s->num_sms + s->cfg.n_heads - 1) / s->cfg.n_heads : 8;
-    if (attn_decode_cluster_splits() > 0) ns = attn_decode_cluster_splits();  // one cluster per (row, head), partials over DSMEM
+    // one cluster of 8 / 4 / 2 CTAs per (row, head), partials over DSMEM: about 256 CTAs in all (measured in situ at 128- and
+    // 1024-token contexts: 4 rows 100.7 -> 95.5 us per layer, 8 rows 110.6 -> 103.1 with 2 instead of 8 CTAs per head)
+    if (attn_decode_cluster_splits() > 0) ns = M == 1 ? 8 : (M < 4 ? 4 : 2);
     if (M > kMaxGemvRows) {
         // batched decode: rows x heads already gives hundreds of CTAs; split only as far as ~4 CTAs per SM needs,
         // and never beyond what the scratch for the partials (sized for 8 rows x 16 splits) holds
@@ -358,6 +361,7 @@ static int attn_splits(const b200_shard* s, const b200_kv* kv, int M) {
         const int cap = (kMaxGemvRows * kMaxSplits) / M;
         if (ns > cap) ns = cap;
         if (ns >= 8) ns = attn_decode_cluster_splits() > 0 ? 8 : ns;
+        if (attn_decode_cluster_splits() > 0 && ns > 1 && ns < 8) ns = ns >= 4 ? 4 : 2;   // cluster sizes are powers of two
     }
     if (forced > 0 && M <= kMaxGemvRows) ns = forced;
     // (the online-softmax kernel streams any number of keys per CTA: no minimum split count follows from the context length)
@@ -366,7 +370,8 @@ static int attn_splits(const b200_shard* s, const b200_kv* kv, int M) {
 }
 // does the split-K scratch (8 rows x 16 splits of partials per head) hold this call?  The cluster variant uses none.
 static bool attn_scratch_fits(int M, int ns) {
-    return (ns == attn_decode_cluster_splits() && ns > 0) || ns == 1 || (int64_t)ns * M <= kMaxGemvRows * kMaxSplits;
+    const bool cluster = attn_decode_cluster_splits() > 0 && (ns == 2 || ns == 4 || ns == 8);   // the cluster variant uses no scratch
+    return cluster || ns == 1 || (int64_t)ns * M <= kMaxGemvRows * kMaxSplits;
 }
 
 static bool stream_gemm_enabled() {  // B200SHARD_STREAM_GEMM=0: 9..32-row decode takes the 128 x 128 tile GEMMs instead (A/B)
@@ -469,11 +474,19 @@ static int enqueue_forward(b200_shard_t* s, b200_kv_t* kv, const SlotList& sl, c
         } else if (stream_path) {
             // 4..32 token rows (batched decode, short prompts): still bound by reading the weights once, now on the tensor cores
             // (gemm_stream_tc.cu); operands fp16, residual stream and q fp32, K/V rounded to bf16 once
-            launch_rmsnorm_bf16(s->x, L.norm1, c.rms_eps, M, H, s->xn, st, B200_DT_F16);
+            // RMSNorm is folded into the GEMMs: the projection that updates the residual stream also writes x * w_norm of the
+            // NEXT norm as the fp16 operand (s->xn), the consuming projection applies 1 / rms in its epilogue.  Only the very
+            // first norm of the call has no producer and runs as its own (un-normalised: weight only) pass.
+            // Every consuming CTA re-reads the M x H residual block for the statistics: free up to 16 rows (138 -> 111 us per
+            // layer at 16, 100 -> 89 at 4), a net loss at 32 (136 -> 138), where the two separate norm passes stay.
+            const bool fold = M <= 16;
+            if (!fold) launch_rmsnorm_bf16(s->x, L.norm1, c.rms_eps, M, H, s->xn, st, B200_DT_F16);
+            else if (l == 0) launch_scale_f16(s->x, L.norm1, M, H, reinterpret_cast<__half*>(s->xn), st);
             StreamGemmParams g{};
             g.W = L.wqkv; g.X = s->xn; g.M = M; g.N = s->qkv_rows; g.K = H;
             g.q_out = s->q_f; g.k_pool = kp; g.v_pool = vp; g.kv_off = s->tm.kv_off; g.cos = s->tm.cos; g.sin = s->tm.sin;
             g.n_heads = c.n_heads; g.n_kv = c.n_kv_heads; g.head_stride = head_stride; g.ws = s->sk_ws; g.ws_flags = s->sk_flags;
+            if (fold) { g.x_res = s->x; g.eps = c.rms_eps; }
             if (launch_gemm_stream(g, EPI_QKV, s->num_sms, st) != 0) return fail(B200_ECUDA, "[ERROR] %s", gemm_stream_last_error());
             AttnDecodeParams a{};
             a.q = s->q_f; a.k_pool = kp; a.v_pool = vp; a.block_table = kv->dev.block_table; a.t_end = s->tm.t_end; a.call_base = s->tm.call_base;
@@ -485,15 +498,18 @@ static int enqueue_forward(b200_shard_t* s, b200_kv_t* kv, const SlotList& sl, c
             launch_attn_decode(a, M, st);
             StreamGemmParams o{};
             o.W = L.wo; o.X = s->attn_b; o.M = M; o.N = H; o.K = s->nq; o.out = s->x; o.ws = s->sk_ws; o.ws_flags = s->sk_flags;
+            if (fold) { o.next_norm_w = L.norm2; o.xw_out = reinterpret_cast<__half*>(s->xn); }
             if (launch_gemm_stream(o, EPI_RESID, s->num_sms, st) != 0) return fail(B200_ECUDA, "[ERROR] %s", gemm_stream_last_error());
-            launch_rmsnorm_bf16(s->x, L.norm2, c.rms_eps, M, H, s->xn, st, B200_DT_F16);
+            if (!fold) launch_rmsnorm_bf16(s->x, L.norm2, c.rms_eps, M, H, s->xn, st, B200_DT_F16);
             StreamGemmParams gu{};
             gu.W = L.wgu; gu.X = s->xn; gu.M = M; gu.N = 2 * I; gu.K = H; gu.act_h = reinterpret_cast<__half*>(s->act_b); gu.ws = s->sk_ws; gu.ws_flags = s->sk_flags;
+            if (fold) { gu.x_res = s->x; gu.eps = c.rms_eps; }
             if (launch_gemm_stream(gu, EPI_SWIGLU, s->num_sms, st) != 0) return fail(B200_ECUDA, "[ERROR] %s", gemm_stream_last_error());
             StreamGemmParams d{};
             d.W = L.wdown; d.X = s->act_b; d.M = M; d.N = H; d.K = I; d.out = s->x; d.ws = s->sk_ws; d.ws_flags = s->sk_flags;
+            if (fold && l + 1 < c.n_layers) { d.next_norm_w = s->layers[l + 1].norm1; d.xw_out = reinterpret_cast<__half*>(s->xn); }
             if (launch_gemm_stream(d, EPI_RESID, s->num_sms, st) != 0) return fail(B200_ECUDA, "[ERROR] %s", gemm_stream_last_error());
-            s->n_launch += 7;
+            s->n_launch += fold ? 5 + (l == 0 ? 1 : 0) : 7;
         } else {
             // activations feeding the tensor cores are fp16 (10 mantissa bits) against exact bf16 weights; q reaches
             // attention as a (hi, lo) bf16 pair; K/V are rounded to bf16 exactly once, inside the QKV epilogue
@@ -628,6 +644,7 @@ static int forward_impl(b200_shard_t* s, b200_kv_t* kv, const int32_t* h_slots, 
             if (r == 0 && with_tail) r = enqueue_tail(s, B, S, true, tok, margin, cs);
             cudaGraph_t graph = nullptr;
             cudaError_t ce = cudaStreamEndCapture(cs, &graph);
+            const uint64_t captured = s->n_launch - launches_before;
             s->n_launch = launches_before;
             if (r != 0 || ce != cudaSuccess || graph == nullptr) {
                 cudaGetLastError();
@@ -651,11 +668,12 @@ static int forward_impl(b200_shard_t* s, b200_kv_t* kv, const int32_t* h_slots, 
             }
             GraphEntry ge;
             ge.exec = exec;
+            ge.launches = captured;
             it = s->graph_cache.emplace(key, ge).first;
         }
         it->second.last_use = ++s->graph_clock;
         CU_TRY(cudaGraphLaunch(it->second.exec, st));
-        s->n_launch += 3 + (uint64_t)s->cfg.n_layers * (B <= gemv_row_limit(s) ? 5 : 7) + (out ? 1 : 0) + (with_tail ? (B <= gemv_row_limit(s) ? 2 : 4) : 0) + (tok_in ? 1 : 0);
+        s->n_launch += it->second.launches;
         done = true;
     }
     if (!done) {

@@ -49,7 +49,7 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t* r) {
 template <int MP>
 constexpr uint32_t sw_stage_bytes() { return kSwStageW + MP * kSwK * 2; }
 template <int MP, int kSwStages>
-constexpr size_t sw_smem_bytes() { return 1024 + (size_t)kSwStages * sw_stage_bytes<MP>() + (size_t)kSwRows * MP * 4 + 128; }
+constexpr size_t sw_smem_bytes() { return 1024 + (size_t)kSwStages * sw_stage_bytes<MP>() + (size_t)kSwRows * MP * 4 + 128 + 128; }
 
 template <int MP, int EPI, int kSwStages>
 __global__ void __launch_bounds__(kSwThreads, 2)
@@ -64,6 +64,7 @@ gemm_stream_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_co
     const uint32_t bars = red_u32 + kSwRows * MP * 4;
     const uint32_t full0 = bars, empty0 = bars + 8 * kSwStages, tmem_full = bars + 16 * kSwStages;
     volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(gbase + kSwStages * kStage + kSwRows * MP * 4 + 16 * kSwStages + 8);
+    float* rstd_s = reinterpret_cast<float*>(gbase + kSwStages * kStage + kSwRows * MP * 4 + 128);   // [MP] 1 / rms of every token row (folded RMSNorm)
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int S = p.split;
@@ -132,6 +133,20 @@ gemm_stream_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_co
         asm volatile("griddepcontrol.wait;" ::: "memory");
         const int quad = warp & 3;
         const int t = quad * 32 + lane;                  // weight row inside the tile = TMEM lane
+        if ((EPI == EPI_QKV || EPI == EPI_SWIGLU) && p.x_res != nullptr) {
+            // folded RMSNorm: while the MMAs run, every CTA recomputes the row statistics from the fp32 residual stream (same
+            // loads, same order in every CTA: identical bits everywhere); one warp per token row, xor-shuffle reduction
+            for (int m = quad; m < p.M; m += 4) {
+                const float4* xr = reinterpret_cast<const float4*>(p.x_res + (size_t)m * p.K);
+                float ss = 0.f;
+                for (int i = lane; i < p.K / 4; i += 32) {
+                    const float4 x4 = xr[i];
+                    ss += x4.x * x4.x + x4.y * x4.y + x4.z * x4.z + x4.w * x4.w;
+                }
+                ss = warp_sum(ss);
+                if (lane == 0) rstd_s[m] = rsqrtf(ss / (float)p.K + p.eps);
+            }
+        }
         uint32_t v[MP];
         if (nk > 0) {
             mbar_wait(tmem_full, 0);
@@ -181,11 +196,24 @@ gemm_stream_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_co
             a += red[((s * 2 + 0) * MP + m) * P + jl];
             b += red[((s * 2 + 1) * MP + m) * P + jl];
         }
+        if ((EPI == EPI_QKV || EPI == EPI_SWIGLU) && p.x_res != nullptr) { a *= rstd_s[m]; b *= rstd_s[m]; }
         const int jj = (int)rank * P + jl;               // 0..63 inside the tile
         const int row0 = tile * kSwRows + jj, row1 = row0 + 64;
         if (EPI == EPI_STORE || EPI == EPI_RESID) {
-            if (row0 < p.N) { float* o = p.out + (size_t)m * p.N + row0; *o = (EPI == EPI_RESID) ? (*o + a) : a; }
-            if (row1 < p.N) { float* o = p.out + (size_t)m * p.N + row1; *o = (EPI == EPI_RESID) ? (*o + b) : b; }
+            if (row0 < p.N) {
+                float* o = p.out + (size_t)m * p.N + row0;
+                const float r = (EPI == EPI_RESID) ? (*o + a) : a;
+                *o = r;
+                if (EPI == EPI_RESID && p.xw_out != nullptr)
+                    p.xw_out[(size_t)m * p.N + row0] = __float2half_rn(fminf(fmaxf(r * __bfloat162float(p.next_norm_w[row0]), -65504.f), 65504.f));
+            }
+            if (row1 < p.N) {
+                float* o = p.out + (size_t)m * p.N + row1;
+                const float r = (EPI == EPI_RESID) ? (*o + b) : b;
+                *o = r;
+                if (EPI == EPI_RESID && p.xw_out != nullptr)
+                    p.xw_out[(size_t)m * p.N + row1] = __float2half_rn(fminf(fmaxf(r * __bfloat162float(p.next_norm_w[row1]), -65504.f), 65504.f));
+            }
         } else if (EPI == EPI_SWIGLU) {   // tile = 64 gate rows + the matching 64 up rows
             if (row0 < p.N) p.act_h[(size_t)m * (p.N >> 1) + tile * 64 + jj] = __float2half_rn(fminf(fmaxf(silu(a) * b, -65504.f), 65504.f));
         } else {                          // EPI_QKV: tile == head, rows jj and jj + 64 are a rotate_half pair
@@ -271,7 +299,13 @@ static bool streamk_enabled() {  // B200SHARD_STREAMK=1: the persistent stream-K
 }
 
 int launch_gemm_stream(const StreamGemmParams& p_in, int epi, int num_sms, cudaStream_t st) {
-    if (streamk_enabled() && p_in.split == 0) {
+    // Measured (tools/stream_gemm_bench.py, profiles/stream_gemm_r2.md): the persistent stream-K kernel wins where there are
+    // at least as many 128-row tiles as SMs (gate/up: 172, lm_head: 250) — every SM streams the same bytes through one deep
+    // ring; with fewer tiles a CTA's whole range lies inside one tile, the hand-off of partials sits at the very end of the
+    // kernel, and the cluster split-K kernel below (DSMEM reduce, two CTAs per SM) is faster.
+    static int sk_all = -1;
+    if (sk_all < 0) { const char* e = getenv("B200SHARD_STREAMK_ALL"); sk_all = (e != nullptr && e[0] == '1') ? 1 : 0; }
+    if (streamk_enabled() && p_in.split == 0 && (sk_all == 1 || (p_in.N + kSwRows - 1) / kSwRows >= num_sms)) {
         const int r = launch_gemm_streamk(p_in, epi, num_sms, st);
         if (r != 0) snprintf(g_stream_err, sizeof(g_stream_err), "%s", gemm_streamk_last_error());
         return r;

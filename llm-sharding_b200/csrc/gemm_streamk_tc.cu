@@ -68,13 +68,13 @@ __device__ __forceinline__ void sk_epi_sync() { asm volatile("bar.sync 1, 128;" 
 template <int MP>
 constexpr uint32_t sk_stage_bytes() { return kSkStageW + MP * kSkK * 2; }
 template <int MP, int NS>
-constexpr size_t sk_smem_bytes() { return 1024 + (size_t)NS * sk_stage_bytes<MP>() + (size_t)kSkRows * MP * 4 + 256; }
+constexpr size_t sk_smem_bytes() { return 1024 + (size_t)NS * sk_stage_bytes<MP>() + (size_t)kSkRows * MP * 4 + 256 + 128; }
 
 // first unit of CTA c when `total` units are cut into `grid` equal contiguous ranges
 __device__ __forceinline__ int64_t sk_range_begin(int64_t total, int grid, int c) { return total * c / grid; }
 
 template <int MP, int EPI, int NS>
-__global__ void __launch_bounds__(kSkThreads, 1)
+__global__ void __launch_bounds__(kSkThreads, NS > 5 ? 1 : 2)
 gemm_streamk_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant__ CUtensorMap map_x, const StreamGemmParams p) {
     constexpr uint32_t kStage = sk_stage_bytes<MP>();
     extern __shared__ uint8_t smem_raw[];
@@ -85,6 +85,7 @@ gemm_streamk_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
     const uint32_t bars = base + NS * kStage + kSkRows * MP * 4;
     const uint32_t full0 = bars, empty0 = bars + 8 * NS, tfull0 = bars + 16 * NS, tempty0 = tfull0 + 16;
     volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(gbase + NS * kStage + kSkRows * MP * 4 + 16 * NS + 32);
+    float* rstd_s = reinterpret_cast<float*>(gbase + NS * kStage + kSkRows * MP * 4 + 256);   // [MP] 1 / rms of every token row (folded RMSNorm)
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int cta = blockIdx.x, grid = gridDim.x;
@@ -162,6 +163,19 @@ gemm_streamk_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
         const int quad = warp & 3;
         const int t = quad * 32 + lane;
         const int j = t & 63, half = t >> 6;
+        if ((EPI == EPI_QKV || EPI == EPI_SWIGLU) && p.x_res != nullptr) {   // folded RMSNorm, see gemm_stream_tc.cu
+            for (int m = quad; m < p.M; m += 4) {
+                const float4* xr = reinterpret_cast<const float4*>(p.x_res + (size_t)m * p.K);
+                float ss = 0.f;
+                for (int i = lane; i < p.K / 4; i += 32) {
+                    const float4 x4 = xr[i];
+                    ss += x4.x * x4.x + x4.y * x4.y + x4.z * x4.z + x4.w * x4.w;
+                }
+                ss = warp_sum(ss);
+                if (lane == 0) rstd_s[m] = rsqrtf(ss / (float)p.K + p.eps);
+            }
+            sk_epi_sync();
+        }
         uint32_t si = 0;
         for (int64_t u = u0; u < u1; ++si) {
             const int tile = (int)(u / ks), kb0 = (int)(u % ks);
@@ -193,21 +207,33 @@ gemm_streamk_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
                 continue;
             }
             if (kb0 + n < ks) {
-                // ---- owner of a tile that continues in the following CTAs: add their partials in CTA order
+                // ---- owner of a tile that continues in the following CTAs: wait for all of them at once (one thread per
+                // contributor), then add their partials in CTA order with every load of the gather in flight together
                 const int64_t tile_end = (int64_t)(tile + 1) * ks;
-                for (int cc = cta + 1; cc < grid && sk_range_begin(total, grid, cc) < tile_end; ++cc) {
-                    if (t == 0) {
-                        const long long t0 = clock64();
-                        while (sk_ld_acquire(p.ws_flags + cc) == 0u)
-                            if (clock64() - t0 > (1ll << 31)) __trap();   // ~1 s: a protocol bug must not hang the GPU
-                    }
-                    sk_epi_sync();
-                    const float* slot = p.ws + (size_t)cc * MP * kSkRows;
-#pragma unroll
-                    for (int m = 0; m < MP; ++m) v[m] += __ldcg(slot + m * kSkRows + t);
-                    sk_epi_sync();
-                    if (t == 0) p.ws_flags[cc] = 0u;   // consumed: the slot is free for the next launch on this stream
+                int n_c = 0;
+                while (cta + 1 + n_c < grid && sk_range_begin(total, grid, cta + 1 + n_c) < tile_end) ++n_c;
+                if (t < n_c) {
+                    const long long t0 = clock64();
+                    while (sk_ld_acquire(p.ws_flags + cta + 1 + t) == 0u)
+                        if (clock64() - t0 > (1ll << 31)) __trap();   // ~1 s: a protocol bug must not hang the GPU
                 }
+                sk_epi_sync();
+                constexpr int Q = 64 / MP;   // contributors' blocks per pass: 64 independent loads per thread
+                for (int c0 = 0; c0 < n_c; c0 += Q) {
+                    float w[Q][MP];
+#pragma unroll
+                    for (int q = 0; q < Q; ++q) {
+                        const float* slot = p.ws + (size_t)(cta + 1 + c0 + q) * MP * kSkRows;
+#pragma unroll
+                        for (int m = 0; m < MP; ++m) w[q][m] = (c0 + q < n_c) ? __ldcg(slot + m * kSkRows + t) : 0.f;
+                    }
+#pragma unroll
+                    for (int q = 0; q < Q; ++q)
+#pragma unroll
+                        for (int m = 0; m < MP; ++m) v[m] += w[q][m];
+                }
+                sk_epi_sync();
+                if (t < n_c) p.ws_flags[cta + 1 + t] = 0u;   // consumed: the slots are free for the next launch on this stream
             }
             // ---- finished tile: rows j and j + 64 (a RoPE pair / a gate-up pair) meet in shared memory
 #pragma unroll
@@ -216,11 +242,24 @@ gemm_streamk_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
             const int n_heads = p.n_heads, n_kv = p.n_kv;
             for (int e = t; e < 64 * p.M; e += 128) {
                 const int jj = e & 63, m = e >> 6;
-                const float a = red[(0 * MP + m) * 64 + jj], b = red[(1 * MP + m) * 64 + jj];
+                float a = red[(0 * MP + m) * 64 + jj], b = red[(1 * MP + m) * 64 + jj];
+                if ((EPI == EPI_QKV || EPI == EPI_SWIGLU) && p.x_res != nullptr) { a *= rstd_s[m]; b *= rstd_s[m]; }
                 const int row0 = tile * kSkRows + jj, row1 = row0 + 64;
                 if (EPI == EPI_STORE || EPI == EPI_RESID) {
-                    if (row0 < p.N) { float* o = p.out + (size_t)m * p.N + row0; *o = (EPI == EPI_RESID) ? (*o + a) : a; }
-                    if (row1 < p.N) { float* o = p.out + (size_t)m * p.N + row1; *o = (EPI == EPI_RESID) ? (*o + b) : b; }
+                    if (row0 < p.N) {
+                        float* o = p.out + (size_t)m * p.N + row0;
+                        const float r = (EPI == EPI_RESID) ? (*o + a) : a;
+                        *o = r;
+                        if (EPI == EPI_RESID && p.xw_out != nullptr)
+                            p.xw_out[(size_t)m * p.N + row0] = __float2half_rn(fminf(fmaxf(r * __bfloat162float(p.next_norm_w[row0]), -65504.f), 65504.f));
+                    }
+                    if (row1 < p.N) {
+                        float* o = p.out + (size_t)m * p.N + row1;
+                        const float r = (EPI == EPI_RESID) ? (*o + b) : b;
+                        *o = r;
+                        if (EPI == EPI_RESID && p.xw_out != nullptr)
+                            p.xw_out[(size_t)m * p.N + row1] = __float2half_rn(fminf(fmaxf(r * __bfloat162float(p.next_norm_w[row1]), -65504.f), 65504.f));
+                    }
                 } else if (EPI == EPI_SWIGLU) {   // tile = 64 gate rows + the matching 64 up rows
                     if (row0 < p.N) p.act_h[(size_t)m * (p.N >> 1) + tile * 64 + jj] = __float2half_rn(fminf(fmaxf(silu(a) * b, -65504.f), 65504.f));
                 } else {                          // EPI_QKV: tile == head, rows jj and jj + 64 are a rotate_half pair
@@ -258,7 +297,7 @@ gemm_streamk_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
 static char g_sk_err[256];
 const char* gemm_streamk_last_error() { return g_sk_err; }
 
-size_t gemm_streamk_ws_floats(int num_sms) { return (size_t)num_sms * kMaxStreamRows * kSkRows; }
+size_t gemm_streamk_ws_floats(int num_sms) { return (size_t)2 * num_sms * kMaxStreamRows * kSkRows; }  // up to two CTAs per SM
 
 // Workspace of the stand-alone entry point (b200_gemm_stream_f16): one per device, allocated on first use and kept.  A shard
 // passes its own (StreamGemmParams::ws), so shards on different streams never share partial slots.
@@ -336,9 +375,18 @@ int launch_gemm_streamk(const StreamGemmParams& p_in, int epi, int num_sms, cuda
         return -1;
     }
     const int64_t total = (int64_t)((p.N + kSkRows - 1) / kSkRows) * ((p.K + kSkK - 1) / kSkK);
-    const int grid = (int)(total < num_sms ? total : num_sms);
-    // ring depth: 16 KB of weights + 2 or 4 KB of token rows per stage; 10 stages ~ 200 KB in flight per SM
-#define B200_SK_CASE(E) (MP == 16 ? sk_launch_one<16, E, 11>(mw, mx, p, grid, st) : sk_launch_one<32, E, 10>(mw, mx, p, grid, st))
+    static int deep = -1, waves = -1;
+    if (deep < 0) {
+        const char* e = getenv("B200SHARD_SK_DEEP");    // 1: one CTA per SM with a ~200 KB ring; 0: ~100 KB rings, two CTAs fit an SM
+        deep = (e != nullptr && e[0] == '0') ? 0 : 1;
+        e = getenv("B200SHARD_SK_WAVES");               // CTAs per SM of this grid (1 leaves the second slot to the next kernel's prologue)
+        waves = (e != nullptr && e[0] == '2') ? 2 : 1;
+    }
+    const int64_t want = (int64_t)num_sms * (deep ? 1 : waves);
+    const int grid = (int)(total < want ? total : want);
+    // ring depth: 16 KB of weights + 2 or 4 KB of token rows per stage
+#define B200_SK_CASE(E) (deep ? (MP == 16 ? sk_launch_one<16, E, 11>(mw, mx, p, grid, st) : sk_launch_one<32, E, 10>(mw, mx, p, grid, st)) \
+                              : (MP == 16 ? sk_launch_one<16, E, 5>(mw, mx, p, grid, st) : sk_launch_one<32, E, 5>(mw, mx, p, grid, st)))
     switch (epi) {
         case EPI_STORE: return B200_SK_CASE(EPI_STORE);
         case EPI_RESID: return B200_SK_CASE(EPI_RESID);

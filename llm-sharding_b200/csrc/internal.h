@@ -68,6 +68,7 @@ void launch_load_residual(const void* in, int dtype, float* x, int64_t n, cudaSt
 // x fp32 [rows,n] -> out_dtype (B200_DT_* code: 0 bf16, 1 fp32, 2 fp16 saturating); norm_w == nullptr: plain convert
 void launch_rmsnorm_bf16(const float* x, const __nv_bfloat16* norm_w, float eps, int rows, int n,
                          void* out, cudaStream_t st, int out_dtype = 0);
+void launch_scale_f16(const float* x, const __nv_bfloat16* norm_w, int rows, int n, __half* out, cudaStream_t st);
 // last-row gather + optional norm, fp32 out [B,n] (input rows b*S+S-1)
 void launch_lastrow_norm_f32(const float* x, const __nv_bfloat16* norm_w, float eps, int B, int S, int n,
                              float* out, cudaStream_t st);
@@ -136,6 +137,14 @@ struct StreamGemmParams {
     const float* sin = nullptr;
     int n_heads = 0, n_kv = 0;
     int64_t head_stride = 0;
+    // RMSNorm folded into the GEMMs (batched-decode path).  Producer side, EPI_RESID: besides x += ..., also write
+    // xw_out[m][n] = fp16(x_new * next_norm_w[n]), the un-normalised operand of the NEXT projection.  Consumer side, EPI_QKV /
+    // EPI_SWIGLU with x_res != nullptr: every CTA recomputes rstd[m] = rsqrt(mean(x_res[m]^2) + eps) from the fp32 residual
+    // while its MMAs run, and scales the finished dot products by it (LlamaRMSNorm, modeling_llama.py:62-67).
+    const __nv_bfloat16* next_norm_w = nullptr;
+    __half* xw_out = nullptr;
+    const float* x_res = nullptr;   // [M,K] fp32
+    float eps = 0.f;
     // stream-K kernel (gemm_streamk_tc.cu): partial-sum slots [grid][MP][128] floats and one flag per CTA (zero between launches)
     float* ws = nullptr;
     unsigned int* ws_flags = nullptr;

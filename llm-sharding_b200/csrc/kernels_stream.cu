@@ -151,7 +151,7 @@ __device__ __forceinline__ uint32_t pack_f16_sat(float a, float b) {
 template <int OUT>  // element type of `out`: 0 bf16, 1 fp32, 2 fp16 (saturating) — the B200_DT_* codes
 __global__ void __launch_bounds__(256) rmsnorm_bf16_kernel(const float* __restrict__ x,
                                                            const __nv_bfloat16* __restrict__ w, float eps, int n,
-                                                           __nv_bfloat16* __restrict__ out) {
+                                                           __nv_bfloat16* __restrict__ out, int normalize) {
     __shared__ float red[33];
     // programmatic dependent launch: x comes from the previous kernel; the next kernel (a weight-streaming GEMM in the
     // batched-decode path) may start requesting its weights while this one runs
@@ -161,7 +161,7 @@ __global__ void __launch_bounds__(256) rmsnorm_bf16_kernel(const float* __restri
     __nv_bfloat16* orow = out + (size_t)blockIdx.x * n * (OUT == 1 ? 2 : 1);
     const int n8 = n / 8;
     float rstd = 1.f;
-    if (w != nullptr) {
+    if (w != nullptr && normalize) {
         float ss = 0.f;
         for (int i = threadIdx.x; i < n8; i += blockDim.x) {
             const float4 a = reinterpret_cast<const float4*>(xr)[2 * i], b = reinterpret_cast<const float4*>(xr)[2 * i + 1];
@@ -210,9 +210,14 @@ void launch_rmsnorm_bf16(const float* x, const __nv_bfloat16* norm_w, float eps,
     const char* e = getenv("B200SHARD_PDL");
     cfg.numAttrs = (e != nullptr && e[0] == '0') ? 0 : 1;
     __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(out);
-    if (out_dtype == 2) cudaLaunchKernelEx(&cfg, rmsnorm_bf16_kernel<2>, x, norm_w, eps, n, o);
-    else if (out_dtype == 1) cudaLaunchKernelEx(&cfg, rmsnorm_bf16_kernel<1>, x, norm_w, eps, n, o);
-    else cudaLaunchKernelEx(&cfg, rmsnorm_bf16_kernel<0>, x, norm_w, eps, n, o);
+    const int normalize = eps >= 0.f ? 1 : 0;
+    if (out_dtype == 2) cudaLaunchKernelEx(&cfg, rmsnorm_bf16_kernel<2>, x, norm_w, eps, n, o, normalize);
+    else if (out_dtype == 1) cudaLaunchKernelEx(&cfg, rmsnorm_bf16_kernel<1>, x, norm_w, eps, n, o, normalize);
+    else cudaLaunchKernelEx(&cfg, rmsnorm_bf16_kernel<0>, x, norm_w, eps, n, o, normalize);
+}
+// x * norm_w -> fp16 without the 1 / rms factor (the consuming GEMM applies it to its finished dot products)
+void launch_scale_f16(const float* x, const __nv_bfloat16* norm_w, int rows, int n, __half* out, cudaStream_t st) {
+    launch_rmsnorm_bf16(x, norm_w, -1.f, rows, n, out, st, 2);
 }
 
 __global__ void __launch_bounds__(256) lastrow_norm_f32_kernel(const float* __restrict__ x,
@@ -428,7 +433,7 @@ constexpr int kAttnClusterThreads = 256;
 // Merge of the NG group partials of one CTA (g_acc / g_m / g_l, already published with __syncthreads) and of the n_splits
 // CTAs of one (row, head): over distributed shared memory inside a cluster, through global scratch + arrival ticket
 // otherwise, or not at all when the CTA saw every key.  Shared by the CUDA-core and the tensor-core kernels.
-template <int NG, bool CLUSTER>
+template <int NG, int CL>  // CL: CTAs of the cluster that shares one (row, head) — 2, 4 or 8; 0: no cluster (global scratch + ticket)
 __device__ __forceinline__ void attn_decode_merge(const AttnDecodeParams& p, const float (*g_acc)[kHeadDim], const float* g_m,
                                                   const float* g_l, float (*c_part)[kPartStride], int& s_last, int split, int h,
                                                   int m, int tid) {
@@ -443,7 +448,7 @@ __device__ __forceinline__ void attn_decode_merge(const AttnDecodeParams& p, con
             den = fmaf(w, g_l[g], den);
         }
     }
-    if (CLUSTER) {
+    if (CL > 0) {
         uint32_t rank;
         asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
         // completes the arrive issued at kernel entry: every CTA of the cluster (rank 0 above all) has started, so its
@@ -464,10 +469,10 @@ __device__ __forceinline__ void attn_decode_merge(const AttnDecodeParams& p, con
         if (rank != 0 || tid >= kHeadDim) return;
         float gmx = -INFINITY;
 #pragma unroll
-        for (int s = 0; s < kAttnCluster; ++s) gmx = fmaxf(gmx, c_part[s][kHeadDim]);
+        for (int s = 0; s < (CL > 0 ? CL : 1); ++s) gmx = fmaxf(gmx, c_part[s][kHeadDim]);
         float n2 = 0.f, d2 = 0.f;
 #pragma unroll
-        for (int s = 0; s < kAttnCluster; ++s) {
+        for (int s = 0; s < (CL > 0 ? CL : 1); ++s) {
             const float pm = c_part[s][kHeadDim];
             const float w = (pm == -INFINITY) ? 0.f : exp2f(pm - gmx);
             n2 = fmaf(w, c_part[s][tid], n2);
@@ -519,16 +524,16 @@ __device__ __forceinline__ void attn_decode_merge(const AttnDecodeParams& p, con
 // travel to cluster rank 0 through distributed shared memory and one hardware cluster barrier replaces the global
 // scratch round trip (store, fence, atomic ticket, reload) — the longest links of this latency-bound kernel's chain.
 
-template <int NT, bool CLUSTER>
+template <int NT, int CL>
 __global__ void __launch_bounds__(NT) attn_decode_kernel(const AttnDecodeParams p) {
     constexpr int NG = NT / 16;  // half-warps: keys processed side by side
     __shared__ float g_acc[NG][kHeadDim];
     __shared__ float g_m[NG], g_l[NG];
     __shared__ int s_last;
-    __shared__ float c_part[CLUSTER ? kAttnCluster : 1][kPartStride];  // rank 0's copy gathers the cluster's partials
+    __shared__ float c_part[CL > 0 ? CL : 1][kPartStride];  // rank 0's copy gathers the cluster's partials
     // distributed shared memory may only be touched once the target CTA is known to be running: arrive now (non-blocking),
     // wait right before the remote stores in attn_decode_merge — by then the wait is free
-    if (CLUSTER) asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
+    if (CL > 0) asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
     const int split = blockIdx.x, h = blockIdx.y, m = blockIdx.z;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int l16 = lane & 15, grp = warp * 2 + (lane >> 4);  // NG half-warps, 16 lanes x 8 dims each
@@ -650,7 +655,7 @@ __global__ void __launch_bounds__(NT) attn_decode_kernel(const AttnDecodeParams 
     for (int e = 0; e < 8; ++e) g_acc[grp][l16 * 8 + e] = acc[e];
     if (l16 == 0) { g_m[grp] = m_run; g_l[grp] = l_run; }
     __syncthreads();
-    attn_decode_merge<NG, CLUSTER>(p, g_acc, g_m, g_l, c_part, s_last, split, h, m, tid);
+    attn_decode_merge<NG, CL>(p, g_acc, g_m, g_l, c_part, s_last, split, h, m, tid);
 }
 
 static bool attn_cluster_enabled() {
@@ -667,12 +672,16 @@ void launch_attn_decode(const AttnDecodeParams& p_in, int M, cudaStream_t st) {
     AttnDecodeParams p = p_in;
     if (p.tickets == nullptr)  // default placement: right behind this call's partials
         p.tickets = reinterpret_cast<unsigned int*>(p.part + (size_t)M * p.n_heads * p.n_splits * kPartStride);
-    const bool cluster = attn_cluster_enabled() && p.n_splits == kAttnCluster;
+    // the CTAs that share one (row, head) form a thread-block cluster when there are 2, 4 or 8 of them
+    const bool cluster = attn_cluster_enabled() && (p.n_splits == 2 || p.n_splits == 4 || p.n_splits == 8);
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(p.n_splits, p.n_heads, M);
-    // one row: 256 threads (128 keys per pass, one pass up to 1024 cached tokens); several rows: 128-thread CTAs pack
-    // four to an SM and finish the rows x heads x 8 CTAs in fewer waves (4 rows: 16.3 us against 19.8 us)
-    const bool wide = cluster && M == 1;
+    // 256-thread CTAs (128 keys per pass) while the whole grid is a single wave of at most two CTAs per SM; beyond that
+    // 128-thread CTAs pack four to an SM and finish in fewer waves (4 rows x 8 splits: 16.3 us against 19.8 us)
+    static int wide_env = -1;
+    if (wide_env < 0) { const char* e = getenv("B200SHARD_ATTN_WIDE"); wide_env = e ? atoi(e) : 2; }
+    const int64_t n_cta = (int64_t)p.n_splits * p.n_heads * M;
+    const bool wide = cluster && (wide_env == 1 || (wide_env == 2 && n_cta <= 2 * 148));
     cfg.blockDim = dim3(wide ? kAttnClusterThreads : kAttnThreads);
     cfg.dynamicSmemBytes = 0;
     cfg.stream = st;
@@ -680,7 +689,7 @@ void launch_attn_decode(const AttnDecodeParams& p_in, int M, cudaStream_t st) {
     int na = 0;
     if (cluster) {
         attr[na].id = cudaLaunchAttributeClusterDimension;
-        attr[na].val.clusterDim.x = kAttnCluster;
+        attr[na].val.clusterDim.x = p.n_splits;
         attr[na].val.clusterDim.y = 1;
         attr[na].val.clusterDim.z = 1;
         ++na;
@@ -693,9 +702,18 @@ void launch_attn_decode(const AttnDecodeParams& p_in, int M, cudaStream_t st) {
     }
     cfg.attrs = attr;
     cfg.numAttrs = na;
-    if (cluster && wide) cudaLaunchKernelEx(&cfg, attn_decode_kernel<kAttnClusterThreads, true>, p);
-    else if (cluster) cudaLaunchKernelEx(&cfg, attn_decode_kernel<kAttnThreads, true>, p);
-    else cudaLaunchKernelEx(&cfg, attn_decode_kernel<kAttnThreads, false>, p);
+#define B200_ATTN_LAUNCH(NT_, CL_) cudaLaunchKernelEx(&cfg, attn_decode_kernel<NT_, CL_>, p)
+    if (!cluster) B200_ATTN_LAUNCH(kAttnThreads, 0);
+    else if (wide) {
+        if (p.n_splits == 8) B200_ATTN_LAUNCH(kAttnClusterThreads, 8);
+        else if (p.n_splits == 4) B200_ATTN_LAUNCH(kAttnClusterThreads, 4);
+        else B200_ATTN_LAUNCH(kAttnClusterThreads, 2);
+    } else {
+        if (p.n_splits == 8) B200_ATTN_LAUNCH(kAttnThreads, 8);
+        else if (p.n_splits == 4) B200_ATTN_LAUNCH(kAttnThreads, 4);
+        else B200_ATTN_LAUNCH(kAttnThreads, 2);
+    }
+#undef B200_ATTN_LAUNCH
 }
 size_t attn_decode_scratch_floats(int rows, int n_heads, int n_splits) {
     return (size_t)rows * n_heads * n_splits * kPartStride + (size_t)rows * n_heads;
