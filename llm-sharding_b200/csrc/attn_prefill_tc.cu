@@ -90,6 +90,8 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap map_qhi, const __grid
 
     if (warp == 0) {
         if (lane == 0) {  // ===== TMA producer: K and V rings are independent (a K stage frees up as soon as its scores are issued)
+            asm volatile("griddepcontrol.wait;" ::: "memory");   // q and the new K/V rows come from the QKV projection just before
+            asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
             const int qrow = b * p.S + q0;
             mbar_expect_tx(q_full, 4 * kHalfTile);
             for (int half = 0; half < 2; ++half) {
@@ -298,7 +300,19 @@ int launch_attn_prefill_tc(const AttnPrefillParams& p, int64_t pool_rows, cudaSt
     if (tma_map_2d(&mv, p.v_pool, (int)pool_rows, kHeadDim, 64) != 0) return -1;
     cudaFuncSetAttribute(attn_prefill_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTcSmem);
     dim3 grid((p.S + kQT - 1) / kQT, p.n_heads, p.B);
-    attn_prefill_tc_kernel<<<grid, kTcThreads, kTcSmem, st>>>(mqh, mql, mk, mv, p);
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid;
+    cfg.blockDim = dim3(kTcThreads);
+    cfg.dynamicSmemBytes = kTcSmem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    static int pdl = -1;
+    if (pdl < 0) { const char* e = getenv("B200SHARD_PDL"); pdl = (e != nullptr && e[0] == '0') ? 0 : 1; }
+    cfg.numAttrs = pdl;
+    cudaLaunchKernelEx(&cfg, attn_prefill_tc_kernel, mqh, mql, mk, mv, p);
     return 0;
 }
 

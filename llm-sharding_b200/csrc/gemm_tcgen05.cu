@@ -205,7 +205,17 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
 
     if (warp == 0) {
         if (lane == 0) {  // ===== TMA producer
-            for (int kb = 0; kb < num_k; ++kb) {
+            // programmatic dependent launch: the weight tiles of the first trip round the ring do not depend on the previous
+            // kernel and are requested before griddepcontrol.wait; the activation tiles follow it
+            const int pre = num_k < kStages ? num_k : kStages;
+            for (int kb = 0; kb < pre; ++kb) {
+                mbar_expect_tx(full0 + 8 * kb, kStageBytes);
+                tma_load_2d(&tma_b, full0 + 8 * kb, base + kb * kStageBytes + kStageBytesA, kb * kBlkK, n_blk * kBlkN);
+            }
+            asm volatile("griddepcontrol.wait;" ::: "memory");
+            asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+            for (int kb = 0; kb < pre; ++kb) tma_load_2d(&tma_a, full0 + 8 * kb, base + kb * kStageBytes, kb * kBlkK, m_blk * kBlkM);
+            for (int kb = pre; kb < num_k; ++kb) {
                 const int st = kb % kStages;
                 const uint32_t ph = (uint32_t)(kb / kStages) & 1u;
                 mbar_wait(empty0 + 8 * st, ph ^ 1u);
@@ -231,6 +241,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
             umma_commit(tmem_full);            // accumulator complete
         }
     } else {  // ===== epilogue: warp w may only touch TMEM lanes 32*(w%4) .. +31
+        asm volatile("griddepcontrol.wait;" ::: "memory");   // the residual stream / RoPE table / KV pages belong to earlier kernels
         mbar_wait(tmem_full, 0);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         const int quad = warp & 3;
@@ -330,6 +341,8 @@ gemm_pair_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
 
     if (warp == 0) {
         if (lane == 0) {  // ===== TMA producer (both CTAs): own A rows + own half of B, completion counted on the leader
+            asm volatile("griddepcontrol.wait;" ::: "memory");   // A comes from the previous kernel (the prologue above overlapped its tail)
+            asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
             uint32_t it = 0;
             for (int t = pair_id; t < n_tiles; t += n_pairs) {
                 const int m_row0 = (t % n_m) * 256 + (int)cta_rank * kBlkM;
@@ -367,6 +380,7 @@ gemm_pair_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
             }
         }
     } else {  // ===== epilogue (both CTAs): own 128 lanes, 256 columns = two logical 128-column tiles
+        asm volatile("griddepcontrol.wait;" ::: "memory");
         const int quad = warp & 3;
         uint32_t ti = 0;
         for (int t = pair_id; t < n_tiles; t += n_pairs, ++ti) {
@@ -430,6 +444,24 @@ int tma_map_2d(void* map_out, const void* ptr, int rows, int cols, int box_rows)
     return make_map(reinterpret_cast<CUtensorMap*>(map_out), ptr, rows, cols, box_rows);
 }
 
+// launch with programmatic stream serialization (B200SHARD_PDL=0 turns it off for A/B runs)
+template <typename K>
+static void launch_pdl(K kfn, dim3 grid, size_t smem, cudaStream_t st, const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid;
+    cfg.blockDim = dim3(kGemmThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    static int pdl = -1;
+    if (pdl < 0) { const char* e = getenv("B200SHARD_PDL"); pdl = (e != nullptr && e[0] == '0') ? 0 : 1; }
+    cfg.numAttrs = pdl;
+    cudaLaunchKernelEx(&cfg, kfn, ma, mb, p);
+}
+
 int launch_gemm(const GemmParams& p, cudaStream_t st) {
     if (p.K % 8 != 0 || p.N % 8 != 0 || p.M <= 0) {
         snprintf(g_gemm_err, sizeof(g_gemm_err), "gemm: need K%%8==0, N%%8==0, M>0 (M=%d N=%d K=%d)", p.M, p.N, p.K);
@@ -465,7 +497,7 @@ int launch_gemm(const GemmParams& p, cudaStream_t st) {
     {                                                                                                       \
         auto kfn = gemm_pair_tcgen05_kernel<E>;                                                             \
         cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);                 \
-        kfn<<<grid2, kGemmThreads, smem2, st>>>(ma, mb, p);                                                 \
+        launch_pdl(kfn, grid2, smem2, st, ma, mb, p);                                                       \
     }
         switch (p.epi) {
             case GEMM_STORE_BF16: B200_GEMM2_LAUNCH(GEMM_STORE_BF16) break;
@@ -482,7 +514,7 @@ int launch_gemm(const GemmParams& p, cudaStream_t st) {
     {                                                                                                       \
         auto kfn = gemm_tcgen05_kernel<E>;                                                                  \
         cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGemmSmem);             \
-        kfn<<<grid, kGemmThreads, kGemmSmem, st>>>(ma, mb, p);                                              \
+        launch_pdl(kfn, grid, kGemmSmem, st, ma, mb, p);                                                    \
     }
     switch (p.epi) {
         case GEMM_STORE_BF16: B200_GEMM_LAUNCH(GEMM_STORE_BF16) break;
