@@ -53,8 +53,11 @@ def _run_both(states, x, steps=0):
 def test_outlier_weights_up_to_1e3_keep_parity(B, S):
     g = torch.Generator().manual_seed(B * 10 + S)
     states = [synth.layer_state(CFG, 41, l) for l in range(2)]
-    for st in states:   # a few large entries in every projection that does not feed the SwiGLU product
-        for k in ("self_attn.q_proj.weight", "self_attn.k_proj.weight", "self_attn.v_proj.weight", "self_attn.o_proj.weight", "mlp.down_proj.weight"):
+    # a few large entries in the projections whose outputs are used linearly.  (Not q / k: logits of order 1e3 turn the
+    # softmax into an arg-max over keys that the bf16 K cache — the model dtype, not the fp16 weight store — cannot rank
+    # to 2e-2; not gate / up: their product would leave fp16's range, which the saturation test below covers.)
+    for st in states:
+        for k in ("self_attn.v_proj.weight", "self_attn.o_proj.weight", "mlp.down_proj.weight"):
             w = st[k].float()
             idx = torch.randint(0, w.numel(), (16,), generator=g)
             w.view(-1)[idx] = torch.tensor([1000.0, -1000.0, 512.0, -768.0] * 4)
