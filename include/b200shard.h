@@ -201,6 +201,13 @@ B200_API int b200_rmsnorm(const float* d_x, const void* d_weight_bf16, float eps
 B200_API int b200_attn_decode(const float* d_q, const void* d_k_pool, const void* d_v_pool, const int32_t* d_block_table,
                               const int32_t* d_t_end, int rows, int n_heads, int n_kv_heads, int page_size,
                               int max_pages_per_row, int n_splits, float* d_scratch, float* d_out, void* stream);
+/* The same attention for MANY rows at once (batched decode: one new token of each of a few dozen requests) on the tensor
+ * cores: K/V pages go HBM -> shared memory by TMA and are consumed in place by tcgen05.mma (one CTA per (row, K/V head), all
+ * query heads of the group together); no scratch memory.  max_keys >= every d_t_end[r]; n_pool_pages = pages in the pools.
+ * Up to 8 query heads per K/V head.  Values stored past a row's length inside its last page must be finite. */
+B200_API int b200_attn_decode_tc(const float* d_q, const void* d_k_pool, const void* d_v_pool, const int32_t* d_block_table,
+                                 const int32_t* d_t_end, int rows, int n_heads, int n_kv_heads, int page_size,
+                                 int max_pages_per_row, int n_pool_pages, int max_keys, float* d_out, void* stream);
 /* No counterpart in the reference.  b200_attn_decode without any device-memory allocation, for callers that cannot
  * allocate: a process whose HBM is already fully owned by another pool (serving runtime, torch caching allocator), a
  * per-token loop that must not hit the device-wide synchronisation of cudaMalloc / cudaFree, or a tool working on K/V

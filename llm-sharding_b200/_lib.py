@@ -73,6 +73,7 @@ PROTOTYPES = {
     "b200_shard_set_io_dtype": (_I, [_P, _I]),
     "b200_rmsnorm": (_I, [_P, _P, C.c_float, _I, _I, _P, _P]),
     "b200_attn_decode": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P, _P]),
+    "b200_attn_decode_tc": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _P, _P]),
     "b200_attn_decode_static": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P]),
     "b200_attn_prefill": (_I, [_P] * 6 + [_I] * 9 + [_P, _P]),
     "b200_gemm_bf16": (_I, [_P, _P, _I, _I, _I, _P, _P]),

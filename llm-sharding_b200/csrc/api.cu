@@ -374,6 +374,18 @@ static bool attn_scratch_fits(int M, int ns) {
     return cluster || ns == 1 || (int64_t)ns * M <= kMaxGemvRows * kMaxSplits;
 }
 
+// Rows from which single-token attention runs on the tensor cores with TMA-staged K/V (attn_decode_tc.cu).
+// B200SHARD_ATTN_DECODE_TC=n moves the threshold, 0 turns it off (A/B against the CUDA-core kernel).
+static int attn_decode_tc_min_rows() {
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("B200SHARD_ATTN_DECODE_TC");
+        v = e ? atoi(e) : 0;
+        if (v < 0) v = 0;
+    }
+    return v;
+}
+
 static bool stream_gemm_enabled() {  // B200SHARD_STREAM_GEMM=0: 9..32-row decode takes the 128 x 128 tile GEMMs instead (A/B)
     static int v = -1;
     if (v < 0) {
@@ -441,6 +453,8 @@ static int enqueue_forward(b200_shard_t* s, b200_kv_t* kv, const SlotList& sl, c
     launch_load_residual(in, tok_in != nullptr ? B200_DT_BF16 : s->io_dtype, s->x, (int64_t)M * H, st);
     s->n_launch += 3;
     const bool gemv_path = M <= gemv_row_limit(s);
+    int max_keys = 0;   // longest context any row of this call attends to (the host mirrors the device lengths)
+    for (int b = 0; b < B; ++b) max_keys = kv->h_len[sl.v[b]] + S > max_keys ? kv->h_len[sl.v[b]] + S : max_keys;
     const bool stream_path = !gemv_path && M <= kMaxStreamRows && stream_gemm_enabled() && H % 64 == 0 && I % 64 == 0 &&
                              attn_scratch_fits(M, attn_splits(s, kv, M));
     for (int l = 0; l < c.n_layers; ++l) {
@@ -495,7 +509,11 @@ static int enqueue_forward(b200_shard_t* s, b200_kv_t* kv, const SlotList& sl, c
             a.n_splits = attn_splits(s, kv, M);
             a.part = s->attn_part; a.out = s->attn_f; a.out_h = reinterpret_cast<__half*>(s->attn_b);
             a.tickets = reinterpret_cast<unsigned int*>(s->attn_part + (size_t)kMaxGemvRows * c.n_heads * kMaxSplits * 130);
-            launch_attn_decode(a, M, st);
+            int tc_rc = 1;
+            if (attn_decode_tc_min_rows() > 0 && M >= attn_decode_tc_min_rows())
+                tc_rc = launch_attn_decode_tc(a, M, max_keys, (int64_t)kv->dev.n_pages * c.n_kv_heads * kv->dev.page_size, st);
+            if (tc_rc < 0) return fail(B200_ECUDA, "[ERROR] %s", gemm_error());
+            if (tc_rc == 1) launch_attn_decode(a, M, st);
             StreamGemmParams o{};
             o.W = L.wo; o.X = s->attn_b; o.M = M; o.N = H; o.K = s->nq; o.out = s->x; o.ws = s->sk_ws; o.ws_flags = s->sk_flags;
             if (fold) { o.next_norm_w = L.norm2; o.xw_out = reinterpret_cast<__half*>(s->xn); }
@@ -631,6 +649,8 @@ static int forward_impl(b200_shard_t* s, b200_kv_t* kv, const int32_t* h_slots, 
         GraphKey key;
         memset(&key, 0, sizeof(key));
         key.B = B; key.causal = causal; key.with_argmax = with_tail ? 1 : 0;
+        // the tensor-core decode attention sizes its score buffer in whole kilo-keys: one graph per bucket of the context length
+        if (attn_decode_tc_min_rows() > 0 && B >= attn_decode_tc_min_rows()) key.pad_ = (kv->h_len[sl.v[0]] + S + 1023) / 1024;
         key.in = in; key.out = out; key.tok = tok; key.margin = margin; key.kv_gen = kv->gen; key.tok_in = tok_in;
         for (int b = 0; b < B; ++b) key.slots[b] = sl.v[b];
         auto it = s->graph_cache.find(key);
@@ -1031,6 +1051,26 @@ extern "C" B200_API int b200_attn_decode(const float* q, const void* k_pool, con
     CU_TRY(cudaMemsetAsync(scratch + (size_t)rows * n_heads * n_splits * 130, 0, (size_t)rows * n_heads * sizeof(unsigned int),
                            (cudaStream_t)stream));
     launch_attn_decode(a, rows, (cudaStream_t)stream);
+    CU_TRY(cudaGetLastError());
+    return 0;
+}
+extern "C" B200_API int b200_attn_decode_tc(const float* q, const void* k_pool, const void* v_pool, const int32_t* block_table,
+                                            const int32_t* t_end, int rows, int n_heads, int n_kv_heads, int page_size,
+                                            int max_pages_per_row, int n_pool_pages, int max_keys, float* out, void* stream) {
+    if (q == nullptr || k_pool == nullptr || v_pool == nullptr || block_table == nullptr || t_end == nullptr || out == nullptr)
+        return fail(B200_EINVAL, "[ERROR] null argument");
+    if (rows < 1 || rows > kMaxBatch || n_heads < 1 || n_kv_heads < 1 || n_heads % n_kv_heads != 0 || page_size < 64 ||
+        page_size % 64 != 0 || max_pages_per_row < 1 || n_pool_pages < 1 || max_keys < 1)
+        return fail(B200_EINVAL, "[ERROR] attn_decode_tc: need 1 <= rows <= %d, n_heads %% n_kv_heads == 0, page_size %% 64 == 0", kMaxBatch);
+    AttnDecodeParams a{};
+    a.q = q; a.k_pool = reinterpret_cast<const __nv_bfloat16*>(k_pool); a.v_pool = reinterpret_cast<const __nv_bfloat16*>(v_pool);
+    a.block_table = block_table; a.t_end = t_end;
+    for (int i = 0; i < rows; ++i) a.slots.v[i] = i;
+    a.S = 1; a.n_heads = n_heads; a.n_kv = n_kv_heads; a.page_size = page_size; a.max_pages_per_slot = max_pages_per_row;
+    a.n_splits = 1; a.out = out;
+    const int rc = launch_attn_decode_tc(a, rows, max_keys, (int64_t)n_pool_pages * n_kv_heads * page_size, (cudaStream_t)stream);
+    if (rc == 1) return fail(B200_EINVAL, "[ERROR] attn_decode_tc: more than 8 query heads per K/V head, or a context too long for its score buffer");
+    if (rc < 0) return fail(B200_ECUDA, "[ERROR] %s", gemm_error());
     CU_TRY(cudaGetLastError());
     return 0;
 }

@@ -98,6 +98,9 @@ struct AttnDecodeParams {
 };
 void launch_attn_decode(const AttnDecodeParams& p, int M, cudaStream_t st);
 size_t attn_decode_scratch_floats(int rows, int n_heads, int n_splits);
+// tensor-core / TMA variant for many rows (attn_decode_tc.cu): one CTA per (row, kv head), no scratch.  max_keys = upper bound of
+// t_end over the rows for as long as the launch may be replayed.  0 = launched, 1 = shape not served (use launch_attn_decode), -1 = error
+int launch_attn_decode_tc(const AttnDecodeParams& p, int M, int max_keys, int64_t pool_rows, cudaStream_t st);
 int attn_decode_cluster_splits();  // split count served by the cluster variant (0: disabled by B200SHARD_ATTN_CLUSTER=0)
 
 struct AttnPrefillParams {

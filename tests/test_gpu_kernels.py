@@ -81,13 +81,13 @@ def test_gemv_rejects_bad_shapes(lib):
         _lib.check(lib.b200_gemm_bf16(w.data_ptr(), w.data_ptr(), 8, 8, 60, o.data_ptr(), _st()))
 
 
-def _paged_kv(rows, n_kv, T_list, page_size, g):
+def _paged_kv(rows, n_kv, T_list, page_size, g, fill=float("nan")):
     """random K/V written into a shuffled page pool; returns pools, block table, dense copies"""
     max_pages = max((t + page_size - 1) // page_size for t in T_list)
     n_pages = rows * max_pages + 3
     # rows the sequences never wrote hold NaN: a kernel that lets them leak into a sum (0 x NaN inside an MMA) is caught
-    k_pool = torch.full((n_pages, n_kv, page_size, 128), float("nan"), device="cuda", dtype=torch.bfloat16)
-    v_pool = torch.full_like(k_pool, float("nan"))
+    k_pool = torch.full((n_pages, n_kv, page_size, 128), fill, device="cuda", dtype=torch.bfloat16)
+    v_pool = torch.full_like(k_pool, fill)
     perm = torch.randperm(n_pages, generator=torch.Generator().manual_seed(7)).tolist()
     bt = torch.full((rows, max_pages), -1, dtype=torch.int32)
     dense = []
@@ -134,6 +134,30 @@ def test_attn_decode_split_k(lib, rows, n_heads, n_kv, T_list, n_splits):
                                     n_heads, n_kv, 64, max_pages, n_splits, scratch.data_ptr(), out.data_ptr(), _st()))
     ref = attn_decode_reference(q, dense, n_heads, n_kv)
     assert rel_l2(out, ref) < 1e-5  # fp32 softmax and accumulation over bf16 K/V; only summation order differs
+
+
+@pytest.mark.parametrize("rows,n_heads,n_kv,T_list", [
+    (1, 2, 2, [1]), (2, 4, 4, [128, 129]), (3, 8, 2, [65, 640, 7]), (4, 32, 32, [704, 704, 333, 1]), (2, 32, 8, [1500, 2048]),
+    (32, 4, 4, list(range(40, 40 + 32 * 37, 37))), (1, 8, 1, [300]), (2, 2, 2, [4096, 3000]), (1, 2, 2, [9000])])
+def test_attn_decode_tensor_core(lib, rows, n_heads, n_kv, T_list):
+    """Batched decode attention on tcgen05 + TMA (one CTA per row and K/V head, grouped query heads as the narrow operand,
+    two passes over the keys).  fp32 q travels as three bf16 parts, probabilities as hi + lo: the same 1e-5 bound as the
+    CUDA-core kernel up to 4096 keys.  Beyond that the output is one fp32 tensor-memory accumulator fed by hundreds of
+    MMAs whose adder truncates rather than rounds (measured 2.2e-5 at 9000 keys): bound 4e-5 there.  Rows past a
+    sequence's end hold large finite values (stale page contents), not NaN."""
+    from llm_sharding_b200 import _lib
+    g = torch.Generator(device="cuda").manual_seed(rows * 100 + n_heads + T_list[0])
+    k_pool, v_pool, bt, dense, max_pages = _paged_kv(rows, n_kv, T_list, 64, g, fill=1.0e4)
+    q = torch.randn(rows, n_heads * 128, device="cuda", generator=g)
+    t_end = torch.tensor(T_list, dtype=torch.int32, device="cuda")
+    out = torch.full_like(q, float("nan"))
+    for _ in range(2):   # the second launch meets whatever the first left in shared / tensor memory
+        _lib.check(lib.b200_attn_decode_tc(q.data_ptr(), k_pool.data_ptr(), v_pool.data_ptr(), bt.data_ptr(), t_end.data_ptr(), rows,
+                                           n_heads, n_kv, 64, max_pages, k_pool.shape[0], max(T_list), out.data_ptr(), _st()))
+    torch.cuda.synchronize()
+    assert torch.isfinite(out).all()
+    ref = attn_decode_reference(q, dense, n_heads, n_kv)
+    assert rel_l2(out, ref) < (1e-5 if max(T_list) <= 4096 else 4e-5)
 
 
 @pytest.mark.parametrize("M,N,K", [(128, 128, 64), (200, 384, 512), (512, 4096, 4096), (77, 4096, 11008)])
