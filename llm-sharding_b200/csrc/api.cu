@@ -380,10 +380,18 @@ static int attn_decode_tc_min_rows() {
     static int v = -1;
     if (v < 0) {
         const char* e = getenv("B200SHARD_ATTN_DECODE_TC");
-        v = e ? atoi(e) : 0;
+        v = e ? atoi(e) : 8;
         if (v < 0) v = 0;
     }
     return v;
+}
+// Measured in the layer (profiles/attn_decode_tc_r2.md): from 16 rows the tensor-core kernel wins at every context length
+// (16 rows x 640 keys: 143 -> 124 us per layer), at 8..15 rows up to about a thousand keys (8 x 640: 113 -> 104); below 8
+// rows, and for 8..15 rows on longer contexts, the CUDA-core kernel with its 2-CTA clusters per head is as fast or faster.
+static bool use_attn_decode_tc(int M, int max_keys) {
+    const int lo = attn_decode_tc_min_rows();
+    if (lo == 0 || M < lo) return false;
+    return M >= 16 || max_keys <= 1024 || lo < 8;
 }
 
 static bool stream_gemm_enabled() {  // B200SHARD_STREAM_GEMM=0: 9..32-row decode takes the 128 x 128 tile GEMMs instead (A/B)
@@ -510,7 +518,7 @@ static int enqueue_forward(b200_shard_t* s, b200_kv_t* kv, const SlotList& sl, c
             a.part = s->attn_part; a.out = s->attn_f; a.out_h = reinterpret_cast<__half*>(s->attn_b);
             a.tickets = reinterpret_cast<unsigned int*>(s->attn_part + (size_t)kMaxGemvRows * c.n_heads * kMaxSplits * 130);
             int tc_rc = 1;
-            if (attn_decode_tc_min_rows() > 0 && M >= attn_decode_tc_min_rows())
+            if (use_attn_decode_tc(M, max_keys))
                 tc_rc = launch_attn_decode_tc(a, M, max_keys, (int64_t)kv->dev.n_pages * c.n_kv_heads * kv->dev.page_size, st);
             if (tc_rc < 0) return fail(B200_ECUDA, "[ERROR] %s", gemm_error());
             if (tc_rc == 1) launch_attn_decode(a, M, st);
