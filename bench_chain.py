@@ -269,7 +269,7 @@ def run_chain(args, config, metric, ClockSampler, peaks):
     dist.all_reduce(err, op=dist.ReduceOp.MAX, group=ctrl)
 
     # ---- the named configurations of BASELINE.json on the same worker and the same ring code
-    c3 = c4 = None
+    c3 = c4 = hop_pipe = None
     if extras:
         clear_all()
         stage.close()
@@ -319,6 +319,52 @@ def run_chain(args, config, metric, ClockSampler, peaks):
               "stage_bytes_per_call": float(c3_b[0]), "stage_hbm_gbs": float(c3_b[0]) / stage_s / 1e9,
               "stage_hbm_frac": float(c3_b[0]) / stage_s / 1e9 / pk["hbm_gbs"], "hop_error_flag": int(c3_err)}
 
+        # the hop as it costs inside the pipeline: ONE stream alone goes round the ring (every stage strictly after the
+        # other), against the same stage calls timed on local buffers; the difference per stage boundary is wait kernel +
+        # NVLink store + flag + publish kernel, i.e. everything the hop adds to a token's path
+        st1, pr1 = ring(1, 1, 64)
+        st1.prefill(0, 64, pr1[0] if rank == 0 else None)
+        for _ in range(W):
+            st1.decode(0)
+        n_ser = 64
+        ser_ms = timed(lambda: [st1.decode(0) for _ in range(n_ser)]) / n_ser
+        reset(st1)
+        st1.close()
+        import ctypes as C
+        kv1 = worker.past_key_value
+        hid = torch.zeros(1, 1, cfg["hidden_size"], dtype=torch.bfloat16, device=device)
+        hid_out = torch.empty_like(hid)
+        tok1 = torch.full((1,), 17, dtype=torch.int64, device=device)
+        tok_out = torch.empty_like(tok1)
+        slots1 = (C.c_int32 * 1)(0)
+        lib1, eh, kh, sp = eng.lib, eng.handle, kv1.handle, torch.cuda.current_stream(device).cuda_stream
+
+        def local_call():
+            if rank == 0 and world > 1:
+                lib1.b200_shard_step_tokens(eh, kh, slots1, tok1.data_ptr(), 1, 1, 0, hid_out.data_ptr(), None, None, sp)
+            elif rank == world - 1:
+                lib1.b200_shard_forward_argmax(eh, kh, slots1, hid.data_ptr(), 1, 1, 0, None, tok_out.data_ptr(), None, sp)
+            else:
+                lib1.b200_shard_forward(eh, kh, slots1, hid.data_ptr(), 1, 1, 0, hid_out.data_ptr(), sp)
+        for _ in range(64 + W):   # same context length as the ring run had
+            local_call()
+        torch.cuda.synchronize()
+        e0, e1 = ev(), ev()
+        e0.record()
+        for _ in range(n_ser):
+            local_call()
+        e1.record()
+        torch.cuda.synchronize()
+        comp = torch.tensor([e0.elapsed_time(e1) / n_ser], dtype=torch.float64)
+        dist.all_reduce(comp, op=dist.ReduceOp.SUM, group=ctrl)
+        worker.past_key_value.reset(-1)
+        torch.cuda.synchronize()
+        dist.barrier(group=ctrl)
+        hop_pipe = {"serial_round_us": 1000 * ser_ms, "sum_of_stage_calls_us": 1000 * float(comp[0]),
+                    "per_hop_us": 1000 * (ser_ms - float(comp[0])) / world,
+                    "how": "one stream alone round the ring (64-token context, 64 rounds) minus the same stage calls on local "
+                           "buffers, divided by the number of stage boundaries (token return included)"}
+
         # configs[3]: prefill-heavy, 16 x 2048-token prompts through the whole chain as 16 micro-batches of one prompt
         st4, pr4 = ring(c4_streams, 1, c4_prompt)
 
@@ -361,7 +407,7 @@ def run_chain(args, config, metric, ClockSampler, peaks):
                          "frac": per_gpu_bytes / (stage_ms / 1000) / 1e9 / pk["hbm_gbs"], "traffic": None, "peak_source": pk["source"]},
             "hop": hop_lat, "hop_error_flag": int(err[0]),
             "prefill_tok_s": prefill_tok_s, "p50_token_ms": ms_per_step,
-            "parity": parity, "c3_batch32": c3, "c4_prefill": c4,
+            "parity": parity, "c3_batch32": c3, "c4_prefill": c4, "hop_in_pipeline": hop_pipe,
         }
         print(json.dumps(line), flush=True)
     dist.barrier(group=ctrl)
