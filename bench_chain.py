@@ -363,7 +363,8 @@ def run_chain(args, config, metric, ClockSampler, peaks):
         hop_pipe = {"serial_round_us": 1000 * ser_ms, "sum_of_stage_calls_us": 1000 * float(comp[0]),
                     "per_hop_us": 1000 * (ser_ms - float(comp[0])) / world,
                     "how": "one stream alone round the ring (64-token context, 64 rounds) minus the same stage calls on local "
-                           "buffers, divided by the number of stage boundaries (token return included)"}
+                           "buffers, divided by the number of stage boundaries (token return included); a difference of two "
+                           "millisecond-scale timings: resolution about 0.2 % of the round, so meaningful at 8 stages, noise at 2"}
 
         # configs[3]: prefill-heavy, 16 x 2048-token prompts through the whole chain as 16 micro-batches of one prompt
         st4, pr4 = ring(c4_streams, 1, c4_prompt)
