@@ -335,3 +335,69 @@ def test_ring_server_stop_rules_on_a_single_stage_ring(tmp_path):
         w.shard.engine.close()
     finally:
         dist.destroy_process_group()
+
+
+def _controller_proc(rank, d, ports, prompt, n_new, q):
+    """One NodeController process on its own GPU, P2P transport (the reference's deployment: run_this.sh starts one
+    start_node.py per node; the master sends each its config)."""
+    import time
+    from llm_sharding_b200.node_worker import NodeController
+    torch.cuda.set_device(rank)
+    c = NodeController(d, f"cuda:{rank}", torch.bfloat16, listen_port=ports[f"cfg{rank}"], max_tokens=64, use_graphs=False, transport="p2p")
+    try:
+        w = c.node_worker
+        if rank == 0:
+            c.receive_request(input_ids=prompt)
+        deadline = time.time() + 90
+        seen_work = False
+        while time.time() < deadline:
+            handled = c.step(n_new)
+            seen_work = seen_work or handled
+            if rank == 0 and c._seen_tokens >= n_new and w.generated_ids == [] and w.past_key_value.get_seq_length() == 0:
+                break
+            if rank == 1 and seen_work and w.past_key_value.get_seq_length() == 0 and w.communicator.seq_in > n_new:
+                break
+        q.put((rank, c._token_log, w.communicator.seq_out, w.communicator.hop.error()))
+    finally:
+        c.node_worker.communicator.close()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_two_node_controllers_on_two_gpus_over_p2p_communicator(tmp_path):
+    """Two NodeController PROCESSES, one per GPU, configured by ConfigSender; hidden states, token ids and the clear-cache
+    command cross NVLink through P2PCommunicator (CUDA-IPC mailbox, handles exchanged over the ZeroMQ control sockets).
+    Tokens must be the reference chain's (tests/golden/tiny_b1.npz)."""
+    import time
+    import torch.multiprocessing as mp
+    from golden_utils import load_golden
+    from gpu_utils import shard_dir
+    from llm_sharding_b200.config_sender import ConfigSender
+    z, meta = load_golden("tiny_b1")
+    d = shard_dir(str(tmp_path), meta["preset"], meta["seed"])
+    ports = dict(cfg0=45960, cfg1=45961, d0=45970, d1=45971)
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    prompt = torch.from_numpy(z["prompt"])
+    procs = [ctx.Process(target=_controller_proc, args=(r, d, ports, prompt, meta["new_tokens"], q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    s0, s1 = ConfigSender(ports["cfg0"]), ConfigSender(ports["cfg1"])
+    s0.build_config(0, 2, True, f"tcp://127.0.0.1:{ports['d0']}", f"tcp://127.0.0.1:{ports['d1']}", f"tcp://127.0.0.1:{ports['d0']}")
+    s1.build_config(2, 4, False, f"tcp://127.0.0.1:{ports['d1']}", f"tcp://127.0.0.1:{ports['d0']}")
+    time.sleep(1.0)
+    s0.send_config("127.0.0.1")
+    s1.send_config("127.0.0.1")
+    got = {}
+    try:
+        for _ in range(2):
+            rank, log, seq_out, err = q.get(timeout=180)
+            got[rank] = (log, seq_out, err)
+    finally:
+        for p in procs:
+            p.join(30)
+            if p.is_alive():
+                p.terminate()
+        s0.close(); s1.close()
+    assert got[0][0] == [int(t) for t in z["tokens"][:, 0]]
+    assert got[0][2] == 0 and got[1][2] == 0
+    assert got[0][1] >= meta["new_tokens"] and got[1][1] >= meta["new_tokens"]
