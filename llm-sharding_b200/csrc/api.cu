@@ -391,7 +391,8 @@ static int attn_decode_tc_min_rows() {
 static bool use_attn_decode_tc(int M, int max_keys) {
     const int lo = attn_decode_tc_min_rows();
     if (lo == 0 || M < lo) return false;
-    return M >= 16 || max_keys <= 1024 || lo < 8;
+    (void)max_keys;
+    return true;
 }
 
 static bool stream_gemm_enabled() {  // B200SHARD_STREAM_GEMM=0: 9..32-row decode takes the 128 x 128 tile GEMMs instead (A/B)

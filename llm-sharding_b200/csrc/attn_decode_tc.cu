@@ -9,10 +9,15 @@
 // One CTA = one (row, kv head): all n_heads / n_kv query heads that share the K/V (1 for Llama-2, 4 for Llama-3.x).
 // The roles of the operands are swapped so that the 128-wide M side of the MMA is always full although there is a
 // single query token:
-//   S^T [128 keys x 8]  = K_tile [128 keys x 128 d]  (A, K-major, straight from the page layout)
-//                         x Q^T  [128 d x 8 heads]    (B: the group's query heads, padded to N = 8; fp32 q as three bf16 parts)
-//   O^T [128 d x 8]    += V_tile^T [128 d x 128 keys] (A, MN-major: the natural [token][dim] page layout, no transpose)
-//                         x P^T  [128 keys x 8 heads] (B, K-major, bf16 hi + lo parts)
+//   S^T [128 keys x 16] = K_tile [128 keys x 128 d]  (A, K-major, straight from the page layout)
+//                         x Q^T  [128 d x 16]         (B, K-major)
+//   O^T [128 d x 16]   += V_tile^T [128 d x 128 keys] (A, MN-major: the natural [token][dim] page layout, no transpose)
+//                         x P^T  [128 keys x 16]      (B, K-major)
+// The 16 columns of the narrow operand carry PRECISION, not padding: fp32 q is split into bf16 parts (hi, mid, lo) and
+// the parts of head h sit in columns h, g + h, 2g + h of the same operand, so ONE pass over the K tile yields the partial
+// scores of every part and the softmax thread adds its columns; the probabilities travel the same way as hi and lo
+// columns and the two output columns are added at the end.  (Measured before this layout, with one MMA pass per part: 40
+// MMAs per 128 keys made the kernel MMA-issue bound, 64-81 % of HBM; 16 MMAs reach 92-94 %, profiles/attn_decode_tc_r2.md.)
 // Two passes over the CTA's keys, so no accumulator is ever rescaled: pass 1 streams the K pages and parks the
 // scaled scores in shared memory (4 bytes per key and head) while a running maximum is kept; pass 2 streams the V pages,
 // turns scores into probabilities against the final maximum and accumulates O^T in tensor memory.  K and V tiles share
@@ -37,11 +42,19 @@ using namespace tc;
 constexpr int kDtThreads = 192;
 constexpr uint32_t kDtTile = 128 * 128 * 2;       // one 128-key K or V tile: 32 KB (two 128B-swizzled halves of 64 dims)
 constexpr uint32_t kDtHalf = kDtTile / 2;
-constexpr uint32_t kDtQBytes = 3 * 2 * 1024;      // q: 3 bf16 parts x 2 dim-halves x one 8-row swizzle atom (pass 1)
-constexpr uint32_t kDtPBytes = 2 * 2 * 2 * 1024;  // P: 2 buffers x (hi, lo) x 2 key-halves x one atom (pass 2, same space)
-static_assert(kDtQBytes <= kDtPBytes, "q parts live in the P buffers' space");
-constexpr int kDtMaxGroup = 8;                    // query heads per kv head that fit the N = 8 operand
+constexpr uint32_t kDtQBytes = 2 * 2 * 1024;      // q operand: 2 dim-halves x two 8-row swizzle atoms (pass 1)
+constexpr uint32_t kDtPBytes = 2 * 2 * 2 * 1024;  // P operand: 2 buffers x 2 key-halves x two atoms (pass 2, same space)
+static_assert(kDtQBytes <= kDtPBytes, "the q operand lives in the P buffers' space");
+constexpr int kDtMaxGroup = 8;                    // query heads per kv head (2 probability columns each)
 
+__device__ __forceinline__ void dt_tmem_ld16(uint32_t taddr, uint32_t* r) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
 __device__ __forceinline__ void dt_tmem_ld8(uint32_t taddr, uint32_t* r) {
     asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                  : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
@@ -49,21 +62,24 @@ __device__ __forceinline__ void dt_tmem_ld8(uint32_t taddr, uint32_t* r) {
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 __device__ __forceinline__ void dt_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }   // the four softmax warps
-// byte offset of element (row r < 8, column c < 64) inside one 8-row x 128-byte SWIZZLE_128B atom of 16-bit elements
-__device__ __forceinline__ uint32_t dt_atom_off(int r, int c) { return (uint32_t)(r * 128 + ((((c >> 3) ^ r) & 7) << 4) + (c & 7) * 2); }
+// byte offset of element (operand row r < 16, column c < 64) inside a 16-row K-major SWIZZLE_128B block: two 8-row atoms
+__device__ __forceinline__ uint32_t dt_op_off(int r, int c) {
+    return (uint32_t)((r >> 3) * 1024 + (r & 7) * 128 + ((((c >> 3) ^ r) & 7) << 4) + (c & 7) * 2);
+}
 __device__ __forceinline__ float dt_ex2(float x) {
     float y;
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
 }
 
-
 struct DtParams {
     AttnDecodeParams a;
     int sc_stride;   // keys the score buffer holds per head (a multiple of 128)
+    int q_parts;     // bf16 parts of q: 3 while 3 * group <= 16, else 2
 };
 
-template <int NS>
+// kDtN: columns of the narrow operand — 8 while the parts of the group fit (3 * g <= 8, e.g. MHA), else 16
+template <int NS, int kDtN>
 __global__ void __launch_bounds__(kDtThreads, NS <= 3 ? 2 : 1)
 attn_decode_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_constant__ CUtensorMap map_v, const DtParams dp) {
     const AttnDecodeParams& p = dp.a;
@@ -104,15 +120,15 @@ attn_decode_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_co
         mbar_init(q_full, 4);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == 1) {  // S^T buffers at columns 0 and 8, O^T at column 16
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(s_u32((const void*)tmem_slot)), "n"(32) : "memory");
+    if (warp == 1) {  // S^T buffers at columns 0 and 16, O^T at column 32
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(s_u32((const void*)tmem_slot)), "n"(64) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     fence_before();
     __syncthreads();
     fence_after();
     const uint32_t tmem_base = *tmem_slot;
-    const uint32_t tmem_o = tmem_base + 16;
+    const uint32_t tmem_o = tmem_base + 32;
 
     if (warp == 0) {
         if (lane == 0) {  // ===== TMA producer: K tiles of pass 1, then V tiles of pass 2, one ring
@@ -144,8 +160,8 @@ attn_decode_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_co
         }
     } else if (warp == 1) {
         if (lane == 0) {  // ===== MMA issuer
-            constexpr uint32_t idesc_qk = umma_idesc(128, 8, 1, 0, 0);   // bf16; K tile K-major, q K-major
-            constexpr uint32_t idesc_pv = umma_idesc(128, 8, 1, 1, 0);   // bf16; V tile MN-major (A), P K-major
+            constexpr uint32_t idesc_qk = umma_idesc(128, kDtN, 1, 0, 0);   // bf16; K tile K-major, q K-major
+            constexpr uint32_t idesc_pv = umma_idesc(128, kDtN, 1, 1, 0);   // bf16; V tile MN-major (A), P K-major
             const uint32_t qp = base + kOffQP;
             mbar_wait(q_full, 0);
             fence_after();
@@ -154,18 +170,13 @@ attn_decode_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_co
                 mbar_wait(full0 + 8 * st, (uint32_t)(j / NS) & 1u);
                 mbar_wait(s_empty0 + 8 * (j & 1), (((uint32_t)j >> 1) & 1u) ^ 1u);
                 fence_after();
-                const uint32_t kt = base + (uint32_t)st * kDtTile, acc = tmem_base + (uint32_t)(j & 1) * 8;
-                uint32_t first = 0;
+                const uint32_t kt = base + (uint32_t)st * kDtTile, acc = tmem_base + (uint32_t)(j & 1) * kDtN;
 #pragma unroll
-                for (int part = 0; part < 3; ++part)
+                for (int half = 0; half < 2; ++half)
 #pragma unroll
-                    for (int half = 0; half < 2; ++half)
-#pragma unroll
-                        for (int k = 0; k < 4; ++k) {
-                            umma_f16(acc, umma_desc_sw128(kt + half * kDtHalf + k * 32, 16, 1024),
-                                     umma_desc_sw128(qp + (part * 2 + half) * 1024 + k * 32, 16, 1024), idesc_qk, first);
-                            first = 1;
-                        }
+                    for (int k = 0; k < 4; ++k)   // every bf16 part of every head of the group rides in the 16 columns: one pass
+                        umma_f16(acc, umma_desc_sw128(kt + half * kDtHalf + k * 32, 16, 1024),
+                                 umma_desc_sw128(qp + half * 2048 + k * 32, 16, 1024), idesc_qk, (half > 0 || k > 0) ? 1u : 0u);
                 umma_commit(s_full0 + 8 * (j & 1));
                 umma_commit(empty0 + 8 * st);
             }
@@ -175,15 +186,11 @@ attn_decode_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_co
                 mbar_wait(p_full0 + 8 * (j & 1), ((uint32_t)j >> 1) & 1u);
                 fence_after();
                 const uint32_t vt = base + (uint32_t)st * kDtTile;
+                const uint32_t pb = qp + (uint32_t)(j & 1) * 4096;
 #pragma unroll
-                for (int part = 0; part < 2; ++part) {
-                    const uint32_t pb = qp + (uint32_t)(((j & 1) * 2 + part) * 2) * 1024;
-#pragma unroll
-                    for (int kk = 0; kk < 8; ++kk)   // 16 keys per MMA
-                        umma_f16(tmem_o, umma_desc_sw128(vt + kk * 2048, kDtHalf, 1024),
-                                 umma_desc_sw128(pb + (kk >> 2) * 1024 + (kk & 3) * 32, 16, 1024), idesc_pv,
-                                 (j > 0 || part > 0 || kk > 0) ? 1u : 0u);
-                }
+                for (int kk = 0; kk < 8; ++kk)   // 16 keys per MMA; hi and lo probabilities are different columns
+                    umma_f16(tmem_o, umma_desc_sw128(vt + kk * 2048, kDtHalf, 1024),
+                             umma_desc_sw128(pb + (kk >> 2) * 2048 + (kk & 3) * 32, 16, 1024), idesc_pv, (j > 0 || kk > 0) ? 1u : 0u);
                 umma_commit(p_empty0 + 8 * (j & 1));
                 umma_commit(empty0 + 8 * st);
             }
@@ -195,18 +202,25 @@ attn_decode_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_co
         const int t = quad * 32 + lane;
         const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
         uint8_t* qp = gbase + kOffQP;
-        // ---- q: fp32 -> three bf16 parts (24 mantissa bits), rows >= g are zero, laid out as the 8-row B operand
-        for (int idx = t; idx < 8 * 128; idx += 128) {
-            const int r = idx >> 7, c = idx & 127;
-            const float v = r < g ? p.q[((size_t)m * p.n_heads + kvh * g + r) * kHeadDim + c] : 0.f;
-            const __nv_bfloat16 hi = __float2bfloat16_rn(v);
-            const float r1 = v - __bfloat162float(hi);
-            const __nv_bfloat16 mid = __float2bfloat16_rn(r1);
-            const __nv_bfloat16 lo = __float2bfloat16_rn(r1 - __bfloat162float(mid));
-            const uint32_t off = (uint32_t)(c >> 6) * 1024 + dt_atom_off(r, c & 63);
-            *reinterpret_cast<__nv_bfloat16*>(qp + 0 * 2048 + off) = hi;
-            *reinterpret_cast<__nv_bfloat16*>(qp + 1 * 2048 + off) = mid;
-            *reinterpret_cast<__nv_bfloat16*>(qp + 2 * 2048 + off) = lo;
+        // ---- q: fp32 -> bf16 parts; part i of head h is operand row i * g + h, the other rows are zero.  Thread t owns dim t.
+        {
+            uint8_t* qcol = qp + (uint32_t)(t >> 6) * 2048;
+            const int c = t & 63;
+            for (int r = 0; r < kDtN; ++r) *reinterpret_cast<__nv_bfloat16*>(qcol + dt_op_off(r, c)) = __float2bfloat16_rn(0.f);
+            float qv[kDtMaxGroup];
+#pragma unroll
+            for (int h = 0; h < kDtMaxGroup; ++h)   // independent loads
+                qv[h] = h < g ? p.q[((size_t)m * p.n_heads + kvh * g + h) * kHeadDim + t] : 0.f;
+#pragma unroll
+            for (int h = 0; h < kDtMaxGroup; ++h)
+                if (h < g) {
+                    float v = qv[h];
+                    for (int part = 0; part < dp.q_parts; ++part) {
+                        const __nv_bfloat16 o = __float2bfloat16_rn(v);
+                        *reinterpret_cast<__nv_bfloat16*>(qcol + dt_op_off(part * g + h, c)) = o;
+                        v -= __bfloat162float(o);
+                    }
+                }
         }
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         __syncwarp();
@@ -219,8 +233,9 @@ attn_decode_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_co
         for (int j = 0; j < n_t; ++j) {
             mbar_wait(s_full0 + 8 * (j & 1), ((uint32_t)j >> 1) & 1u);
             fence_after();
-            uint32_t r[8];
-            dt_tmem_ld8(tmem_base + (uint32_t)(j & 1) * 8 + lane_addr, r);
+            uint32_t r[16];
+            if constexpr (kDtN == 16) dt_tmem_ld16(tmem_base + (uint32_t)(j & 1) * kDtN + lane_addr, r);
+            else dt_tmem_ld8(tmem_base + (uint32_t)(j & 1) * kDtN + lane_addr, r);
             fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(s_empty0 + 8 * (j & 1));
@@ -228,7 +243,10 @@ attn_decode_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_co
 #pragma unroll
             for (int h = 0; h < kDtMaxGroup; ++h)
                 if (h < g) {
-                    const float s = key < T ? __uint_as_float(r[h]) * scale_log2 : -INFINITY;
+                    float dot = __uint_as_float(r[h]);   // columns h, g + h, 2g + h: the partial scores of the bf16 parts of q
+                    if (dp.q_parts > 1) dot += __uint_as_float(r[g + h]);
+                    if (dp.q_parts > 2) dot += __uint_as_float(r[2 * g + h]);
+                    const float s = key < T ? dot * scale_log2 : -INFINITY;
                     sc[h * dp.sc_stride + key] = s;
                     m_run[h] = fmaxf(m_run[h], s);
                 }
@@ -249,7 +267,7 @@ attn_decode_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_co
         for (int j = 0; j < n_t; ++j) {
             mbar_wait(p_empty0 + 8 * (j & 1), (((uint32_t)j >> 1) & 1u) ^ 1u);
             const int key = j * 128 + t;
-            uint8_t* pb = qp + (uint32_t)((j & 1) * 4) * 1024 + (uint32_t)(t >> 6) * 1024;
+            uint8_t* pb = qp + (uint32_t)(j & 1) * 4096 + (uint32_t)(t >> 6) * 2048;
 #pragma unroll
             for (int h = 0; h < kDtMaxGroup; ++h)
                 if (h < g) {
@@ -258,9 +276,8 @@ attn_decode_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_co
                     l_run[h] += pr;
                     const __nv_bfloat16 hi = __float2bfloat16_rn(pr);
                     const __nv_bfloat16 lo = __float2bfloat16_rn(pr - __bfloat162float(hi));
-                    const uint32_t off = dt_atom_off(h, t & 63);
-                    *reinterpret_cast<__nv_bfloat16*>(pb + off) = hi;
-                    *reinterpret_cast<__nv_bfloat16*>(pb + 2048 + off) = lo;
+                    *reinterpret_cast<__nv_bfloat16*>(pb + dt_op_off(h, t & 63)) = hi;        // column h
+                    *reinterpret_cast<__nv_bfloat16*>(pb + dt_op_off(g + h, t & 63)) = lo;    // column g + h
                 }
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             __syncwarp();
@@ -276,13 +293,14 @@ attn_decode_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_co
         // ---- output: TMEM lane = dim t of every head of the group
         mbar_wait(o_full, 0);
         fence_after();
-        uint32_t o[8];
-        dt_tmem_ld8(tmem_o + lane_addr, o);
+        uint32_t o[16];
+        if constexpr (kDtN == 16) dt_tmem_ld16(tmem_o + lane_addr, o);
+        else dt_tmem_ld8(tmem_o + lane_addr, o);
 #pragma unroll
         for (int h = 0; h < kDtMaxGroup; ++h)
             if (h < g) {
                 const float l = (red_sum[h] + red_sum[8 + h]) + (red_sum[16 + h] + red_sum[24 + h]);
-                const float v = __uint_as_float(o[h]) / l;
+                const float v = (__uint_as_float(o[h]) + __uint_as_float(o[g + h])) / l;
                 const size_t idx = ((size_t)m * p.n_heads + kvh * g + h) * kHeadDim + t;
                 p.out[idx] = v;
                 if (p.out_h != nullptr) p.out_h[idx] = __float2half_rn(v);
@@ -292,7 +310,7 @@ attn_decode_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_co
     __syncthreads();
     if (warp == 1) {
         fence_after();
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(32) : "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(64) : "memory");
     }
 }
 
@@ -302,6 +320,8 @@ int launch_attn_decode_tc(const AttnDecodeParams& p, int M, int max_keys, int64_
     if (g < 1 || g > kDtMaxGroup || p.n_heads % p.n_kv != 0 || p.page_size % 64 != 0 || max_keys < 1) return 1;
     DtParams dp;
     dp.a = p;
+    const int n_cols = 3 * g <= 8 ? 8 : 16;
+    dp.q_parts = 3 * g <= n_cols ? 3 : 2;   // 24 or 16 mantissa bits of q; the probabilities always travel as hi + lo (2 * g <= n_cols)
     dp.sc_stride = (max_keys + 1023) / 1024 * 1024;   // whole kilo-keys: a captured graph stays valid while the context grows inside its bucket
     const size_t fixed = 1024 + kDtPBytes + (size_t)g * dp.sc_stride * 4 + 512;
     int ns = 0;
@@ -326,16 +346,22 @@ int launch_attn_decode_tc(const AttnDecodeParams& p, int M, int max_keys, int64_
     if (pdl < 0) { const char* e = getenv("B200SHARD_PDL"); pdl = (e != nullptr && e[0] == '0') ? 0 : 1; }
     cfg.numAttrs = pdl;
     cudaError_t e;
-    if (ns == 3) {
-        cudaFuncSetAttribute(attn_decode_tc_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        e = cudaLaunchKernelEx(&cfg, attn_decode_tc_kernel<3>, mk, mv, dp);
-    } else if (ns == 6) {
-        cudaFuncSetAttribute(attn_decode_tc_kernel<6>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        e = cudaLaunchKernelEx(&cfg, attn_decode_tc_kernel<6>, mk, mv, dp);
-    } else {
-        cudaFuncSetAttribute(attn_decode_tc_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        e = cudaLaunchKernelEx(&cfg, attn_decode_tc_kernel<4>, mk, mv, dp);
+#define B200_DT_LAUNCH(KFN)                                                                        \
+    {                                                                                              \
+        auto kfn_ = KFN;                                                                           \
+        cudaFuncSetAttribute(kfn_, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);        \
+        e = cudaLaunchKernelEx(&cfg, kfn_, mk, mv, dp);                                            \
     }
+    if (n_cols == 8) {
+        if (ns == 3) B200_DT_LAUNCH((attn_decode_tc_kernel<3, 8>))
+        else if (ns == 6) B200_DT_LAUNCH((attn_decode_tc_kernel<6, 8>))
+        else B200_DT_LAUNCH((attn_decode_tc_kernel<4, 8>))
+    } else {
+        if (ns == 3) B200_DT_LAUNCH((attn_decode_tc_kernel<3, 16>))
+        else if (ns == 6) B200_DT_LAUNCH((attn_decode_tc_kernel<6, 16>))
+        else B200_DT_LAUNCH((attn_decode_tc_kernel<4, 16>))
+    }
+#undef B200_DT_LAUNCH
     return e == cudaSuccess ? 0 : -1;
 }
 
