@@ -71,7 +71,6 @@ struct b200_shard {
     __nv_bfloat16 *xn = nullptr, *qrot = nullptr, *qrot_lo = nullptr, *attn_b = nullptr, *act_b = nullptr;  // 16-bit staging (xn / attn_b / act_b hold fp16)
     float *q_f = nullptr, *attn_f = nullptr, *act_f = nullptr;  // GEMV path (<= 4 rows), fp32
     float *lastrow = nullptr, *logits = nullptr, *attn_part = nullptr;
-    unsigned int* gemm_sync = nullptr;  // CTA-pair GEMM split-K: one counter per output tile (zero between launches)
     float* sk_ws = nullptr;             // stream-K GEMM: partial-sum slots, one per SM
     unsigned int* sk_flags = nullptr;   // and their flags (zero between launches)
     __nv_bfloat16* lastrow_b = nullptr;
@@ -165,7 +164,6 @@ extern "C" B200_API int b200_shard_create(const b200_shard_config_t* c, int devi
     // partials for rows x splits <= 8 x 16 per head, followed by one arrival ticket per (row, head) for up to 32 rows
     const size_t part_floats = (size_t)kMaxGemvRows * c->n_heads * kMaxSplits * 130 + (size_t)kMaxStreamRows * c->n_heads;
     r |= dev_alloc(A, &s->attn_part, part_floats);
-    r |= dev_alloc(A, &s->gemm_sync, 1024);
     r |= dev_alloc(A, &s->sk_ws, gemm_streamk_ws_floats(s->num_sms));
     r |= dev_alloc(A, &s->sk_flags, (size_t)2 * s->num_sms + 8);
     r |= dev_alloc(A, &s->lastrow, (size_t)c->max_batch * H);
@@ -180,7 +178,6 @@ extern "C" B200_API int b200_shard_create(const b200_shard_config_t* c, int devi
     if (r != 0) { b200_shard_destroy(s); return B200_ENOMEM; }
     // arrival tickets of decode attention start at zero (the kernel re-zeroes them itself afterwards)
     CU_TRY(cudaMemset(s->attn_part, 0, part_floats * sizeof(float)));
-    CU_TRY(cudaMemset(s->gemm_sync, 0, 1024 * sizeof(unsigned int)));
     CU_TRY(cudaMemset(s->sk_flags, 0, ((size_t)2 * s->num_sms + 8) * sizeof(unsigned int)));
     *out = s;
     return 0;
@@ -562,7 +559,7 @@ static int enqueue_forward(b200_shard_t* s, b200_kv_t* kv, const SlotList& sl, c
                 launch_attn_prefill(ap, st);
             }
             GemmParams o{};
-            o.A = s->attn_b; o.W = L.wo; o.M = M; o.N = H; o.K = s->nq; o.out = s->x; o.epi = GEMM_RESID_F32; o.ab_f16 = 1; o.split_sync = s->gemm_sync;
+            o.A = s->attn_b; o.W = L.wo; o.M = M; o.N = H; o.K = s->nq; o.out = s->x; o.epi = GEMM_RESID_F32; o.ab_f16 = 1;
             if (launch_gemm(o, st) != 0) return fail(B200_ECUDA, "[ERROR] %s", gemm_error());
             launch_rmsnorm_bf16(s->x, L.norm2, c.rms_eps, M, H, s->xn, st, B200_DT_F16);
             GemmParams gu{};
@@ -570,7 +567,7 @@ static int enqueue_forward(b200_shard_t* s, b200_kv_t* kv, const SlotList& sl, c
             gu.ab_f16 = 1; gu.out_f16 = 1;
             if (launch_gemm(gu, st) != 0) return fail(B200_ECUDA, "[ERROR] %s", gemm_error());
             GemmParams d{};
-            d.A = s->act_b; d.W = L.wdown; d.M = M; d.N = H; d.K = I; d.out = s->x; d.epi = GEMM_RESID_F32; d.ab_f16 = 1; d.split_sync = s->gemm_sync;
+            d.A = s->act_b; d.W = L.wdown; d.M = M; d.N = H; d.K = I; d.out = s->x; d.epi = GEMM_RESID_F32; d.ab_f16 = 1;
             if (launch_gemm(d, st) != 0) return fail(B200_ECUDA, "[ERROR] %s", gemm_error());
             s->n_launch += 7;
         }

@@ -320,10 +320,6 @@ gemm_pair_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
     const int n_m = (p.M + 255) / 256, n_n = (p.N + kBlkN2 - 1) / kBlkN2;
     const int n_tiles = n_m * n_n;
     const int num_k = (p.K + kBlkK - 1) / kBlkK;
-    // split-K (RESID_F32 only): work item = (k part, tile), parts of one tile run on different pairs at the same time; the
-    // epilogues add into the output in part order (a per-tile counter), so the sum is the same bits on every run
-    const int n_split = (EPI == GEMM_RESID_F32 && p.split_k > 1) ? p.split_k : 1;
-    const int n_items = n_tiles * n_split;
     const uint32_t idesc = kIdescBase2 | (p.ab_f16 ? 0u : ((1u << 7) | (1u << 10)));
 
     if (warp == 0 && lane == 0) {
@@ -348,12 +344,10 @@ gemm_pair_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
             asm volatile("griddepcontrol.wait;" ::: "memory");   // A comes from the previous kernel (the prologue above overlapped its tail)
             asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
             uint32_t it = 0;
-            for (int w = pair_id; w < n_items; w += n_pairs) {
-                const int t = w % n_tiles, part = w / n_tiles;
-                const int kb0 = num_k * part / n_split, kb1 = num_k * (part + 1) / n_split;
+            for (int t = pair_id; t < n_tiles; t += n_pairs) {
                 const int m_row0 = (t % n_m) * 256 + (int)cta_rank * kBlkM;
                 const int n_row0 = (t / n_m) * kBlkN2 + (int)cta_rank * (kBlkN2 / 2);
-                for (int kb = kb0; kb < kb1; ++kb, ++it) {
+                for (int kb = 0; kb < num_k; ++kb, ++it) {
                     const uint32_t st = it % kStages, ph = (it / kStages) & 1u;
                     mbar_wait(empty0 + 8 * st, ph ^ 1u);
                     if (leader) mbar_expect_tx(full0 + 8 * st, 2 * kStageBytes2);
@@ -367,21 +361,19 @@ gemm_pair_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
     } else if (warp == 1) {
         if (leader && lane == 0) {  // ===== MMA issuer: one thread for the pair
             uint32_t it = 0, ti = 0;
-            for (int w = pair_id; w < n_items; w += n_pairs, ++ti) {
-                const int part = w / n_tiles;
-                const int kb0 = num_k * part / n_split, kb1 = num_k * (part + 1) / n_split;
+            for (int t = pair_id; t < n_tiles; t += n_pairs, ++ti) {
                 const uint32_t buf = ti & 1u;
                 mbar_wait(tempty0 + 8 * buf, ((ti >> 1) & 1u) ^ 1u);  // both CTAs' epilogues have drained this accumulator
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 const uint32_t acc = tmem_base + buf * kBlkN2;
-                for (int kb = kb0; kb < kb1; ++kb, ++it) {
+                for (int kb = 0; kb < num_k; ++kb, ++it) {
                     const uint32_t st = it % kStages, ph = (it / kStages) & 1u;
                     mbar_wait(full0 + 8 * st, ph);
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                     const uint32_t sa = base + st * kStageBytes2, sb = sa + kStageBytesA;
 #pragma unroll
                     for (int k = 0; k < kBlkK / 16; ++k)
-                        umma_f16_pair(acc, umma_desc(sa + k * 32), umma_desc(sb + k * 32), idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+                        umma_f16_pair(acc, umma_desc(sa + k * 32), umma_desc(sb + k * 32), idesc, (kb > 0 || k > 0) ? 1u : 0u);
                     umma_commit_pair(empty0 + 8 * st);
                 }
                 umma_commit_pair(tfull0 + 8 * buf);
@@ -391,36 +383,18 @@ gemm_pair_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
         asm volatile("griddepcontrol.wait;" ::: "memory");
         const int quad = warp & 3;
         uint32_t ti = 0;
-        for (int w = pair_id; w < n_items; w += n_pairs, ++ti) {
-            const int t = w % n_tiles, part = w / n_tiles;
+        for (int t = pair_id; t < n_tiles; t += n_pairs, ++ti) {
             const uint32_t buf = ti & 1u;
             const int m_row0 = (t % n_m) * 256 + (int)cta_rank * kBlkM, n_blk = t / n_m;
             mbar_wait(tfull0 + 8 * buf, (ti >> 1) & 1u);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            if (n_split > 1 && part > 0) {   // the earlier parts of this tile must have added their sums (8 epilogue warps each)
-                if (lane == 0) {
-                    const long long t0 = clock64();
-                    unsigned int seen;
-                    do {
-                        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(p.split_sync + t) : "memory");
-                        if (clock64() - t0 > (1ll << 31)) __trap();
-                    } while (seen < 8u * (unsigned int)part);
-                }
-                __syncwarp();
-            }
             const int row = m_row0 + quad * 32 + lane;
             const uint32_t trow = tmem_base + buf * kBlkN2 + ((uint32_t)(quad * 32) << 16);
 #pragma unroll 1
             for (int sub = 0; sub < 2; ++sub)
                 if ((n_blk * 2 + sub) * kBlkN < p.N) gemm_epilogue<EPI>(p, trow + sub * kBlkN, row, n_blk * 2 + sub);
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-            if (n_split > 1) __threadfence();
             __syncwarp();
-            if (n_split > 1 && lane == 0) {
-                unsigned int old;
-                asm volatile("atom.add.release.gpu.global.u32 %0, [%1], 1;" : "=r"(old) : "l"(p.split_sync + t) : "memory");
-                if (old + 1u == 8u * (unsigned int)n_split) p.split_sync[t] = 0u;   // last arrival of the tile: ready for the next launch
-            }
             if (lane == 0) mbar_arrive_leader(tempty0 + 8 * buf);  // this warp no longer reads accumulator `buf`
         }
     }
@@ -488,8 +462,7 @@ static void launch_pdl(K kfn, dim3 grid, size_t smem, cudaStream_t st, const CUt
     cudaLaunchKernelEx(&cfg, kfn, ma, mb, p);
 }
 
-int launch_gemm(const GemmParams& p_in, cudaStream_t st) {
-    GemmParams p = p_in;
+int launch_gemm(const GemmParams& p, cudaStream_t st) {
     if (p.K % 8 != 0 || p.N % 8 != 0 || p.M <= 0) {
         snprintf(g_gemm_err, sizeof(g_gemm_err), "gemm: need K%%8==0, N%%8==0, M>0 (M=%d N=%d K=%d)", p.M, p.N, p.K);
         return -1;
@@ -512,22 +485,11 @@ int launch_gemm(const GemmParams& p_in, cudaStream_t st) {
     }
     // CTA pairs (256 x 256 tiles, half the L2 -> shared-memory traffic per flop) once there are enough tiles to occupy
     // most SM pairs; small problems keep the finer 128 x 128 tiling (measured: profiles/gemm_bench_r1.md)
-    // Too few 256 x 256 tiles for the SM pairs (a 512-token prompt times a 4096-wide projection: 32): the residual-adding
-    // GEMMs split K over 2..4 work items per tile instead of falling back to the L2-bound 128 x 128 kernel.
-    const int64_t tiles2_all = (int64_t)((p.M + 255) / 256) * ((p.N + kBlkN2 - 1) / kBlkN2);
-    static int splitk_mode = -1;
-    if (splitk_mode < 0) { const char* e = getenv("B200SHARD_GEMM_SPLITK"); splitk_mode = (e != nullptr && e[0] == '0') ? 0 : 1; }
-    p.split_k = 1;
-    if (splitk_mode == 1 && p.epi == GEMM_RESID_F32 && p.split_sync != nullptr && p.M > kBlkM && tiles2_all < 64 && tiles2_all <= 1024) {
-        const int num_k = (p.K + kBlkK - 1) / kBlkK;
-        for (int sk = 2; sk <= 4; ++sk)
-            if (tiles2_all * sk >= 56 && num_k / sk >= 16) { p.split_k = sk; break; }
-    }
-    if (pair_mode == 1 && p.M > kBlkM && tiles2_all * p.split_k >= (p.split_k > 1 ? 56 : 64)) {
+    if (pair_mode == 1 && p.M > kBlkM && (int64_t)((p.M + 255) / 256) * ((p.N + kBlkN2 - 1) / kBlkN2) >= 64) {
         int n_sms = 148, dev = 0;
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, dev);
-        const int64_t tiles2 = tiles2_all * p.split_k;
+        const int64_t tiles2 = (int64_t)((p.M + 255) / 256) * ((p.N + kBlkN2 - 1) / kBlkN2);
         const int pairs = (int)(tiles2 < n_sms / 2 ? tiles2 : n_sms / 2);
         dim3 grid2(2 * pairs);
         const size_t smem2 = 1024 + (size_t)kStages * kStageBytes2 + 256;

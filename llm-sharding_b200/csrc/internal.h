@@ -178,10 +178,6 @@ struct GemmParams {
     const float* sin = nullptr;
     int n_heads = 0, n_kv = 0;
     int64_t head_stride = 0;
-    // CTA-pair kernel, RESID_F32 only: split the K range of every tile over `split_k` work items when the tiles alone do
-    // not occupy the SM pairs (M = 512 prompts); `split_sync` = one zeroed counter per tile ordering the read-modify-writes
-    int split_k = 1;
-    unsigned int* split_sync = nullptr;
 };
 // returns cudaError-like int (0 ok); message via get_gemm_error()
 int launch_gemm(const GemmParams& p, cudaStream_t st);
