@@ -452,15 +452,23 @@ static int enqueue_forward(b200_shard_t* s, b200_kv_t* kv, const SlotList& sl, c
     const b200_shard_config_t& c = s->cfg;
     const int M = B * S, H = c.hidden_size, I = c.intermediate_size;
     const int64_t head_stride = (int64_t)kv->dev.page_size * 128;
-    if (tok_in != nullptr) {  // entry == head node: embed_tokens (utils/node_worker.py:215,302) straight into the workspace
-        launch_embed(s->embedding, tok_in, M, H, c.vocab_size, s->xn, B200_DT_BF16, st);
+    static int fused_prologue = -1;   // B200SHARD_FUSED_PROLOGUE=0: the four separate launches (A/B)
+    if (fused_prologue < 0) { const char* e = getenv("B200SHARD_FUSED_PROLOGUE"); fused_prologue = (e != nullptr && e[0] == '0') ? 0 : 1; }
+    if (fused_prologue == 1 && S == 1 && B <= kMaxGemvRows && H % 8 == 0) {
+        launch_decode_prologue(kv->dev, sl, B, causal, s->inv, c.n_kv_heads, s->tm, in, s->io_dtype, tok_in, s->embedding, c.vocab_size,
+                               H, s->x, st);
         s->n_launch += 1;
-        in = s->xn;
+    } else {
+        if (tok_in != nullptr) {  // entry == head node: embed_tokens (utils/node_worker.py:215,302) straight into the workspace
+            launch_embed(s->embedding, tok_in, M, H, c.vocab_size, s->xn, B200_DT_BF16, st);
+            s->n_launch += 1;
+            in = s->xn;
+        }
+        launch_kv_alloc(kv->dev, sl, B, S, s->tm.call_base, st);
+        launch_prep(kv->dev, sl, B, S, causal, s->inv, c.n_kv_heads, s->tm, st);
+        launch_load_residual(in, tok_in != nullptr ? B200_DT_BF16 : s->io_dtype, s->x, (int64_t)M * H, st);
+        s->n_launch += 3;
     }
-    launch_kv_alloc(kv->dev, sl, B, S, s->tm.call_base, st);
-    launch_prep(kv->dev, sl, B, S, causal, s->inv, c.n_kv_heads, s->tm, st);
-    launch_load_residual(in, tok_in != nullptr ? B200_DT_BF16 : s->io_dtype, s->x, (int64_t)M * H, st);
-    s->n_launch += 3;
     const bool gemv_path = M <= gemv_row_limit(s);
     int max_keys = 0;   // longest context any row of this call attends to (the host mirrors the device lengths)
     for (int b = 0; b < B; ++b) max_keys = kv->h_len[sl.v[b]] + S > max_keys ? kv->h_len[sl.v[b]] + S : max_keys;

@@ -65,6 +65,10 @@ void launch_prep(const KvDev& kv, const SlotList& slots, int B, int S, int causa
 
 // `in` in any message dtype (B200_DT_* code) -> fp32 residual stream
 void launch_load_residual(const void* in, int dtype, float* x, int64_t n, cudaStream_t st);
+// kv_alloc + prep + (embedding gather | load_residual) of a single-token call for a few rows, one launch
+void launch_decode_prologue(const KvDev& kv, const SlotList& slots, int B, int causal, const InvFreq& inv, int n_kv, const TokMeta& tm,
+                            const void* in, int in_dtype, const int64_t* tok_in, const __nv_bfloat16* table, int V, int H, float* x,
+                            cudaStream_t st);
 // x fp32 [rows,n] -> out_dtype (B200_DT_* code: 0 bf16, 1 fp32, 2 fp16 saturating); norm_w == nullptr: plain convert
 void launch_rmsnorm_bf16(const float* x, const __nv_bfloat16* norm_w, float eps, int rows, int n,
                          void* out, cudaStream_t st, int out_dtype = 0);

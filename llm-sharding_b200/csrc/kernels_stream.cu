@@ -108,6 +108,75 @@ __device__ __forceinline__ float load_as_float(const void* src, int dtype, int64
     if (dtype == 1) return reinterpret_cast<const float*>(src)[i];
     return __half2float(reinterpret_cast<const __half*>(src)[i]);
 }
+// Everything that precedes the first layer of a single-token call for a few rows, in ONE launch instead of four: page
+// hand-out (kv_alloc_kernel), positions / RoPE table / page addresses (prep_kernel), and the fp32 residual stream either
+// from the incoming hidden state (load_residual) or straight from the embedding table (embed_tokens,
+// utils/node_worker.py:302).  One CTA: thread 0 hands out the pages, the barrier publishes call_base to the rest.
+__global__ void __launch_bounds__(1024) decode_prologue_kernel(KvDev kv, SlotList slots, int B, int causal, InvFreq inv, int n_kv,
+                                                               TokMeta tm, const void* __restrict__ in, int in_dtype,
+                                                               const int64_t* __restrict__ tok_in,
+                                                               const __nv_bfloat16* __restrict__ table, int V, int H,
+                                                               float* __restrict__ x) {
+    if (threadIdx.x == 0) {
+        int top = *kv.free_top;
+        for (int b = 0; b < B; ++b) {
+            const int slot = slots.v[b];
+            const int base = kv.seq_lens[slot];
+            tm.call_base[b] = base;
+            const int need = (base + 1 + kv.page_size - 1) / kv.page_size;
+            int held = kv.pages_held[slot];
+            if (need > kv.max_pages_per_slot) { *kv.error = 2; continue; }
+            while (held < need) {
+                if (top <= 0) { *kv.error = 1; break; }
+                kv.block_table[slot * kv.max_pages_per_slot + held] = kv.free_stack[--top];
+                ++held;
+            }
+            kv.pages_held[slot] = held;
+            kv.seq_lens[slot] = base + 1;
+        }
+        *kv.free_top = top;
+    }
+    __syncthreads();
+    for (int idx = threadIdx.x; idx < B * kHalfDim; idx += blockDim.x) {   // prep_kernel for S == 1
+        const int m = idx / kHalfDim, j = idx % kHalfDim;
+        const int pos = tm.call_base[m];
+        float sn, cs;
+        sincosf((float)pos * inv.v[j], &sn, &cs);
+        tm.cos[(size_t)m * kHalfDim + j] = cs;
+        tm.sin[(size_t)m * kHalfDim + j] = sn;
+        if (j == 0) {
+            const int page = kv.block_table[slots.v[m] * kv.max_pages_per_slot + pos / kv.page_size];
+            tm.pos[m] = pos;
+            tm.t_end[m] = pos + 1;   // causal or not: a single new token sees every cached key and itself
+            tm.kv_off[m] = ((int64_t)page * n_kv * kv.page_size + (pos % kv.page_size)) * kHeadDim;
+        }
+    }
+    (void)causal;
+    const int n8 = B * H / 8;
+    for (int i = threadIdx.x; i < n8; i += blockDim.x) {
+        float v[8];
+        if (tok_in != nullptr) {
+            const int m = (i * 8) / H, c = (i * 8) % H;
+            int64_t id = tok_in[m];
+            id = id < 0 ? 0 : (id >= V ? V - 1 : id);
+            const uint4 w = *reinterpret_cast<const uint4*>(table + (size_t)id * H + c);
+            v[0] = bf_lo(w.x); v[1] = bf_hi(w.x); v[2] = bf_lo(w.y); v[3] = bf_hi(w.y);
+            v[4] = bf_lo(w.z); v[5] = bf_hi(w.z); v[6] = bf_lo(w.w); v[7] = bf_hi(w.w);
+        } else {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) v[e] = load_as_float(in, in_dtype, (int64_t)i * 8 + e);
+        }
+        float4* o = reinterpret_cast<float4*>(x) + 2 * i;
+        o[0] = make_float4(v[0], v[1], v[2], v[3]);
+        o[1] = make_float4(v[4], v[5], v[6], v[7]);
+    }
+}
+void launch_decode_prologue(const KvDev& kv, const SlotList& slots, int B, int causal, const InvFreq& inv, int n_kv, const TokMeta& tm,
+                            const void* in, int in_dtype, const int64_t* tok_in, const __nv_bfloat16* table, int V, int H, float* x,
+                            cudaStream_t st) {
+    decode_prologue_kernel<<<1, 1024, 0, st>>>(kv, slots, B, causal, inv, n_kv, tm, in, in_dtype, tok_in, table, V, H, x);
+}
+
 __global__ void load_residual_kernel(const __nv_bfloat16* __restrict__ in, float* __restrict__ x, int64_t n8) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
