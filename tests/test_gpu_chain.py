@@ -401,3 +401,83 @@ def test_two_node_controllers_on_two_gpus_over_p2p_communicator(tmp_path):
     assert got[0][0] == [int(t) for t in z["tokens"][:, 0]]
     assert got[0][2] == 0 and got[1][2] == 0
     assert got[0][1] >= meta["new_tokens"] and got[1][1] >= meta["new_tokens"]
+
+
+def _server_stage_proc(rank, world, port, shard_dir, reqs, eos, q):
+    import torch.distributed as dist
+    from llm_sharding_b200.chain import ChainStage, LoopbackCommunicator, RingServer, layer_range
+    from llm_sharding_b200.node_worker import NodeWorker
+    from oracle import synth
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        cfg = synth.PRESETS["tiny"]
+        s, e = layer_range(rank, world, cfg.num_hidden_layers)
+        src, dst = f"tcp://*:{47400 + rank}", f"tcp://127.0.0.1:{47400 + (rank + 1) % world}"
+        w = NodeWorker(src, dst, rank == 0, shard_dir, device=f"cuda:{rank}", dtype=torch.bfloat16,
+                       communicator=LoopbackCommunicator(src, dst), max_tokens=64, max_batch=1, max_slots=2)
+        w.load_shards(s, e)
+        stage = ChainStage(w, rank, world, 2, 64, ctrl_group=None, transport="p2p", max_wait_us=20_000_000)
+        srv = RingServer(stage, dist.group.WORLD, eos_token_id=eos)
+        rids = [srv.submit(ids, n) for ids, n in reqs] if rank == 0 else []
+        out = srv.serve()
+        torch.cuda.synchronize()
+        dist.barrier()
+        if rank == 0:
+            q.put(([out[r][:, 0].tolist() for r in rids], stage.error()))
+        kv_clear = all(w.past_key_value.get_seq_length(i) == 0 for i in range(2))
+        assert kv_clear
+        dist.barrier()
+        stage.close()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_ring_server_on_two_gpus_applies_stop_rules_per_stream(tmp_path):
+    """The generalised run_worker_loop across two GPUs: three requests, two streams, per-request budgets and an EOS id;
+    the head's per-round plan reaches the tail over gloo, hidden states and tokens cross NVLink; every request must yield
+    what it yields alone through the reference-shaped loop, cut by the reference's stop rule."""
+    import torch.multiprocessing as mp
+    from gpu_utils import build_chain, close_chain, shard_dir
+    from llm_sharding_b200.chain import generate
+    from oracle import synth
+    cfg = synth.PRESETS["tiny"]
+    d = shard_dir(str(tmp_path), "tiny", 28)
+    reqs = [(synth.prompt_ids(cfg, 930, 1, 17), 5), (synth.prompt_ids(cfg, 931, 1, 40), 2), (synth.prompt_ids(cfg, 932, 1, 8), 6)]
+    alone = []
+    workers = build_chain(str(tmp_path), "tiny", 28, [(0, 2), (2, 4)], max_tokens=64)
+    try:
+        for ids, n in reqs:
+            for w in workers:
+                w.clear_KV_cache()
+            toks, _ = generate(workers, ids, 6)
+            alone.append([int(t) for t in toks[:, 0]])
+    finally:
+        close_chain(workers)
+    eos = alone[2][3]
+
+    def ruled(tokens, budget):
+        out = []
+        for t in tokens[:budget]:
+            out.append(t)
+            if t == eos:
+                break
+        return out
+    expected = [ruled(alone[i], reqs[i][1]) for i in range(3)]
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_server_stage_proc, args=(r, 2, port, d, reqs, eos, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(180)
+    hung = [p for p in procs if p.is_alive()]
+    for p in hung:
+        p.terminate()
+    assert not hung and all(p.exitcode == 0 for p in procs)
+    got, err = q.get(timeout=10)
+    assert err == 0
+    assert got == expected
