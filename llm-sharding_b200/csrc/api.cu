@@ -78,6 +78,7 @@ struct b200_shard {
     InvFreq inv{};
     uint64_t n_launch = 0, n_bytes = 0, n_flops = 0, n_calls = 0;
     bool graphs = false;
+    bool tail_xw_ready = false;   // set by enqueue_forward when the last layer wrote the lm_head operand (folded final norm)
     int io_dtype = B200_DT_BF16;  // element type of hidden states crossing the ABI (the node's dtype, utils/node_worker.py:252)
     std::map<GraphKey, GraphEntry> graph_cache;
     uint64_t graph_clock = 0;
@@ -445,6 +446,12 @@ static int check_call(b200_shard_t* s, b200_kv_t* kv, const int32_t* h_slots, co
     return 0;
 }
 
+// Batched single-token tail (4..16 rows): the last down_proj writes x * w_final as the fp16 operand of lm_head and the
+// lm_head GEMM applies 1 / rms in its epilogue — no separate final-norm or cast launch (same fold as between the layers).
+static bool tail_fold(const b200_shard* s, int B, int S, bool stream_path) {
+    return stream_path && S == 1 && B <= 16 && s->cfg.has_final_norm && s->final_norm != nullptr && s->cfg.hidden_size % 64 == 0;
+}
+
 // enqueue every kernel of one forward (+ optional tail); no host synchronisation
 static int enqueue_forward(b200_shard_t* s, b200_kv_t* kv, const SlotList& sl, const void* in, const int64_t* tok_in,
                            int B, int S, int causal, void* out, int64_t* tok, float* margin, bool with_tail,
@@ -470,6 +477,7 @@ static int enqueue_forward(b200_shard_t* s, b200_kv_t* kv, const SlotList& sl, c
         s->n_launch += 3;
     }
     const bool gemv_path = M <= gemv_row_limit(s);
+    s->tail_xw_ready = false;
     int max_keys = 0;   // longest context any row of this call attends to (the host mirrors the device lengths)
     for (int b = 0; b < B; ++b) max_keys = kv->h_len[sl.v[b]] + S > max_keys ? kv->h_len[sl.v[b]] + S : max_keys;
     const bool stream_path = !gemv_path && M <= kMaxStreamRows && stream_gemm_enabled() && H % 64 == 0 && I % 64 == 0 &&
@@ -543,6 +551,10 @@ static int enqueue_forward(b200_shard_t* s, b200_kv_t* kv, const SlotList& sl, c
             StreamGemmParams d{};
             d.W = L.wdown; d.X = s->act_b; d.M = M; d.N = H; d.K = I; d.out = s->x; d.ws = s->sk_ws; d.ws_flags = s->sk_flags;
             if (fold && l + 1 < c.n_layers) { d.next_norm_w = s->layers[l + 1].norm1; d.xw_out = reinterpret_cast<__half*>(s->xn); }
+            else if (with_tail && tail_fold(s, B, S, true)) {
+                d.next_norm_w = s->final_norm; d.xw_out = reinterpret_cast<__half*>(s->xn);
+                s->tail_xw_ready = true;
+            }
             if (launch_gemm_stream(d, EPI_RESID, s->num_sms, st) != 0) return fail(B200_ECUDA, "[ERROR] %s", gemm_stream_last_error());
             s->n_launch += fold ? 5 + (l == 0 ? 1 : 0) : 7;
         } else {
@@ -584,7 +596,7 @@ static int enqueue_forward(b200_shard_t* s, b200_kv_t* kv, const SlotList& sl, c
         launch_rmsnorm_bf16(s->x, c.has_final_norm ? s->final_norm : nullptr, c.rms_eps, M, H, out, st, s->io_dtype);
         s->n_launch += 1;
     }
-    if (with_tail && B > gemv_row_limit(s)) {  // batched tail goes through the GEMM; small batches fuse the norm into the GEMV
+    if (with_tail && B > gemv_row_limit(s) && !s->tail_xw_ready) {  // batched tail goes through the GEMM; small batches fuse the norm into the GEMV
         launch_lastrow_norm_f32(s->x, c.has_final_norm ? s->final_norm : nullptr, c.rms_eps, B, S, H, s->lastrow, st);
         s->n_launch += 1;
     }
@@ -606,6 +618,11 @@ static int enqueue_tail(b200_shard_t* s, int B, int S, bool from_residual, int64
             g.x = s->lastrow;
             launch_gemv(g, B, EPI_STORE, false, s->num_sms, st);
         }
+    } else if (from_residual && s->tail_xw_ready) {   // the last down_proj of this very call left x * w_final in s->xn
+        StreamGemmParams g{};
+        g.W = s->lm_head; g.X = s->xn; g.M = B; g.N = c.vocab_size; g.K = c.hidden_size; g.out = s->logits; g.ws = s->sk_ws; g.ws_flags = s->sk_flags;
+        g.x_res = s->x; g.eps = c.rms_eps;
+        if (launch_gemm_stream(g, EPI_STORE, s->num_sms, st) != 0) return fail(B200_ECUDA, "[ERROR] %s", gemm_stream_last_error());
     } else {
         launch_rmsnorm_bf16(s->lastrow, nullptr, 0.f, B, c.hidden_size, s->lastrow_b, st, B200_DT_F16);
         if (B <= kMaxStreamRows && stream_gemm_enabled() && c.hidden_size % 64 == 0) {

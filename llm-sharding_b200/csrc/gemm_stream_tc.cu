@@ -133,7 +133,7 @@ gemm_stream_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_co
         asm volatile("griddepcontrol.wait;" ::: "memory");
         const int quad = warp & 3;
         const int t = quad * 32 + lane;                  // weight row inside the tile = TMEM lane
-        if ((EPI == EPI_QKV || EPI == EPI_SWIGLU) && p.x_res != nullptr) {
+        if ((EPI == EPI_QKV || EPI == EPI_SWIGLU || EPI == EPI_STORE) && p.x_res != nullptr) {
             // folded RMSNorm: while the MMAs run, every CTA recomputes the row statistics from the fp32 residual stream (same
             // loads, same order in every CTA: identical bits everywhere); one warp per token row, xor-shuffle reduction
             for (int m = quad; m < p.M; m += 4) {
@@ -196,7 +196,7 @@ gemm_stream_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_co
             a += red[((s * 2 + 0) * MP + m) * P + jl];
             b += red[((s * 2 + 1) * MP + m) * P + jl];
         }
-        if ((EPI == EPI_QKV || EPI == EPI_SWIGLU) && p.x_res != nullptr) { a *= rstd_s[m]; b *= rstd_s[m]; }
+        if ((EPI == EPI_QKV || EPI == EPI_SWIGLU || EPI == EPI_STORE) && p.x_res != nullptr) { a *= rstd_s[m]; b *= rstd_s[m]; }
         const int jj = (int)rank * P + jl;               // 0..63 inside the tile
         const int row0 = tile * kSwRows + jj, row1 = row0 + 64;
         if (EPI == EPI_STORE || EPI == EPI_RESID) {

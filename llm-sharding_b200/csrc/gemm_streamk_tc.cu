@@ -163,7 +163,7 @@ gemm_streamk_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
         const int quad = warp & 3;
         const int t = quad * 32 + lane;
         const int j = t & 63, half = t >> 6;
-        if ((EPI == EPI_QKV || EPI == EPI_SWIGLU) && p.x_res != nullptr) {   // folded RMSNorm, see gemm_stream_tc.cu
+        if ((EPI == EPI_QKV || EPI == EPI_SWIGLU || EPI == EPI_STORE) && p.x_res != nullptr) {   // folded RMSNorm, see gemm_stream_tc.cu
             for (int m = quad; m < p.M; m += 4) {
                 const float4* xr = reinterpret_cast<const float4*>(p.x_res + (size_t)m * p.K);
                 float ss = 0.f;
@@ -243,7 +243,7 @@ gemm_streamk_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
             for (int e = t; e < 64 * p.M; e += 128) {
                 const int jj = e & 63, m = e >> 6;
                 float a = red[(0 * MP + m) * 64 + jj], b = red[(1 * MP + m) * 64 + jj];
-                if ((EPI == EPI_QKV || EPI == EPI_SWIGLU) && p.x_res != nullptr) { a *= rstd_s[m]; b *= rstd_s[m]; }
+                if ((EPI == EPI_QKV || EPI == EPI_SWIGLU || EPI == EPI_STORE) && p.x_res != nullptr) { a *= rstd_s[m]; b *= rstd_s[m]; }
                 const int row0 = tile * kSkRows + jj, row1 = row0 + 64;
                 if (EPI == EPI_STORE || EPI == EPI_RESID) {
                     if (row0 < p.N) {
