@@ -160,6 +160,21 @@ def test_attn_decode_tensor_core(lib, rows, n_heads, n_kv, T_list):
     assert rel_l2(out, ref) < (1e-5 if max(T_list) <= 4096 else 4e-5)
 
 
+def test_attn_decode_tensor_core_rejects_what_it_does_not_serve(lib):
+    from llm_sharding_b200 import _lib
+    g = torch.Generator(device="cuda").manual_seed(1)
+    k_pool, v_pool, bt, dense, max_pages = _paged_kv(1, 1, [70], 64, g, fill=0.0)
+    q = torch.randn(1, 16 * 128, device="cuda", generator=g)
+    t_end = torch.tensor([70], dtype=torch.int32, device="cuda")
+    out = torch.zeros_like(q)
+    with pytest.raises(ValueError):   # 16 query heads on one K/V head: more than the narrow operand holds
+        _lib.check(lib.b200_attn_decode_tc(q.data_ptr(), k_pool.data_ptr(), v_pool.data_ptr(), bt.data_ptr(), t_end.data_ptr(), 1,
+                                           16, 1, 64, max_pages, k_pool.shape[0], 70, out.data_ptr(), _st()))
+    with pytest.raises(ValueError):   # page size must be a multiple of 64
+        _lib.check(lib.b200_attn_decode_tc(q.data_ptr(), k_pool.data_ptr(), v_pool.data_ptr(), bt.data_ptr(), t_end.data_ptr(), 1,
+                                           16, 16, 48, max_pages, k_pool.shape[0], 70, out.data_ptr(), _st()))
+
+
 @pytest.mark.parametrize("M,N,K", [(128, 128, 64), (200, 384, 512), (512, 4096, 4096), (77, 4096, 11008)])
 def test_gemm_tcgen05_fp16_operands(lib, M, N, K):
     from llm_sharding_b200 import _lib

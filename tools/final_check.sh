@@ -9,4 +9,4 @@ timeout 200 python tools/prefill_bench.py > gpurun_out/prefill_noncausal.txt 2>&
 timeout 200 python tools/prefill_bench.py --causal 1 > gpurun_out/prefill_causal.txt 2>&1; tail -4 gpurun_out/prefill_causal.txt
 timeout 200 python tools/kernel_bench.py > gpurun_out/kernel_bench.txt 2>&1; grep rows= gpurun_out/kernel_bench.txt
 K='regex:gemv|attn|gemm|rmsnorm|argmax|embed|prep_kernel|kv_alloc|load_residual|lastrow|convert'
-timeout 500 ncu --metrics gpu__time_duration.sum --clock-control none -k "$K" --launch-skip 2000 -c 1500 --csv --log-file gpurun_out/launches_r1_ncu_v3.csv python bench.py --steps 2 --warmup 1 --no-cpu-baseline > gpurun_out/ncu_run.log 2>&1; echo "ncu rc=$?"
+timeout 500 ncu --metrics gpu__time_duration.sum --clock-control none -k "$K" --launch-skip 2000 -c 1500 --csv --log-file gpurun_out/launches_r2_ncu.csv python bench.py --steps 2 --warmup 1 --no-cpu-baseline > gpurun_out/ncu_run.log 2>&1; echo "ncu rc=$?"
