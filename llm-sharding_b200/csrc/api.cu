@@ -411,7 +411,7 @@ static int gemv_row_limit(const b200_shard* s) {
     if (cap < 0) {
         const char* e = getenv("B200SHARD_GEMV_ROWS");
         cap = e ? atoi(e) : kGemvRowsDefault;
-        if (cap < 1 || cap > kMaxGemvRows) cap = kGemvRowsDefault;
+        if (cap < 0 || cap > kMaxGemvRows) cap = kGemvRowsDefault;   // 0: even a single row takes the tensor-core streaming GEMM (experiment)
     }
     int lim = cap;
     while (lim > 0 && gemv_smem_bytes(lim, kmax) > 220 * 1024) --lim;
