@@ -27,23 +27,6 @@ constexpr int kGemvWarps = kGemvThreads / 32;
 constexpr int kR = 4;  // weight rows per group
 
 __device__ __forceinline__ float2 unpack2(uint32_t v) { return __half22float2(*reinterpret_cast<const __half2*>(&v)); }
-// Blackwell's packed fp32 pipe: one instruction = two independent fp32 FMAs with scalar rounding.  The dot product keeps an
-// (even, odd) accumulator pair per row: half the FMA issue slots of the scalar chain, and less power per byte streamed.
-__device__ __forceinline__ uint64_t pk2(float lo, float hi) {
-    uint64_t r;
-    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
-    return r;
-}
-__device__ __forceinline__ uint64_t fma2(uint64_t a, uint64_t b, uint64_t c) {
-    uint64_t d;
-    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
-    return d;
-}
-__device__ __forceinline__ float sum2(uint64_t v) {
-    float lo, hi;
-    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
-    return lo + hi;
-}
 
 // shared-memory layout of an activation row: the two float4 halves of chunk c = j*512 + t live at float4 index
 // (j*2 + half)*512 + t, so that the CTA's reads of one step are contiguous (no bank conflicts)
@@ -130,11 +113,11 @@ __global__ void __launch_bounds__(kGemvThreads, (M <= 2 ? 2 : 1)) gemv_kernel(co
 
     const float4* xs4 = reinterpret_cast<const float4*>(xs);
     const int m_stride4 = Kpad >> 2;
-    uint64_t acc[kR][M];   // (even, odd) fp32 pair per row and token
+    float acc[kR][M];
 #pragma unroll
     for (int r = 0; r < kR; ++r)
 #pragma unroll
-        for (int m = 0; m < M; ++m) acc[r][m] = 0ull;
+        for (int m = 0; m < M; ++m) acc[r][m] = 0.f;
 
     int g = 0, j = 0, buf = 0;
     for (int step = 0; step < total_steps; ++step) {
@@ -146,16 +129,15 @@ __global__ void __launch_bounds__(kGemvThreads, (M <= 2 ? 2 : 1)) gemv_kernel(co
         for (int m = 0; m < M; ++m) {
             const float4 xl = xs4[m * m_stride4 + i4];
             const float4 xh = xs4[m * m_stride4 + i4 + kGemvThreads];
-            const uint64_t x0 = pk2(xl.x, xl.y), x1 = pk2(xl.z, xl.w), x2 = pk2(xh.x, xh.y), x3 = pk2(xh.z, xh.w);
 #pragma unroll
             for (int r = 0; r < kR; ++r) {
                 const uint4 ww = wc[r];
                 const float2 w0 = unpack2(ww.x), w1 = unpack2(ww.y), w2 = unpack2(ww.z), w3 = unpack2(ww.w);
-                uint64_t a = acc[r][m];
-                a = fma2(pk2(w0.x, w0.y), x0, a);
-                a = fma2(pk2(w1.x, w1.y), x1, a);
-                a = fma2(pk2(w2.x, w2.y), x2, a);
-                a = fma2(pk2(w3.x, w3.y), x3, a);
+                float a = acc[r][m];
+                a = fmaf(w0.x, xl.x, a); a = fmaf(w0.y, xl.y, a);
+                a = fmaf(w1.x, xl.z, a); a = fmaf(w1.y, xl.w, a);
+                a = fmaf(w2.x, xh.x, a); a = fmaf(w2.y, xh.y, a);
+                a = fmaf(w3.x, xh.z, a); a = fmaf(w3.y, xh.w, a);
                 acc[r][m] = a;
             }
         }
@@ -165,9 +147,9 @@ __global__ void __launch_bounds__(kGemvThreads, (M <= 2 ? 2 : 1)) gemv_kernel(co
             for (int r = 0; r < kR; ++r)
 #pragma unroll
                 for (int m = 0; m < M; ++m) {
-                    const float v = warp_sum(sum2(acc[r][m]));
+                    const float v = warp_sum(acc[r][m]);
                     if (lane == 0) pb[warp * kR * M + r * M + m] = v;
-                    acc[r][m] = 0ull;
+                    acc[r][m] = 0.f;
                 }
             __syncthreads();  // one barrier per group; `part` is double buffered so fast warps may run ahead
             if (PAIRED) {
