@@ -60,6 +60,7 @@ struct GraphEntry {
 };
 constexpr size_t kMaxCachedGraphs = 64;  // least-recently-used graphs beyond this are destroyed (callers that pass fresh pointers every step)
 
+constexpr int kRowSsParts = 512;   // most CTAs a residual-producing streaming GEMM launches (per-CTA partial sums of squares per token row)
 struct b200_shard {
     b200_shard_config_t cfg;
     int device = 0, num_sms = 148;
@@ -73,11 +74,13 @@ struct b200_shard {
     float *lastrow = nullptr, *logits = nullptr, *attn_part = nullptr;
     float* sk_ws = nullptr;             // stream-K GEMM: partial-sum slots, one per SM
     unsigned int* sk_flags = nullptr;   // and their flags (zero between launches)
+    float* row_ss = nullptr;            // folded RMSNorm: two buffers of [kMaxStreamRows][kRowSsParts] partial sums of squares
     __nv_bfloat16* lastrow_b = nullptr;
     TokMeta tm{};
     InvFreq inv{};
     uint64_t n_launch = 0, n_bytes = 0, n_flops = 0, n_calls = 0;
     bool graphs = false;
+    int tail_ss_parts = 0;        // > 0: that down_proj also left the rows' partial sums of squares in row_ss (buffer A)
     bool tail_xw_ready = false;   // set by enqueue_forward when the last layer wrote the lm_head operand (folded final norm)
     int io_dtype = B200_DT_BF16;  // element type of hidden states crossing the ABI (the node's dtype, utils/node_worker.py:252)
     std::map<GraphKey, GraphEntry> graph_cache;
@@ -167,6 +170,7 @@ extern "C" B200_API int b200_shard_create(const b200_shard_config_t* c, int devi
     r |= dev_alloc(A, &s->attn_part, part_floats);
     r |= dev_alloc(A, &s->sk_ws, gemm_streamk_ws_floats(s->num_sms));
     r |= dev_alloc(A, &s->sk_flags, (size_t)2 * s->num_sms + 8);
+    r |= dev_alloc(A, &s->row_ss, (size_t)2 * kMaxStreamRows * kRowSsParts);
     r |= dev_alloc(A, &s->lastrow, (size_t)c->max_batch * H);
     r |= dev_alloc(A, &s->lastrow_b, (size_t)c->max_batch * H);
     r |= dev_alloc(A, &s->logits, (size_t)c->max_batch * V);
@@ -446,10 +450,25 @@ static int check_call(b200_shard_t* s, b200_kv_t* kv, const int32_t* h_slots, co
     return 0;
 }
 
-// Batched single-token tail (4..16 rows): the last down_proj writes x * w_final as the fp16 operand of lm_head and the
-// lm_head GEMM applies 1 / rms in its epilogue — no separate final-norm or cast launch (same fold as between the layers).
+// RMSNorm folded into the streaming GEMMs: up to B200SHARD_FOLD_ROWS rows (default: all 32 of the path).  The consumer's
+// row statistics either come from re-reading the residual block in every consuming CTA, or as per-CTA partial sums of
+// squares left by the producer (row_ss).  B200SHARD_ROW_SS: 0 never, 1 from 17 rows (default: below that the re-read hides
+// behind the weight stream and the partials cost 0.3-0.5 us per layer), 2 always.
+static int row_ss_mode() {
+    static int v = -1;
+    if (v < 0) { const char* e = getenv("B200SHARD_ROW_SS"); v = e != nullptr ? atoi(e) : 1; }
+    return gemm_streamk_active() ? 0 : v;
+}
+static bool row_ss_for(int M) { return row_ss_mode() == 2 || (row_ss_mode() == 1 && M > 16); }
+static int fold_row_limit() {
+    static int v = -1;
+    if (v < 0) { const char* e = getenv("B200SHARD_FOLD_ROWS"); v = e != nullptr ? atoi(e) : kMaxStreamRows; }
+    return row_ss_mode() == 0 && v > 16 ? 16 : v;   // without the partials, folding beyond 16 rows is a net loss (136 -> 138 us)
+}
+// Batched single-token tail: the last down_proj writes x * w_final as the fp16 operand of lm_head and the lm_head GEMM
+// applies 1 / rms in its epilogue — no separate final-norm or cast launch (same fold as between the layers).
 static bool tail_fold(const b200_shard* s, int B, int S, bool stream_path) {
-    return stream_path && S == 1 && B <= 16 && s->cfg.has_final_norm && s->final_norm != nullptr && s->cfg.hidden_size % 64 == 0;
+    return stream_path && S == 1 && B <= fold_row_limit() && s->cfg.has_final_norm && s->final_norm != nullptr && s->cfg.hidden_size % 64 == 0;
 }
 
 // enqueue every kernel of one forward (+ optional tail); no host synchronisation
@@ -518,14 +537,20 @@ static int enqueue_forward(b200_shard_t* s, b200_kv_t* kv, const SlotList& sl, c
             // first norm of the call has no producer and runs as its own (un-normalised: weight only) pass.
             // Every consuming CTA re-reads the M x H residual block for the statistics: free up to 16 rows (138 -> 111 us per
             // layer at 16, 100 -> 89 at 4), a net loss at 32 (136 -> 138), where the two separate norm passes stay.
-            const bool fold = M <= 16;
+            const bool fold = M <= fold_row_limit();
+            // partial sums of squares: buffer A travels down_proj (or the scale pass) -> QKV / lm_head, buffer B o_proj -> gate/up
+            const int parts_o = gemm_stream_parts(H, s->nq, s->num_sms), parts_d = gemm_stream_parts(H, I, s->num_sms);
+            const bool rss = fold && row_ss_for(M) && parts_o <= kRowSsParts && parts_d <= kRowSsParts;
+            float* ss_a = s->row_ss;
+            float* ss_b = s->row_ss + (size_t)kMaxStreamRows * kRowSsParts;
             if (!fold) launch_rmsnorm_bf16(s->x, L.norm1, c.rms_eps, M, H, s->xn, st, B200_DT_F16);
-            else if (l == 0) launch_scale_f16(s->x, L.norm1, M, H, reinterpret_cast<__half*>(s->xn), st);
+            else if (l == 0) launch_scale_f16(s->x, L.norm1, M, H, reinterpret_cast<__half*>(s->xn), rss ? ss_a : nullptr, st);
             StreamGemmParams g{};
             g.W = L.wqkv; g.X = s->xn; g.M = M; g.N = s->qkv_rows; g.K = H;
             g.q_out = s->q_f; g.k_pool = kp; g.v_pool = vp; g.kv_off = s->tm.kv_off; g.cos = s->tm.cos; g.sin = s->tm.sin;
             g.n_heads = c.n_heads; g.n_kv = c.n_kv_heads; g.head_stride = head_stride; g.ws = s->sk_ws; g.ws_flags = s->sk_flags;
             if (fold) { g.x_res = s->x; g.eps = c.rms_eps; }
+            if (rss) { g.row_ss = ss_a; g.row_ss_parts = l == 0 ? 1 : parts_d; }
             if (launch_gemm_stream(g, EPI_QKV, s->num_sms, st) != 0) return fail(B200_ECUDA, "[ERROR] %s", gemm_stream_last_error());
             AttnDecodeParams a{};
             a.q = s->q_f; a.k_pool = kp; a.v_pool = vp; a.block_table = kv->dev.block_table; a.t_end = s->tm.t_end; a.call_base = s->tm.call_base;
@@ -542,11 +567,13 @@ static int enqueue_forward(b200_shard_t* s, b200_kv_t* kv, const SlotList& sl, c
             StreamGemmParams o{};
             o.W = L.wo; o.X = s->attn_b; o.M = M; o.N = H; o.K = s->nq; o.out = s->x; o.ws = s->sk_ws; o.ws_flags = s->sk_flags;
             if (fold) { o.next_norm_w = L.norm2; o.xw_out = reinterpret_cast<__half*>(s->xn); }
+            if (rss) o.row_ss_out = ss_b;
             if (launch_gemm_stream(o, EPI_RESID, s->num_sms, st) != 0) return fail(B200_ECUDA, "[ERROR] %s", gemm_stream_last_error());
             if (!fold) launch_rmsnorm_bf16(s->x, L.norm2, c.rms_eps, M, H, s->xn, st, B200_DT_F16);
             StreamGemmParams gu{};
             gu.W = L.wgu; gu.X = s->xn; gu.M = M; gu.N = 2 * I; gu.K = H; gu.act_h = reinterpret_cast<__half*>(s->act_b); gu.ws = s->sk_ws; gu.ws_flags = s->sk_flags;
             if (fold) { gu.x_res = s->x; gu.eps = c.rms_eps; }
+            if (rss) { gu.row_ss = ss_b; gu.row_ss_parts = parts_o; }
             if (launch_gemm_stream(gu, EPI_SWIGLU, s->num_sms, st) != 0) return fail(B200_ECUDA, "[ERROR] %s", gemm_stream_last_error());
             StreamGemmParams d{};
             d.W = L.wdown; d.X = s->act_b; d.M = M; d.N = H; d.K = I; d.out = s->x; d.ws = s->sk_ws; d.ws_flags = s->sk_flags;
@@ -555,6 +582,8 @@ static int enqueue_forward(b200_shard_t* s, b200_kv_t* kv, const SlotList& sl, c
                 d.next_norm_w = s->final_norm; d.xw_out = reinterpret_cast<__half*>(s->xn);
                 s->tail_xw_ready = true;
             }
+            if (rss && d.xw_out != nullptr) { d.row_ss_out = ss_a; s->tail_ss_parts = parts_d; }
+            else s->tail_ss_parts = 0;
             if (launch_gemm_stream(d, EPI_RESID, s->num_sms, st) != 0) return fail(B200_ECUDA, "[ERROR] %s", gemm_stream_last_error());
             s->n_launch += fold ? 5 + (l == 0 ? 1 : 0) : 7;
         } else {
@@ -622,6 +651,7 @@ static int enqueue_tail(b200_shard_t* s, int B, int S, bool from_residual, int64
         StreamGemmParams g{};
         g.W = s->lm_head; g.X = s->xn; g.M = B; g.N = c.vocab_size; g.K = c.hidden_size; g.out = s->logits; g.ws = s->sk_ws; g.ws_flags = s->sk_flags;
         g.x_res = s->x; g.eps = c.rms_eps;
+        if (s->tail_ss_parts > 0) { g.row_ss = s->row_ss; g.row_ss_parts = s->tail_ss_parts; }
         if (launch_gemm_stream(g, EPI_STORE, s->num_sms, st) != 0) return fail(B200_ECUDA, "[ERROR] %s", gemm_stream_last_error());
     } else {
         launch_rmsnorm_bf16(s->lastrow, nullptr, 0.f, B, c.hidden_size, s->lastrow_b, st, B200_DT_F16);

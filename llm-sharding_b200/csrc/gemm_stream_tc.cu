@@ -136,12 +136,19 @@ gemm_stream_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_co
         if ((EPI == EPI_QKV || EPI == EPI_SWIGLU || EPI == EPI_STORE) && p.x_res != nullptr) {
             // folded RMSNorm: while the MMAs run, every CTA recomputes the row statistics from the fp32 residual stream (same
             // loads, same order in every CTA: identical bits everywhere); one warp per token row, xor-shuffle reduction
+            // With row_ss the producer of the residual stream left per-CTA partial sums of squares: M x parts floats to add
+            // instead of the M x K block to re-read.
             for (int m = quad; m < p.M; m += 4) {
-                const float4* xr = reinterpret_cast<const float4*>(p.x_res + (size_t)m * p.K);
                 float ss = 0.f;
-                for (int i = lane; i < p.K / 4; i += 32) {
-                    const float4 x4 = xr[i];
-                    ss += x4.x * x4.x + x4.y * x4.y + x4.z * x4.z + x4.w * x4.w;
+                if (p.row_ss != nullptr) {
+                    const float* pr = p.row_ss + (size_t)m * p.row_ss_parts;
+                    for (int i = lane; i < p.row_ss_parts; i += 32) ss += pr[i];
+                } else {
+                    const float4* xr = reinterpret_cast<const float4*>(p.x_res + (size_t)m * p.K);
+                    for (int i = lane; i < p.K / 4; i += 32) {
+                        const float4 x4 = xr[i];
+                        ss += x4.x * x4.x + x4.y * x4.y + x4.z * x4.z + x4.w * x4.w;
+                    }
                 }
                 ss = warp_sum(ss);
                 if (lane == 0) rstd_s[m] = rsqrtf(ss / (float)p.K + p.eps);
@@ -189,6 +196,7 @@ gemm_stream_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_co
     // ===== epilogue, phase 2: this rank's P row pairs x M tokens, summed over the ranks in rank order
     const int P = 64 / S;
     const int n_heads = p.n_heads, n_kv = p.n_kv;
+    float* sq_s = reinterpret_cast<float*>(gbase);       // [M][P] squares of this CTA's new residual values; the ring is idle by now
     for (int e = (int)threadIdx.x - 64; e < P * p.M; e += kSwThreads - 64) {
         const int jl = e % P, m = e / P;
         float a = 0.f, b = 0.f;
@@ -200,10 +208,12 @@ gemm_stream_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_co
         const int jj = (int)rank * P + jl;               // 0..63 inside the tile
         const int row0 = tile * kSwRows + jj, row1 = row0 + 64;
         if (EPI == EPI_STORE || EPI == EPI_RESID) {
+            float sq = 0.f;
             if (row0 < p.N) {
                 float* o = p.out + (size_t)m * p.N + row0;
                 const float r = (EPI == EPI_RESID) ? (*o + a) : a;
                 *o = r;
+                sq = r * r;
                 if (EPI == EPI_RESID && p.xw_out != nullptr)
                     p.xw_out[(size_t)m * p.N + row0] = __float2half_rn(fminf(fmaxf(r * __bfloat162float(p.next_norm_w[row0]), -65504.f), 65504.f));
             }
@@ -211,9 +221,11 @@ gemm_stream_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_co
                 float* o = p.out + (size_t)m * p.N + row1;
                 const float r = (EPI == EPI_RESID) ? (*o + b) : b;
                 *o = r;
+                sq = fmaf(r, r, sq);
                 if (EPI == EPI_RESID && p.xw_out != nullptr)
                     p.xw_out[(size_t)m * p.N + row1] = __float2half_rn(fminf(fmaxf(r * __bfloat162float(p.next_norm_w[row1]), -65504.f), 65504.f));
             }
+            if (EPI == EPI_RESID && p.row_ss_out != nullptr) sq_s[e] = sq;   // e = m * P + jl
         } else if (EPI == EPI_SWIGLU) {   // tile = 64 gate rows + the matching 64 up rows
             if (row0 < p.N) p.act_h[(size_t)m * (p.N >> 1) + tile * 64 + jj] = __float2half_rn(fminf(fmaxf(silu(a) * b, -65504.f), 65504.f));
         } else {                          // EPI_QKV: tile == head, rows jj and jj + 64 are a rotate_half pair
@@ -237,6 +249,16 @@ gemm_stream_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_co
             }
         }
     }
+    if (EPI == EPI_RESID && p.row_ss_out != nullptr) {
+        // this CTA's share of every token row's sum of squares (folded RMSNorm of the next projection), added in a fixed order
+        asm volatile("bar.sync 1, 128;" ::: "memory");   // the four epilogue warps
+        const int m = (int)threadIdx.x - 64;
+        if (m < p.M) {
+            float ss = 0.f;
+            for (int jl = 0; jl < P; ++jl) ss += sq_s[m * P + jl];
+            p.row_ss_out[(size_t)m * gridDim.x + blockIdx.x] = ss;
+        }
+    }
 }
 
 static char g_stream_err[256];
@@ -252,6 +274,8 @@ int gemm_stream_split(int N, int K, int num_sms) {
     while (S < 8 && tiles * S < num_sms && ks / (2 * S) >= 4) S *= 2;
     return S;
 }
+
+int gemm_stream_parts(int N, int K, int num_sms) { return ((N + kSwRows - 1) / kSwRows) * gemm_stream_split(N, K, num_sms); }
 
 template <int MP, int EPI, int NS>
 static int launch_one(const CUtensorMap& mw, const CUtensorMap& mx, const StreamGemmParams& p, cudaStream_t st) {
@@ -297,6 +321,8 @@ static bool streamk_enabled() {  // B200SHARD_STREAMK=1: the persistent stream-K
     }
     return v == 1;
 }
+
+bool gemm_streamk_active() { return streamk_enabled(); }
 
 int launch_gemm_stream(const StreamGemmParams& p_in, int epi, int num_sms, cudaStream_t st) {
     // Measured (tools/stream_gemm_bench.py, profiles/stream_gemm_r2.md): the persistent stream-K kernel wins where there are

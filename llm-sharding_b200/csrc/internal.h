@@ -72,7 +72,7 @@ void launch_decode_prologue(const KvDev& kv, const SlotList& slots, int B, int c
 // x fp32 [rows,n] -> out_dtype (B200_DT_* code: 0 bf16, 1 fp32, 2 fp16 saturating); norm_w == nullptr: plain convert
 void launch_rmsnorm_bf16(const float* x, const __nv_bfloat16* norm_w, float eps, int rows, int n,
                          void* out, cudaStream_t st, int out_dtype = 0);
-void launch_scale_f16(const float* x, const __nv_bfloat16* norm_w, int rows, int n, __half* out, cudaStream_t st);
+void launch_scale_f16(const float* x, const __nv_bfloat16* norm_w, int rows, int n, __half* out, float* ss_out, cudaStream_t st);
 // last-row gather + optional norm, fp32 out [B,n] (input rows b*S+S-1)
 void launch_lastrow_norm_f32(const float* x, const __nv_bfloat16* norm_w, float eps, int B, int S, int n,
                              float* out, cudaStream_t st);
@@ -152,6 +152,13 @@ struct StreamGemmParams {
     __half* xw_out = nullptr;
     const float* x_res = nullptr;   // [M,K] fp32
     float eps = 0.f;
+    // Row statistics handed from producer to consumer instead of being recomputed by every consuming CTA: the producer's CTA
+    // number c (tile * split + rank, `gemm_stream_parts` of them) writes row_ss_out[m * parts + c] = sum of x_new[m][n]^2 over
+    // the columns n it owns, in a fixed order; the consumer adds the `row_ss_parts` partials of a row in a fixed order too
+    // (bit-reproducible, no atomics) and needs M * parts floats instead of the M x K residual block.
+    float* row_ss_out = nullptr;
+    const float* row_ss = nullptr;
+    int row_ss_parts = 0;
     // stream-K kernel (gemm_streamk_tc.cu): partial-sum slots [grid][MP][128] floats and one flag per CTA (zero between launches)
     float* ws = nullptr;
     unsigned int* ws_flags = nullptr;
@@ -161,6 +168,8 @@ const char* gemm_streamk_last_error();
 size_t gemm_streamk_ws_floats(int num_sms);
 int launch_gemm_stream(const StreamGemmParams& p, int epi, int num_sms, cudaStream_t st);
 int gemm_stream_split(int N, int K, int num_sms);
+int gemm_stream_parts(int N, int K, int num_sms);   // CTAs (= row_ss partials per token row) of the default launch of an N x K GEMM
+bool gemm_streamk_active();                         // B200SHARD_STREAMK=1: that kernel neither writes nor reads row_ss
 const char* gemm_stream_last_error();
 
 enum GemmEpi { GEMM_STORE_BF16 = 0, GEMM_RESID_F32 = 1, GEMM_SWIGLU_BF16 = 2, GEMM_STORE_F32 = 3, GEMM_QKV_ROPE = 4 };

@@ -220,7 +220,8 @@ __device__ __forceinline__ uint32_t pack_f16_sat(float a, float b) {
 template <int OUT>  // element type of `out`: 0 bf16, 1 fp32, 2 fp16 (saturating) — the B200_DT_* codes
 __global__ void __launch_bounds__(256) rmsnorm_bf16_kernel(const float* __restrict__ x,
                                                            const __nv_bfloat16* __restrict__ w, float eps, int n,
-                                                           __nv_bfloat16* __restrict__ out, int normalize) {
+                                                           __nv_bfloat16* __restrict__ out, int normalize,
+                                                           float* __restrict__ ss_out) {
     __shared__ float red[33];
     // programmatic dependent launch: x comes from the previous kernel; the next kernel (a weight-streaming GEMM in the
     // batched-decode path) may start requesting its weights while this one runs
@@ -230,14 +231,15 @@ __global__ void __launch_bounds__(256) rmsnorm_bf16_kernel(const float* __restri
     __nv_bfloat16* orow = out + (size_t)blockIdx.x * n * (OUT == 1 ? 2 : 1);
     const int n8 = n / 8;
     float rstd = 1.f;
-    if (w != nullptr && normalize) {
+    if (w != nullptr && (normalize || ss_out != nullptr)) {
         float ss = 0.f;
         for (int i = threadIdx.x; i < n8; i += blockDim.x) {
             const float4 a = reinterpret_cast<const float4*>(xr)[2 * i], b = reinterpret_cast<const float4*>(xr)[2 * i + 1];
             ss += a.x * a.x + a.y * a.y + a.z * a.z + a.w * a.w + b.x * b.x + b.y * b.y + b.z * b.z + b.w * b.w;
         }
         ss = block_sum(ss, red);
-        rstd = rsqrtf(ss / (float)n + eps);
+        if (normalize) rstd = rsqrtf(ss / (float)n + eps);
+        if (ss_out != nullptr && threadIdx.x == 0) ss_out[blockIdx.x] = ss;   // the row's sum of squares, as one partial (row_ss_parts == 1)
     }
     for (int i = threadIdx.x; i < n8; i += blockDim.x) {
         const float4 a = reinterpret_cast<const float4*>(xr)[2 * i], b = reinterpret_cast<const float4*>(xr)[2 * i + 1];
@@ -265,8 +267,8 @@ __global__ void __launch_bounds__(256) rmsnorm_bf16_kernel(const float* __restri
         reinterpret_cast<uint4*>(orow)[i] = o;
     }
 }
-void launch_rmsnorm_bf16(const float* x, const __nv_bfloat16* norm_w, float eps, int rows, int n,
-                         void* out, cudaStream_t st, int out_dtype) {
+static void launch_rmsnorm_any(const float* x, const __nv_bfloat16* norm_w, float eps, int rows, int n,
+                               void* out, cudaStream_t st, int out_dtype, float* ss_out) {
     if (rows <= 0) return;
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(rows);
@@ -280,13 +282,18 @@ void launch_rmsnorm_bf16(const float* x, const __nv_bfloat16* norm_w, float eps,
     cfg.numAttrs = (e != nullptr && e[0] == '0') ? 0 : 1;
     __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(out);
     const int normalize = eps >= 0.f ? 1 : 0;
-    if (out_dtype == 2) cudaLaunchKernelEx(&cfg, rmsnorm_bf16_kernel<2>, x, norm_w, eps, n, o, normalize);
-    else if (out_dtype == 1) cudaLaunchKernelEx(&cfg, rmsnorm_bf16_kernel<1>, x, norm_w, eps, n, o, normalize);
-    else cudaLaunchKernelEx(&cfg, rmsnorm_bf16_kernel<0>, x, norm_w, eps, n, o, normalize);
+    if (out_dtype == 2) cudaLaunchKernelEx(&cfg, rmsnorm_bf16_kernel<2>, x, norm_w, eps, n, o, normalize, ss_out);
+    else if (out_dtype == 1) cudaLaunchKernelEx(&cfg, rmsnorm_bf16_kernel<1>, x, norm_w, eps, n, o, normalize, ss_out);
+    else cudaLaunchKernelEx(&cfg, rmsnorm_bf16_kernel<0>, x, norm_w, eps, n, o, normalize, ss_out);
 }
-// x * norm_w -> fp16 without the 1 / rms factor (the consuming GEMM applies it to its finished dot products)
-void launch_scale_f16(const float* x, const __nv_bfloat16* norm_w, int rows, int n, __half* out, cudaStream_t st) {
-    launch_rmsnorm_bf16(x, norm_w, -1.f, rows, n, out, st, 2);
+void launch_rmsnorm_bf16(const float* x, const __nv_bfloat16* norm_w, float eps, int rows, int n,
+                         void* out, cudaStream_t st, int out_dtype) {
+    launch_rmsnorm_any(x, norm_w, eps, rows, n, out, st, out_dtype, nullptr);
+}
+// x * norm_w -> fp16 without the 1 / rms factor (the consuming GEMM applies it to its finished dot products); ss_out (may be
+// null): [rows] sums of squares for that consumer
+void launch_scale_f16(const float* x, const __nv_bfloat16* norm_w, int rows, int n, __half* out, float* ss_out, cudaStream_t st) {
+    launch_rmsnorm_any(x, norm_w, -1.f, rows, n, out, st, 2, ss_out);
 }
 
 __global__ void __launch_bounds__(256) lastrow_norm_f32_kernel(const float* __restrict__ x,
