@@ -74,6 +74,8 @@ struct b200_shard {
     float *lastrow = nullptr, *logits = nullptr, *attn_part = nullptr;
     float* sk_ws = nullptr;             // stream-K GEMM: partial-sum slots, one per SM
     unsigned int* sk_flags = nullptr;   // and their flags (zero between launches)
+    MegaLayer* mega_layers = nullptr;   // persistent decode kernel: the layers' weight pointers, in device memory
+    unsigned int* mega_bar = nullptr;   // and its grid barrier (arrivals, generation), then the kernel's failure record
     float* row_ss = nullptr;            // folded RMSNorm: two buffers of [kMaxStreamRows][kRowSsParts] partial sums of squares
     __nv_bfloat16* lastrow_b = nullptr;
     TokMeta tm{};
@@ -171,6 +173,8 @@ extern "C" B200_API int b200_shard_create(const b200_shard_config_t* c, int devi
     r |= dev_alloc(A, &s->sk_ws, gemm_streamk_ws_floats(s->num_sms));
     r |= dev_alloc(A, &s->sk_flags, (size_t)2 * s->num_sms + 8);
     r |= dev_alloc(A, &s->row_ss, (size_t)2 * kMaxStreamRows * kRowSsParts);
+    r |= dev_alloc(A, &s->mega_layers, (size_t)c->n_layers);
+    r |= dev_alloc(A, &s->mega_bar, (size_t)8);
     r |= dev_alloc(A, &s->lastrow, (size_t)c->max_batch * H);
     r |= dev_alloc(A, &s->lastrow_b, (size_t)c->max_batch * H);
     r |= dev_alloc(A, &s->logits, (size_t)c->max_batch * V);
@@ -184,6 +188,7 @@ extern "C" B200_API int b200_shard_create(const b200_shard_config_t* c, int devi
     // arrival tickets of decode attention start at zero (the kernel re-zeroes them itself afterwards)
     CU_TRY(cudaMemset(s->attn_part, 0, part_floats * sizeof(float)));
     CU_TRY(cudaMemset(s->sk_flags, 0, ((size_t)2 * s->num_sms + 8) * sizeof(unsigned int)));
+    CU_TRY(cudaMemset(s->mega_bar, 0, 8 * sizeof(unsigned int)));
     *out = s;
     return 0;
 }
@@ -241,6 +246,11 @@ extern "C" B200_API int b200_shard_set_layer(b200_shard_t* s, int rel, const voi
     launch_convert_to_bf16(n2, dtype, L.norm2, (int64_t)H, st);
     CU_TRY(cudaGetLastError());
     CU_TRY(cudaStreamSynchronize(st));
+    MegaLayer ml;
+    ml.wqkv = reinterpret_cast<const __half*>(L.wqkv); ml.wo = reinterpret_cast<const __half*>(L.wo);
+    ml.wgu = reinterpret_cast<const __half*>(L.wgu); ml.wdown = reinterpret_cast<const __half*>(L.wdown);
+    ml.norm1 = L.norm1; ml.norm2 = L.norm2;
+    CU_TRY(cudaMemcpy(s->mega_layers + rel, &ml, sizeof(ml), cudaMemcpyHostToDevice));
     L.set = true;
     return 0;
 }
@@ -422,6 +432,12 @@ static int gemv_row_limit(const b200_shard* s) {
     return lim;
 }
 
+static bool mega_enabled() {
+    static int v = -1;
+    if (v < 0) { const char* e = getenv("B200SHARD_MEGA"); v = (e != nullptr && e[0] == '1') ? 1 : 0; }
+    return v == 1;
+}
+
 static int check_call(b200_shard_t* s, b200_kv_t* kv, const int32_t* h_slots, const void* in, int B, int S, SlotList* sl) {
     if (s == nullptr || kv == nullptr || h_slots == nullptr || in == nullptr) return fail(B200_EINVAL, "[ERROR] null argument");
     if (kv->shard != s) return fail(B200_ESTATE, "[ERROR] this KV cache belongs to another shard");
@@ -501,7 +517,24 @@ static int enqueue_forward(b200_shard_t* s, b200_kv_t* kv, const SlotList& sl, c
     for (int b = 0; b < B; ++b) max_keys = kv->h_len[sl.v[b]] + S > max_keys ? kv->h_len[sl.v[b]] + S : max_keys;
     const bool stream_path = !gemv_path && M <= kMaxStreamRows && stream_gemm_enabled() && H % 64 == 0 && I % 64 == 0 &&
                              attn_scratch_fits(M, attn_splits(s, kv, M));
-    for (int l = 0; l < c.n_layers; ++l) {
+    // One row, one token: every layer in ONE persistent kernel (decode_mega.cu) whose weight stream runs through the phase
+    // boundaries.  B200SHARD_MEGA=0 keeps the five launches per layer (A/B).
+    bool mega_done = false;
+    if (gemv_path && M == 1 && mega_enabled()) {
+        MegaParams mp{};
+        mp.layers = s->mega_layers; mp.n_layers = c.n_layers; mp.H = H; mp.I = I; mp.n_heads = c.n_heads; mp.n_kv = c.n_kv_heads;
+        mp.qkv_rows = s->qkv_rows; mp.eps = c.rms_eps; mp.x = s->x; mp.qkv_raw = s->q_f; mp.attn_out = s->attn_f; mp.gu_raw = s->act_f;
+        mp.k_pool = kv->k_pool; mp.v_pool = kv->v_pool; mp.layer_stride = kv->layer_stride; mp.head_stride = head_stride;
+        mp.block_table = kv->dev.block_table; mp.slot = sl.v[0]; mp.max_pages_per_slot = kv->dev.max_pages_per_slot;
+        mp.page_size = kv->dev.page_size; mp.t_end = s->tm.t_end; mp.kv_off = s->tm.kv_off; mp.cos = s->tm.cos; mp.sin = s->tm.sin;
+        mp.part = s->attn_part;
+        mp.tickets = reinterpret_cast<unsigned int*>(s->attn_part + (size_t)kMaxGemvRows * c.n_heads * kMaxSplits * 130);
+        mp.bar = s->mega_bar;
+        const int rc = launch_decode_mega(mp, s->num_sms, st);
+        if (rc < 0) return fail(B200_ECUDA, "[ERROR] %s", decode_mega_last_error());
+        if (rc == 0) { mega_done = true; s->n_launch += 1; }
+    }
+    for (int l = 0; l < c.n_layers && !mega_done; ++l) {
         const LayerW& L = s->layers[l];
         __nv_bfloat16* kp = kv->k_pool + (int64_t)l * kv->layer_stride;
         __nv_bfloat16* vp = kv->v_pool + (int64_t)l * kv->layer_stride;

@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <stdint.h>
 
 namespace b200 {
@@ -171,6 +172,33 @@ int gemm_stream_split(int N, int K, int num_sms);
 int gemm_stream_parts(int N, int K, int num_sms);   // CTAs (= row_ss partials per token row) of the default launch of an N x K GEMM
 bool gemm_streamk_active();                         // B200SHARD_STREAMK=1: that kernel neither writes nor reads row_ss
 const char* gemm_stream_last_error();
+
+// Persistent single-token decode kernel (decode_mega.cu): every layer of the shard in one cooperative launch.
+struct MegaLayer { const __half *wqkv, *wo, *wgu, *wdown; const __nv_bfloat16 *norm1, *norm2; };
+struct MegaParams {
+    const MegaLayer* layers;   // [n_layers] in device memory
+    int n_layers, H, I, n_heads, n_kv, qkv_rows;
+    float eps;
+    float* x;                  // [H] fp32 residual stream (in / out)
+    float* qkv_raw;            // [qkv_rows] q | k | v before RoPE
+    float* attn_out;           // [n_heads * 128]
+    float* gu_raw;             // [2 I] gate / up in the packed row order of wgu
+    __nv_bfloat16* k_pool;     // layer 0's pools; layer l at + l * layer_stride
+    __nv_bfloat16* v_pool;
+    int64_t layer_stride, head_stride;
+    const int32_t* block_table;
+    int slot, max_pages_per_slot, page_size;
+    const int32_t* t_end;      // TokMeta of the call (row 0)
+    const int64_t* kv_off;
+    const float* cos;
+    const float* sin;
+    float* part;               // [n_heads][n_splits][130] split-K partials
+    unsigned int* tickets;     // [n_heads], zero between launches
+    unsigned int* bar;         // [8] words 6-7: the grid barrier's 64-bit arrival counter; 2..5: failure record of a wait that ran out
+    int n_splits = 0, n_slots = 0, xs_floats = 0, profile = 0;   // filled in by the launcher
+};
+int launch_decode_mega(const MegaParams& p, int num_sms, cudaStream_t st);   // 0 launched, 1 shape not served, -1 error
+const char* decode_mega_last_error();
 
 enum GemmEpi { GEMM_STORE_BF16 = 0, GEMM_RESID_F32 = 1, GEMM_SWIGLU_BF16 = 2, GEMM_STORE_F32 = 3, GEMM_QKV_ROPE = 4 };
 struct GemmParams {
