@@ -353,7 +353,12 @@ int launch_gemm_stream(const StreamGemmParams& p_in, int epi, int num_sms, cudaS
         snprintf(g_stream_err, sizeof(g_stream_err), "gemm_stream: tensor map creation failed");
         return -1;
     }
-#define B200_SW_CASE(E) (MP == 16 ? launch_one<16, E, 4>(mw, mx, p, st) : launch_one<32, E, 4>(mw, mx, p, st))
+    // ring depth: 5 stages of 18 KB for the 16-column operand (two CTAs of 101 KB still share an SM; same-box A/B against 4
+    // stages: layer at 4 / 8 / 16 rows 89.0 / 94.0 / 102.7 -> 87.7 / 92.9 / 101.1 us, lm_head 43.7 -> 42.8 us), 4 stages of 20 KB
+    // for the 32-column one.  B200SHARD_SW_STAGES=4 restores the shallower ring (A/B).
+    static int deep = -1;
+    if (deep < 0) { const char* e = getenv("B200SHARD_SW_STAGES"); deep = (e != nullptr && atoi(e) == 4) ? 0 : 1; }
+#define B200_SW_CASE(E) (MP == 16 ? (deep ? launch_one<16, E, 5>(mw, mx, p, st) : launch_one<16, E, 4>(mw, mx, p, st)) : launch_one<32, E, 4>(mw, mx, p, st))
     switch (epi) {
         case EPI_STORE: return B200_SW_CASE(EPI_STORE);
         case EPI_RESID: return B200_SW_CASE(EPI_RESID);
