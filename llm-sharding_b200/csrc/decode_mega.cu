@@ -144,9 +144,8 @@ struct MegaShared {
 // One projection: this CTA's rows of W [N,K] against the staged vector xs; scale multiplies every result (1 / rms).
 // ALL consumer warps work on the oldest slot of the ring together (thread t owns the 16-byte chunks t, t + 512, ... of every
 // row in it), so slots are consumed strictly in the order they were requested and live in shared memory only for as long as
-// their bytes are in flight — the whole ring is bytes in flight, as the registers of the per-kernel GEMV were.  The threads'
-// partial sums are combined once per group of two slots (one row when a row spans several slots): warp shuffles, a
-// double-buffered 16 x 8 array, ONE named barrier per group, and up to eight threads finish while the rest stream on.
+// their bytes are in flight — the whole ring is bytes in flight, as the registers of the per-kernel GEMV were (and every
+// thread waits for every slot in order, so a parity wait can never be taken for an earlier use of the barrier).
 template <int EPI>
 __device__ __forceinline__ void mega_gemv(const MegaShared& sh, uint32_t& cidx, uint32_t& cpar, const float* xs, float* part, int& buf, int N,
                                        int K, float scale, float* out, int tid, int warp, int lane) {
@@ -626,6 +625,8 @@ int launch_decode_mega(const MegaParams& p_in, int num_sms, cudaStream_t st) {
     if (ns < 1) ns = 1;
     if (ns > kMaxSplits) ns = kMaxSplits;
     p.n_splits = ns;
+    // measurement modes: 1 = timestamps (MEGA_PROFILE builds only), 2 = no FMA loop, 3 = no FMA loop and no reductions (results are
+    // garbage in modes 2 and 3; they exist for the breakdown in profiles/decode_mega_r2.md)
     { const char* e = getenv("B200SHARD_MEGA_PROFILE"); p.profile = e != nullptr ? atoi(e) : 0; }
     const size_t smem = mega_smem(n_slots, xs);
     if (cudaFuncSetAttribute(decode_mega_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) {
