@@ -26,7 +26,6 @@ constexpr int kBlkM = 128, kBlkN = 128, kBlkK = 64, kStages = 6;
 constexpr int kGemmThreads = 192;
 constexpr uint32_t kStageBytesA = kBlkM * kBlkK * 2, kStageBytesB = kBlkN * kBlkK * 2;
 constexpr uint32_t kStageBytes = kStageBytesA + kStageBytesB;
-constexpr uint32_t kTmemCols = 128;
 constexpr size_t kGemmSmem = 1024 /*align slack*/ + (size_t)kStages * kStageBytes + 256 /*barriers*/;
 
 // K-major operand tile, 128-byte swizzle, rows of 64 x 16-bit (= 128 B); 8-row groups are 1024 B apart
@@ -36,7 +35,6 @@ __device__ __forceinline__ uint64_t umma_desc(uint32_t smem_addr) { return umma_
 // instruction on sm_100a — measured).  The shard path runs fp16 x fp16: the bf16 model weights are held as fp16
 // (exact for every bf16 value in fp16's normal range) so that activations can carry 10 mantissa bits — 8x less
 // rounding than bf16 — into the tensor cores at no cost.
-constexpr uint32_t kIdescBase = (1u << 4) | ((uint32_t)(kBlkN >> 3) << 17) | ((uint32_t)(kBlkM >> 4) << 24);
 __device__ __forceinline__ uint32_t pack_f16(float a, float b) {
     a = fminf(fmaxf(a, -65504.f), 65504.f);
     b = fminf(fmaxf(b, -65504.f), 65504.f);
@@ -46,7 +44,7 @@ __device__ __forceinline__ uint32_t pack_f16(float a, float b) {
 
 // One accumulator row per thread: `trow` = TMEM address of this thread's lane at the first column of a 128-column
 // logical tile, `n_blk` = index of that tile along N (one head for QKV_ROPE, one gate/up pair block for SWIGLU).
-template <int EPI>
+template <int EPI, int BN = kBlkN>   // BN: columns of the tile for the plain store / residual epilogues (the paired ones are 128 wide)
 __device__ __forceinline__ void gemm_epilogue(const GemmParams& p, const uint32_t trow, const int row, const int n_blk) {
     const bool row_ok = row < p.M;
     if (EPI == GEMM_SWIGLU_BF16) {
@@ -136,10 +134,10 @@ __device__ __forceinline__ void gemm_epilogue(const GemmParams& p, const uint32_
         }
     } else {
 #pragma unroll 1
-        for (int c = 0; c < kBlkN / 32; ++c) {
+        for (int c = 0; c < BN / 32; ++c) {
             uint32_t r[32];
             tmem_ld32(trow + c * 32, r);
-            const int col0 = n_blk * kBlkN + c * 32;
+            const int col0 = n_blk * BN + c * 32;
             if (row_ok) {
                 if (EPI == GEMM_STORE_BF16) {
                     __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(p.out) + (size_t)row * p.N + col0;
@@ -170,32 +168,36 @@ __device__ __forceinline__ void gemm_epilogue(const GemmParams& p, const uint32_
     }
 }
 
-template <int EPI>
-__global__ void __launch_bounds__(kGemmThreads, 1)
+// BN x NSTG: 128 columns behind a 6-stage ring (one CTA per SM), or 64 columns behind a 4-stage ring — 97 KB, two CTAs per SM —
+// for the GEMMs that have too few 128 x 128 tiles to give every SM more than one (o_proj / down_proj of a 512-token prompt:
+// 128 tiles for 148 SMs, nothing to overlap a tile's ramp and epilogue with; 256 half-width tiles, two resident per SM, do).
+template <int EPI, int BN, int NSTG>
+__global__ void __launch_bounds__(kGemmThreads, (BN == 128 ? 1 : 2))
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                     const GemmParams p) {
+    constexpr uint32_t kStB = BN * kBlkK * 2, kSt = kStageBytesA + kStB;   // bytes per stage: W tile, both tiles
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw = s_u32(smem_raw);
     const uint32_t base = (raw + 1023u) & ~1023u;  // SWIZZLE_128B tiles need 1024-byte alignment
     uint8_t* gen_base = smem_raw + (base - raw);
-    const uint32_t bars = base + kStages * kStageBytes;
-    const uint32_t full0 = bars, empty0 = bars + 8 * kStages, tmem_full = bars + 16 * kStages;
-    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(gen_base + kStages * kStageBytes + 16 * kStages + 8);
+    const uint32_t bars = base + NSTG * kSt;
+    const uint32_t full0 = bars, empty0 = bars + 8 * NSTG, tmem_full = bars + 16 * NSTG;
+    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(gen_base + NSTG * kSt + 16 * NSTG + 8);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n_blk = blockIdx.x, m_blk = blockIdx.y;
     const int num_k = (p.K + kBlkK - 1) / kBlkK;
-    const uint32_t idesc = kIdescBase | (p.ab_f16 ? 0u : ((1u << 7) | (1u << 10)));
+    const uint32_t idesc = (1u << 4) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(kBlkM >> 4) << 24) | (p.ab_f16 ? 0u : ((1u << 7) | (1u << 10)));
 
     if (warp == 0 && lane == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_a) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_b) : "memory");
-        for (int i = 0; i < kStages; ++i) { mbar_init(full0 + 8 * i, 1); mbar_init(empty0 + 8 * i, 1); }
+        for (int i = 0; i < NSTG; ++i) { mbar_init(full0 + 8 * i, 1); mbar_init(empty0 + 8 * i, 1); }
         mbar_init(tmem_full, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(s_u32((const void*)tmem_slot)), "n"(kTmemCols) : "memory");
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(s_u32((const void*)tmem_slot)), "n"(BN) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -207,32 +209,32 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
         if (lane == 0) {  // ===== TMA producer
             // programmatic dependent launch: the weight tiles of the first trip round the ring do not depend on the previous
             // kernel and are requested before griddepcontrol.wait; the activation tiles follow it
-            const int pre = num_k < kStages ? num_k : kStages;
+            const int pre = num_k < NSTG ? num_k : NSTG;
             for (int kb = 0; kb < pre; ++kb) {
-                mbar_expect_tx(full0 + 8 * kb, kStageBytes);
-                tma_load_2d(&tma_b, full0 + 8 * kb, base + kb * kStageBytes + kStageBytesA, kb * kBlkK, n_blk * kBlkN);
+                mbar_expect_tx(full0 + 8 * kb, kSt);
+                tma_load_2d(&tma_b, full0 + 8 * kb, base + kb * kSt + kStageBytesA, kb * kBlkK, n_blk * BN);
             }
             asm volatile("griddepcontrol.wait;" ::: "memory");
             asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-            for (int kb = 0; kb < pre; ++kb) tma_load_2d(&tma_a, full0 + 8 * kb, base + kb * kStageBytes, kb * kBlkK, m_blk * kBlkM);
+            for (int kb = 0; kb < pre; ++kb) tma_load_2d(&tma_a, full0 + 8 * kb, base + kb * kSt, kb * kBlkK, m_blk * kBlkM);
             for (int kb = pre; kb < num_k; ++kb) {
-                const int st = kb % kStages;
-                const uint32_t ph = (uint32_t)(kb / kStages) & 1u;
+                const int st = kb % NSTG;
+                const uint32_t ph = (uint32_t)(kb / NSTG) & 1u;
                 mbar_wait(empty0 + 8 * st, ph ^ 1u);
-                mbar_expect_tx(full0 + 8 * st, kStageBytes);
-                const uint32_t sa = base + st * kStageBytes, sb = sa + kStageBytesA;
+                mbar_expect_tx(full0 + 8 * st, kSt);
+                const uint32_t sa = base + st * kSt, sb = sa + kStageBytesA;
                 tma_load_2d(&tma_a, full0 + 8 * st, sa, kb * kBlkK, m_blk * kBlkM);
-                tma_load_2d(&tma_b, full0 + 8 * st, sb, kb * kBlkK, n_blk * kBlkN);
+                tma_load_2d(&tma_b, full0 + 8 * st, sb, kb * kBlkK, n_blk * BN);
             }
         }
     } else if (warp == 1) {
         if (lane == 0) {  // ===== MMA issuer (one thread drives the tensor core for the CTA)
             for (int kb = 0; kb < num_k; ++kb) {
-                const int st = kb % kStages;
-                const uint32_t ph = (uint32_t)(kb / kStages) & 1u;
+                const int st = kb % NSTG;
+                const uint32_t ph = (uint32_t)(kb / NSTG) & 1u;
                 mbar_wait(full0 + 8 * st, ph);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                const uint32_t sa = base + st * kStageBytes, sb = sa + kStageBytesA;
+                const uint32_t sa = base + st * kSt, sb = sa + kStageBytesA;
 #pragma unroll
                 for (int k = 0; k < kBlkK / 16; ++k)
                     umma_f16(tmem_base, umma_desc(sa + k * 32), umma_desc(sb + k * 32), idesc, (kb > 0 || k > 0) ? 1u : 0u);
@@ -247,13 +249,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
         const int quad = warp & 3;
         const int row = m_blk * kBlkM + quad * 32 + lane;
         const uint32_t trow = tmem_base + ((uint32_t)(quad * 32) << 16);
-        gemm_epilogue<EPI>(p, trow, row, n_blk);
+        gemm_epilogue<EPI, BN>(p, trow, row, n_blk);
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     }
     __syncthreads();
     if (warp == 1) {
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(kTmemCols) : "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(BN) : "memory");
     }
 }
 
@@ -509,10 +511,32 @@ int launch_gemm(const GemmParams& p, cudaStream_t st) {
 #undef B200_GEMM2_LAUNCH
         return 0;
     }
+    // Few 128 x 128 tiles (less than 1.5 per SM) and an epilogue that does not pair columns: half-width tiles, two CTAs per SM.
+    static int n64 = -1;   // B200SHARD_GEMM_N64=0: always 128-column tiles (A/B)
+    if (n64 < 0) { const char* e = getenv("B200SHARD_GEMM_N64"); n64 = (e != nullptr && e[0] == '0') ? 0 : 1; }
+    const int64_t tiles128 = (int64_t)((p.N + kBlkN - 1) / kBlkN) * ((p.M + kBlkM - 1) / kBlkM);
+    const bool plain = p.epi == GEMM_STORE_BF16 || p.epi == GEMM_RESID_F32 || p.epi == GEMM_STORE_F32;
+    if (n64 == 1 && plain && tiles128 < 222 && p.N % 64 == 0) {
+        CUtensorMap mb64;
+        if (make_map(&mb64, p.W, p.N, p.K, 64) != 0) return -1;
+        dim3 grid64((p.N + 63) / 64, (p.M + kBlkM - 1) / kBlkM);
+        constexpr size_t smem64 = 1024 + (size_t)4 * (kStageBytesA + 64 * kBlkK * 2) + 256;
+#define B200_GEMM64_LAUNCH(E)                                                                               \
+    {                                                                                                       \
+        auto kfn = gemm_tcgen05_kernel<E, 64, 4>;                                                           \
+        cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem64);                \
+        launch_pdl(kfn, grid64, smem64, st, ma, mb64, p);                                                   \
+    }
+        if (p.epi == GEMM_STORE_BF16) B200_GEMM64_LAUNCH(GEMM_STORE_BF16)
+        else if (p.epi == GEMM_RESID_F32) B200_GEMM64_LAUNCH(GEMM_RESID_F32)
+        else B200_GEMM64_LAUNCH(GEMM_STORE_F32)
+#undef B200_GEMM64_LAUNCH
+        return 0;
+    }
     dim3 grid((p.N + kBlkN - 1) / kBlkN, (p.M + kBlkM - 1) / kBlkM);
 #define B200_GEMM_LAUNCH(E)                                                                                 \
     {                                                                                                       \
-        auto kfn = gemm_tcgen05_kernel<E>;                                                                  \
+        auto kfn = gemm_tcgen05_kernel<E, kBlkN, kStages>;                                                  \
         cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGemmSmem);             \
         launch_pdl(kfn, grid, kGemmSmem, st, ma, mb, p);                                                    \
     }
