@@ -272,7 +272,6 @@ constexpr uint32_t kStageBytesB2 = (kBlkN2 / 2) * kBlkK * 2;         // this CTA
 constexpr uint32_t kStageBytes2 = kStageBytesA + kStageBytesB2;      // 32 KB per CTA per stage
 
 constexpr uint32_t kPeerMask = 0xFEFFFFFFu;                          // shared::cluster address of the same offset in CTA rank 0
-constexpr uint32_t kIdescBase2 = (1u << 4) | ((uint32_t)(kBlkN2 >> 3) << 17) | ((uint32_t)(256 >> 4) << 24);
 
 __device__ __forceinline__ void tma_load_2d_pair(const CUtensorMap* map, uint32_t leader_bar, uint32_t dst, int x, int y) {
     asm volatile(
@@ -302,32 +301,35 @@ __device__ __forceinline__ void mbar_arrive_leader(uint32_t bar) {
 // Persistent: one CTA pair per SM pair walks over the 256 x 256 tiles (m fastest, so that concurrently running pairs
 // share the weight tile in L2).  The accumulator is double buffered in tensor memory (2 x 256 columns): the epilogue of
 // tile i (TMEM -> registers -> global, with the fused RoPE / SwiGLU / residual work) overlaps the MMAs of tile i+1.
-template <int EPI>
+// BN2: columns of the pair's tile — 256, or 128 (with NSTG2 = 8 stages of 24 KB) for the residual GEMMs of mid-sized prompts, where 256 x 256
+// tiles number fewer than the SM pairs and 128 x 128 single-CTA tiles move a third more bytes through shared memory per flop.
+template <int EPI, int BN2, int NSTG2>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
 gemm_pair_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                          const GemmParams p) {
+    constexpr uint32_t kStB2 = (BN2 / 2) * kBlkK * 2, kSt2 = kStageBytesA + kStB2;   // this CTA's half of the B tile; both tiles
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw = s_u32(smem_raw);
     const uint32_t base = (raw + 1023u) & ~1023u;
     uint8_t* gen_base = smem_raw + (base - raw);
-    const uint32_t bars = base + kStages * kStageBytes2;
-    const uint32_t full0 = bars, empty0 = bars + 8 * kStages, tfull0 = bars + 16 * kStages, tempty0 = tfull0 + 16;
-    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(gen_base + kStages * kStageBytes2 + 16 * kStages + 32);
+    const uint32_t bars = base + NSTG2 * kSt2;
+    const uint32_t full0 = bars, empty0 = bars + 8 * NSTG2, tfull0 = bars + 16 * NSTG2, tempty0 = tfull0 + 16;
+    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(gen_base + NSTG2 * kSt2 + 16 * NSTG2 + 32);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     uint32_t cta_rank;
     asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(cta_rank));
     const bool leader = cta_rank == 0;
     const int pair_id = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
-    const int n_m = (p.M + 255) / 256, n_n = (p.N + kBlkN2 - 1) / kBlkN2;
+    const int n_m = (p.M + 255) / 256, n_n = (p.N + BN2 - 1) / BN2;
     const int n_tiles = n_m * n_n;
     const int num_k = (p.K + kBlkK - 1) / kBlkK;
-    const uint32_t idesc = kIdescBase2 | (p.ab_f16 ? 0u : ((1u << 7) | (1u << 10)));
+    const uint32_t idesc = (1u << 4) | ((uint32_t)(BN2 >> 3) << 17) | ((uint32_t)(256 >> 4) << 24) | (p.ab_f16 ? 0u : ((1u << 7) | (1u << 10)));
 
     if (warp == 0 && lane == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_a) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_b) : "memory");
-        for (int i = 0; i < kStages; ++i) { mbar_init(full0 + 8 * i, 1); mbar_init(empty0 + 8 * i, 1); }
+        for (int i = 0; i < NSTG2; ++i) { mbar_init(full0 + 8 * i, 1); mbar_init(empty0 + 8 * i, 1); }
         for (int i = 0; i < 2; ++i) { mbar_init(tfull0 + 8 * i, 1); mbar_init(tempty0 + 8 * i, 8); }  // 4 epilogue warps x 2 CTAs
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -348,12 +350,12 @@ gemm_pair_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
             uint32_t it = 0;
             for (int t = pair_id; t < n_tiles; t += n_pairs) {
                 const int m_row0 = (t % n_m) * 256 + (int)cta_rank * kBlkM;
-                const int n_row0 = (t / n_m) * kBlkN2 + (int)cta_rank * (kBlkN2 / 2);
+                const int n_row0 = (t / n_m) * BN2 + (int)cta_rank * (BN2 / 2);
                 for (int kb = 0; kb < num_k; ++kb, ++it) {
-                    const uint32_t st = it % kStages, ph = (it / kStages) & 1u;
+                    const uint32_t st = it % NSTG2, ph = (it / NSTG2) & 1u;
                     mbar_wait(empty0 + 8 * st, ph ^ 1u);
-                    if (leader) mbar_expect_tx(full0 + 8 * st, 2 * kStageBytes2);
-                    const uint32_t sa = base + st * kStageBytes2, sb = sa + kStageBytesA;
+                    if (leader) mbar_expect_tx(full0 + 8 * st, 2 * kSt2);
+                    const uint32_t sa = base + st * kSt2, sb = sa + kStageBytesA;
                     const uint32_t lbar = (full0 + 8 * st) & kPeerMask;
                     tma_load_2d_pair(&tma_a, lbar, sa, kb * kBlkK, m_row0);
                     tma_load_2d_pair(&tma_b, lbar, sb, kb * kBlkK, n_row0);
@@ -367,12 +369,12 @@ gemm_pair_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
                 const uint32_t buf = ti & 1u;
                 mbar_wait(tempty0 + 8 * buf, ((ti >> 1) & 1u) ^ 1u);  // both CTAs' epilogues have drained this accumulator
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                const uint32_t acc = tmem_base + buf * kBlkN2;
+                const uint32_t acc = tmem_base + buf * BN2;
                 for (int kb = 0; kb < num_k; ++kb, ++it) {
-                    const uint32_t st = it % kStages, ph = (it / kStages) & 1u;
+                    const uint32_t st = it % NSTG2, ph = (it / NSTG2) & 1u;
                     mbar_wait(full0 + 8 * st, ph);
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                    const uint32_t sa = base + st * kStageBytes2, sb = sa + kStageBytesA;
+                    const uint32_t sa = base + st * kSt2, sb = sa + kStageBytesA;
 #pragma unroll
                     for (int k = 0; k < kBlkK / 16; ++k)
                         umma_f16_pair(acc, umma_desc(sa + k * 32), umma_desc(sb + k * 32), idesc, (kb > 0 || k > 0) ? 1u : 0u);
@@ -391,10 +393,10 @@ gemm_pair_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
             mbar_wait(tfull0 + 8 * buf, (ti >> 1) & 1u);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const int row = m_row0 + quad * 32 + lane;
-            const uint32_t trow = tmem_base + buf * kBlkN2 + ((uint32_t)(quad * 32) << 16);
+            const uint32_t trow = tmem_base + buf * BN2 + ((uint32_t)(quad * 32) << 16);
 #pragma unroll 1
-            for (int sub = 0; sub < 2; ++sub)
-                if ((n_blk * 2 + sub) * kBlkN < p.N) gemm_epilogue<EPI>(p, trow + sub * kBlkN, row, n_blk * 2 + sub);
+            for (int sub = 0; sub < BN2 / kBlkN; ++sub)
+                if ((n_blk * (BN2 / kBlkN) + sub) * kBlkN < p.N) gemm_epilogue<EPI>(p, trow + sub * kBlkN, row, n_blk * (BN2 / kBlkN) + sub);
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
             __syncwarp();
             if (lane == 0) mbar_arrive_leader(tempty0 + 8 * buf);  // this warp no longer reads accumulator `buf`
@@ -487,7 +489,36 @@ int launch_gemm(const GemmParams& p, cudaStream_t st) {
     }
     // CTA pairs (256 x 256 tiles, half the L2 -> shared-memory traffic per flop) once there are enough tiles to occupy
     // most SM pairs; small problems keep the finer 128 x 128 tiling (measured: profiles/gemm_bench_r1.md)
-    if (pair_mode == 1 && p.M > kBlkM && (int64_t)((p.M + 255) / 256) * ((p.N + kBlkN2 - 1) / kBlkN2) >= 64) {
+    // Residual / plain-store GEMMs whose 256 x 256 tiles would not fill the SM pairs: 256 x 128 pair tiles, where there are more
+    // of those than SM pairs so that the persistent pairs overlap one tile's epilogue with the next tile's main loop (513..768
+    // rows for N = 4096: per layer 406 -> 384 us at 768 tokens; with a single tile per pair, 512 rows, it loses 264 -> 268 us,
+    // same box).  B200SHARD_GEMM_PAIR_N128=0 keeps the single-CTA kernels there (A/B).
+    static int pair_n128 = -1;
+    if (pair_n128 < 0) { const char* e = getenv("B200SHARD_GEMM_PAIR_N128"); pair_n128 = (e != nullptr && e[0] == '0') ? 0 : 1; }
+    const int64_t tiles256 = (int64_t)((p.M + 255) / 256) * ((p.N + kBlkN2 - 1) / kBlkN2);
+    if (pair_mode == 1 && pair_n128 == 1 && p.M > kBlkM && tiles256 < 64 && p.N % 128 == 0 && 2 * tiles256 > 74 &&
+        (p.epi == GEMM_RESID_F32 || p.epi == GEMM_STORE_F32 || p.epi == GEMM_STORE_BF16)) {
+        int n_sms = 148, dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, dev);
+        const int64_t tiles = (int64_t)((p.M + 255) / 256) * (p.N / 128);
+        const int pairs = (int)(tiles < n_sms / 2 ? tiles : n_sms / 2);
+        CUtensorMap mb64;
+        if (make_map(&mb64, p.W, p.N, p.K, 64) != 0) return -1;
+        constexpr size_t smem3 = 1024 + (size_t)8 * (kStageBytesA + 64 * kBlkK * 2) + 256;
+#define B200_GEMM3_LAUNCH(E)                                                                                \
+    {                                                                                                       \
+        auto kfn = gemm_pair_tcgen05_kernel<E, 128, 8>;                                                     \
+        cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem3);                 \
+        launch_pdl(kfn, dim3(2 * pairs), smem3, st, ma, mb64, p);                                           \
+    }
+        if (p.epi == GEMM_RESID_F32) B200_GEMM3_LAUNCH(GEMM_RESID_F32)
+        else if (p.epi == GEMM_STORE_F32) B200_GEMM3_LAUNCH(GEMM_STORE_F32)
+        else B200_GEMM3_LAUNCH(GEMM_STORE_BF16)
+#undef B200_GEMM3_LAUNCH
+        return 0;
+    }
+    if (pair_mode == 1 && p.M > kBlkM && tiles256 >= 64) {
         int n_sms = 148, dev = 0;
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, dev);
@@ -497,7 +528,7 @@ int launch_gemm(const GemmParams& p, cudaStream_t st) {
         const size_t smem2 = 1024 + (size_t)kStages * kStageBytes2 + 256;
 #define B200_GEMM2_LAUNCH(E)                                                                                \
     {                                                                                                       \
-        auto kfn = gemm_pair_tcgen05_kernel<E>;                                                             \
+        auto kfn = gemm_pair_tcgen05_kernel<E, kBlkN2, kStages>;                                                             \
         cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);                 \
         launch_pdl(kfn, grid2, smem2, st, ma, mb, p);                                                       \
     }
