@@ -133,6 +133,26 @@ B200_API int b200_shard_forward_argmax(b200_shard_t* s, b200_kv_t* kv, const int
 B200_API int b200_shard_step_tokens(b200_shard_t* s, b200_kv_t* kv, const int32_t* h_slots, const int64_t* d_tok_in,
                                     int B, int S, int causal, void* d_hidden_out, int64_t* d_tok_out,
                                     float* d_margin_out, void* stream);
+/* Vocabulary-split tail for a layer-sharded ring of single-token rows.  The reference puts final norm + lm_head + argmax on
+ * the last worker (utils/node_worker.py:155-164,260-264), which makes that stage the slowest of the ring by one 262 MB
+ * matrix per token.  Here the tail may score only lm_head rows [0, split) and hand the rest to the stage that follows it
+ * in the ring (the head, which receives the token anyway): no counterpart in the reference, same logits bit for bit, same
+ * arg-max (first index of the maximum).
+ *   b200_shard_forward_partial   (tail)  forward over the shard's layers, then d_msg_out receives
+ *        float x[B][H]        the last fp32 residual row of every batch row (before the final norm)
+ *        float best[B], second[B]; int64 idx[B]   best / second-best score and best row over lm_head rows [0, split)
+ *        = B200_PARTIAL_MSG_BYTES(B, H) bytes; at most 3 rows per call.
+ *   b200_shard_set_vocab_tail    (next stage)  rows [split, V) of lm_head ([V - split, H], row-major) and the final norm
+ *        weight (NULL: the model has none), device pointers of element type `dtype`; the split of a shard is fixed.
+ *   b200_shard_token_from_partial (next stage)  scores its rows against x (same fused final norm), merges with the
+ *        partial result and writes the token ids (int64 [B]) and, if asked, the top-1 margins. */
+#define B200_PARTIAL_MSG_BYTES(B, H) ((size_t)(B) * ((size_t)(H) * 4 + 16))
+B200_API int b200_shard_forward_partial(b200_shard_t* s, b200_kv_t* kv, const int32_t* h_slots, const void* d_hidden_in, int B, int S,
+                                        int causal, int split, void* d_msg_out, void* stream);
+B200_API int b200_shard_set_vocab_tail(b200_shard_t* s, const void* d_lm_head_rows, const void* d_final_norm, int split, int dtype,
+                                       void* stream);
+B200_API int b200_shard_token_from_partial(b200_shard_t* s, const void* d_msg_in, int B, int64_t* d_tok_out, float* d_margin_out,
+                                           void* stream);
 /* Entry node: embed_tokens(ids) (utils/node_worker.py:215,302). d_ids int64 [n] -> bf16 [n,H] */
 B200_API int b200_shard_embed(b200_shard_t* s, const int64_t* d_ids, int n, void* d_hidden_out, void* stream);
 

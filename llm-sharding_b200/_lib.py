@@ -53,6 +53,9 @@ PROTOTYPES = {
     "b200_shard_forward_argmax": (_I, [_P, _P, C.POINTER(C.c_int32), _P, _I, _I, _I, _P, _P, _P, _P]),
     "b200_shard_embed": (_I, [_P, _P, _I, _P, _P]),
     "b200_shard_step_tokens": (_I, [_P, _P, C.POINTER(C.c_int32), _P, _I, _I, _I, _P, _P, _P, _P]),
+    "b200_shard_forward_partial": (_I, [_P, _P, C.POINTER(C.c_int32), _P, _I, _I, _I, _I, _P, _P]),
+    "b200_shard_set_vocab_tail": (_I, [_P, _P, _P, _I, _I, _P]),
+    "b200_shard_token_from_partial": (_I, [_P, _P, _I, _P, _P, _P]),
     "b200_shard_run_kernel": (_I, [_P, _P, _I, _I, _I, _P]),
     "b200_hop_create": (_I, [_I, _I, _I64, C.POINTER(_P)]),
     "b200_hop_export": (_I, [_P, _P]),

@@ -74,6 +74,9 @@ struct b200_shard {
     float *lastrow = nullptr, *logits = nullptr, *attn_part = nullptr;
     float* sk_ws = nullptr;             // stream-K GEMM: partial-sum slots, one per SM
     unsigned int* sk_flags = nullptr;   // and their flags (zero between launches)
+    // vocabulary-split tail: rows [aux_split, V) of lm_head and the final norm, held by the stage that FOLLOWS the tail in a ring
+    __nv_bfloat16 *aux_lm_head = nullptr, *aux_final_norm = nullptr;
+    int aux_split = 0;
     MegaLayer* mega_layers = nullptr;   // persistent decode kernel: the layers' weight pointers, in device memory
     unsigned int* mega_bar = nullptr;   // and its grid barrier (arrivals, generation), then the kernel's failure record
     float* row_ss = nullptr;            // folded RMSNorm: two buffers of [kMaxStreamRows][kRowSsParts] partial sums of squares
@@ -705,6 +708,29 @@ static int enqueue_tail(b200_shard_t* s, int B, int S, bool from_residual, int64
     return 0;
 }
 
+// Vocabulary-split tail, first half (the tail shard): the message for the next stage = the last fp32 residual row of every
+// batch row, then best / second-best score and best index over lm_head rows [0, split).  Same GEMV, same fused final norm as
+// enqueue_tail, so every logit has the bits it would have in the unsplit call.
+static int enqueue_tail_partial(b200_shard_t* s, int B, int S, int split, void* msg, cudaStream_t st) {
+    const b200_shard_config_t& c = s->cfg;
+    const int H = c.hidden_size;
+    if (B > gemv_row_limit(s)) return fail(B200_EINVAL, "[ERROR] the vocabulary-split tail serves at most %d rows per call", gemv_row_limit(s));
+    if (split < 1 || split >= c.vocab_size) return fail(B200_EINVAL, "[ERROR] split must lie inside the vocabulary");
+    float* mx = reinterpret_cast<float*>(msg);
+    float* best = mx + (size_t)B * H;
+    float* second = best + B;
+    int64_t* idx = reinterpret_cast<int64_t*>(second + B);
+    launch_lastrow_norm_f32(s->x, nullptr, 0.f, B, S, H, mx, st);
+    GemvParams g{};
+    g.W = s->lm_head; g.N = split; g.K = H; g.out = s->logits;
+    g.x = s->x + (size_t)(S - 1) * H; g.x_stride = (int64_t)S * H;
+    g.norm_w = c.has_final_norm ? s->final_norm : nullptr; g.eps = c.rms_eps;
+    launch_gemv(g, B, EPI_STORE, c.has_final_norm != 0, s->num_sms, st);
+    launch_argmax_range(s->logits, B, split, 0, nullptr, nullptr, nullptr, best, second, idx, nullptr, st);
+    s->n_launch += 3;
+    return 0;
+}
+
 static void account(b200_shard_t* s, b200_kv_t* kv, const SlotList& sl, int B, int S, int causal, bool tail) {
     const b200_shard_config_t& c = s->cfg;
     const uint64_t H = c.hidden_size, I = c.intermediate_size;
@@ -727,28 +753,35 @@ static void account(b200_shard_t* s, b200_kv_t* kv, const SlotList& sl, int B, i
     s->n_calls += 1;
 }
 
+// partial_split > 0: vocabulary-split tail — instead of the token, `msg` receives the message of enqueue_tail_partial
 static int forward_impl(b200_shard_t* s, b200_kv_t* kv, const int32_t* h_slots, const void* in, const int64_t* tok_in,
-                        int B, int S, int causal, void* out, int64_t* tok, float* margin, bool with_tail, void* stream) {
+                        int B, int S, int causal, void* out, int64_t* tok, float* margin, bool with_tail, void* stream,
+                        int partial_split = 0, void* msg = nullptr) {
     SlotList sl{};
     TRY(check_call(s, kv, h_slots, tok_in != nullptr ? (const void*)tok_in : in, B, S, &sl));
     if (tok_in != nullptr && (!s->cfg.has_embedding || s->embedding == nullptr))
         return fail(B200_ESTATE, "[ERROR] this node does not have embedding layer while receiving user request.");
     if (with_tail) {
         if (!s->cfg.has_lm_head || s->lm_head == nullptr) return fail(B200_ESTATE, "[ERROR] this shard does not hold the lm_head");
-        if (tok == nullptr) return fail(B200_EINVAL, "[ERROR] null token output");
+        if (tok == nullptr && partial_split == 0) return fail(B200_EINVAL, "[ERROR] null token output");
+        if (partial_split > 0 && msg == nullptr) return fail(B200_EINVAL, "[ERROR] null message output");
     }
     if (s->cfg.has_final_norm && s->final_norm == nullptr) return fail(B200_ESTATE, "[ERROR] final norm weight not loaded");
     CU_TRY(cudaSetDevice(s->device));
     cudaStream_t st = (cudaStream_t)stream;
     account(s, kv, sl, B, S, causal, with_tail);
+    if (partial_split > 0) {   // only rows [0, split) of lm_head are read here
+        s->n_bytes -= (uint64_t)(s->cfg.vocab_size - partial_split) * s->cfg.hidden_size * 2;
+        s->n_flops -= 2ull * (uint64_t)(s->cfg.vocab_size - partial_split) * s->cfg.hidden_size * B;
+    }
     bool done = false;
     if (s->graphs && S == 1) {
         GraphKey key;
         memset(&key, 0, sizeof(key));
-        key.B = B; key.causal = causal; key.with_argmax = with_tail ? 1 : 0;
+        key.B = B; key.causal = causal; key.with_argmax = with_tail ? (partial_split > 0 ? 2 + partial_split : 1) : 0;
         // the tensor-core decode attention sizes its score buffer in whole kilo-keys: one graph per bucket of the context length
         if (attn_decode_tc_min_rows() > 0 && B >= attn_decode_tc_min_rows()) key.pad_ = (kv->h_len[sl.v[0]] + S + 1023) / 1024;
-        key.in = in; key.out = out; key.tok = tok; key.margin = margin; key.kv_gen = kv->gen; key.tok_in = tok_in;
+        key.in = in; key.out = partial_split > 0 ? msg : out; key.tok = tok; key.margin = margin; key.kv_gen = kv->gen; key.tok_in = tok_in;
         for (int b = 0; b < B; ++b) key.slots[b] = sl.v[b];
         auto it = s->graph_cache.find(key);
         if (it == s->graph_cache.end()) {
@@ -758,7 +791,7 @@ static int forward_impl(b200_shard_t* s, b200_kv_t* kv, const int32_t* h_slots, 
             const uint64_t launches_before = s->n_launch;
             CU_TRY(cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal));
             int r = enqueue_forward(s, kv, sl, in, tok_in, B, S, causal, out, tok, margin, with_tail, cs);
-            if (r == 0 && with_tail) r = enqueue_tail(s, B, S, true, tok, margin, cs);
+            if (r == 0 && with_tail) r = partial_split > 0 ? enqueue_tail_partial(s, B, S, partial_split, msg, cs) : enqueue_tail(s, B, S, true, tok, margin, cs);
             cudaGraph_t graph = nullptr;
             cudaError_t ce = cudaStreamEndCapture(cs, &graph);
             const uint64_t captured = s->n_launch - launches_before;
@@ -795,7 +828,10 @@ static int forward_impl(b200_shard_t* s, b200_kv_t* kv, const int32_t* h_slots, 
     }
     if (!done) {
         TRY(enqueue_forward(s, kv, sl, in, tok_in, B, S, causal, out, tok, margin, with_tail, st));
-        if (with_tail) TRY(enqueue_tail(s, B, S, true, tok, margin, st));
+        if (with_tail) {
+            if (partial_split > 0) { TRY(enqueue_tail_partial(s, B, S, partial_split, msg, st)); }
+            else { TRY(enqueue_tail(s, B, S, true, tok, margin, st)); }
+        }
         CU_TRY(cudaGetLastError());
     }
     for (int b = 0; b < B; ++b) {  // host mirror of what kv_alloc_kernel does on the device
@@ -822,6 +858,54 @@ extern "C" B200_API int b200_shard_step_tokens(b200_shard_t* s, b200_kv_t* kv, c
     const bool tail = s != nullptr && s->cfg.has_lm_head;
     if (!tail && out == nullptr) return fail(B200_EINVAL, "[ERROR] null output");
     return forward_impl(s, kv, h_slots, nullptr, tok_in, B, S, causal, out, tail ? tok : nullptr, tail ? margin : nullptr, tail, stream);
+}
+
+extern "C" B200_API int b200_shard_forward_partial(b200_shard_t* s, b200_kv_t* kv, const int32_t* h_slots, const void* in, int B, int S,
+                                                   int causal, int split, void* msg_out, void* stream) {
+    if (split < 1) return fail(B200_EINVAL, "[ERROR] split must be positive");
+    return forward_impl(s, kv, h_slots, in, nullptr, B, S, causal, nullptr, nullptr, nullptr, true, stream, split, msg_out);
+}
+extern "C" B200_API int b200_shard_set_vocab_tail(b200_shard_t* s, const void* lm_head_rows, const void* final_norm, int split, int dtype,
+                                                  void* stream) {
+    if (s == nullptr || lm_head_rows == nullptr) return fail(B200_EINVAL, "[ERROR] null argument");
+    if (split < 1 || split >= s->cfg.vocab_size) return fail(B200_EINVAL, "[ERROR] split must lie inside the vocabulary");
+    if (dtype < 0 || dtype > 2) return fail(B200_EINVAL, "[ERROR] unsupported weight dtype %d", dtype);
+    CU_TRY(cudaSetDevice(s->device));
+    const size_t H = s->cfg.hidden_size, rows = (size_t)(s->cfg.vocab_size - split);
+    if (s->aux_lm_head != nullptr && s->aux_split != split) return fail(B200_ESTATE, "[ERROR] the vocabulary split of a shard cannot change");
+    if (s->aux_lm_head == nullptr) TRY(dev_alloc(s->allocs, &s->aux_lm_head, rows * H));
+    launch_convert_to_bf16(lm_head_rows, dtype, s->aux_lm_head, (int64_t)(rows * H), (cudaStream_t)stream, true);
+    if (final_norm != nullptr) {
+        if (s->aux_final_norm == nullptr) TRY(dev_alloc(s->allocs, &s->aux_final_norm, H));
+        launch_convert_to_bf16(final_norm, dtype, s->aux_final_norm, (int64_t)H, (cudaStream_t)stream);
+    }
+    CU_TRY(cudaGetLastError());
+    CU_TRY(cudaStreamSynchronize((cudaStream_t)stream));
+    s->aux_split = split;
+    return 0;
+}
+extern "C" B200_API int b200_shard_token_from_partial(b200_shard_t* s, const void* msg_in, int B, int64_t* tok_out, float* margin_out,
+                                                      void* stream) {
+    if (s == nullptr || msg_in == nullptr || tok_out == nullptr) return fail(B200_EINVAL, "[ERROR] null argument");
+    if (s->aux_lm_head == nullptr) return fail(B200_ESTATE, "[ERROR] this shard holds no vocabulary tail (b200_shard_set_vocab_tail)");
+    if (B < 1 || B > gemv_row_limit(s) || B > s->cfg.max_batch) return fail(B200_EINVAL, "[ERROR] bad row count %d", B);
+    CU_TRY(cudaSetDevice(s->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    const int H = s->cfg.hidden_size, rows = s->cfg.vocab_size - s->aux_split;
+    const float* mx = reinterpret_cast<const float*>(msg_in);
+    const float* best = mx + (size_t)B * H;
+    const float* second = best + B;
+    const int64_t* idx = reinterpret_cast<const int64_t*>(second + B);
+    GemvParams g{};
+    g.W = s->aux_lm_head; g.N = rows; g.K = H; g.out = s->logits; g.x = mx; g.x_stride = H;
+    g.norm_w = s->aux_final_norm; g.eps = s->cfg.rms_eps;
+    launch_gemv(g, B, EPI_STORE, s->aux_final_norm != nullptr, s->num_sms, st);
+    launch_argmax_range(s->logits, B, rows, s->aux_split, best, second, idx, nullptr, nullptr, tok_out, margin_out, st);
+    s->n_launch += 2;
+    s->n_bytes += (uint64_t)rows * H * 2;
+    s->n_flops += 2ull * rows * H * B;
+    CU_TRY(cudaGetLastError());
+    return 0;
 }
 
 extern "C" B200_API int b200_shard_run_kernel(b200_shard_t* s, b200_kv_t* kv, int kind, int layer, int rows, void* stream) {

@@ -79,6 +79,8 @@ void launch_lastrow_norm_f32(const float* x, const __nv_bfloat16* norm_w, float 
                              float* out, cudaStream_t st);
 void launch_lastrow_to_f32(const void* h, int dtype, int B, int S, int n, float* out, cudaStream_t st);
 void launch_argmax(const float* logits, int B, int V, int64_t* tok, float* margin, cudaStream_t st);
+void launch_argmax_range(const float* logits, int B, int n, int offset, const float* in_best, const float* in_second, const int64_t* in_idx,
+                         float* out_best, float* out_second, int64_t* out_idx, float* out_margin, cudaStream_t st);
 void launch_embed(const __nv_bfloat16* table, const int64_t* ids, int n, int H, int V, void* out, int out_dtype,
                   cudaStream_t st);
 // src (.pth storage dtype) -> bf16, or -> fp16 (saturating) when f16_out

@@ -403,6 +403,79 @@ void launch_argmax(const float* logits, int B, int V, int64_t* tok, float* margi
     cudaLaunchKernelEx(&cfg, argmax_kernel, logits, V, tok, margin);
 }
 
+// arg-max over a RANGE of the vocabulary (the vocabulary-split tail of the ring: the tail stage scores rows [0, split) of
+// lm_head, its successor the rest).  logits: [B][n] scores of vocabulary rows offset .. offset + n - 1.  The range's best and
+// second-best values and the best index are merged with an incoming partial result (in_*: another, LOWER range's, may be
+// null) exactly as torch.argmax over the whole row would decide (first index of the maximum), and go out as a partial
+// result (out_best / out_second / out_idx) and / or as the final token id and its top-1 margin.
+__global__ void __launch_bounds__(1024) argmax_range_kernel(const float* __restrict__ logits, int n, int offset, const float* in_best,
+                                                            const float* in_second, const int64_t* in_idx, float* out_best,
+                                                            float* out_second, int64_t* out_idx, float* out_margin) {
+    __shared__ float sv[32], s2[32];
+    __shared__ int si[32];
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    const float* row = logits + (size_t)blockIdx.x * n;
+    float best = -INFINITY, second = -INFINITY;
+    int bi = 0x7fffffff;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {   // increasing indices per thread: '>' keeps the first maximum
+        const float v = __ldcg(row + i);
+        if (v > best) { second = best; best = v; bi = i; }
+        else if (v > second) second = v;
+    }
+    auto merge = [](float& b, int& i, float& s, float ob, int oi, float os) {
+        if (ob > b || (ob == b && oi < i)) { s = fmaxf(fmaxf(b, os), s); b = ob; i = oi; }
+        else s = fmaxf(s, ob);
+    };
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+        const float os = __shfl_xor_sync(0xffffffffu, second, o);
+        merge(best, bi, second, ob, oi, os);
+    }
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    if (lane == 0) { sv[w] = best; si[w] = bi; s2[w] = second; }
+    __syncthreads();
+    if (w == 0) {
+        const int nw = blockDim.x >> 5;
+        best = lane < nw ? sv[lane] : -INFINITY;
+        bi = lane < nw ? si[lane] : 0x7fffffff;
+        second = lane < nw ? s2[lane] : -INFINITY;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+            const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+            const float os = __shfl_xor_sync(0xffffffffu, second, o);
+            merge(best, bi, second, ob, oi, os);
+        }
+        if (lane == 0) {
+            int64_t idx = (int64_t)bi + offset;
+            if (in_best != nullptr) {   // the incoming range lies below this one: it wins ties
+                const float ib = in_best[blockIdx.x], is = in_second[blockIdx.x];
+                if (ib >= best) { second = fmaxf(is, best); best = ib; idx = in_idx[blockIdx.x]; }
+                else second = fmaxf(second, ib);
+            }
+            if (out_best != nullptr) { out_best[blockIdx.x] = best; out_second[blockIdx.x] = second; }
+            if (out_idx != nullptr) out_idx[blockIdx.x] = idx;
+            if (out_margin != nullptr) out_margin[blockIdx.x] = best - second;
+        }
+    }
+}
+void launch_argmax_range(const float* logits, int B, int n, int offset, const float* in_best, const float* in_second, const int64_t* in_idx,
+                         float* out_best, float* out_second, int64_t* out_idx, float* out_margin, cudaStream_t st) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(B);
+    cfg.blockDim = dim3(1024);
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    const char* e = getenv("B200SHARD_PDL");
+    cfg.numAttrs = (e != nullptr && e[0] == '0') ? 0 : 1;
+    cudaLaunchKernelEx(&cfg, argmax_range_kernel, logits, n, offset, in_best, in_second, in_idx, out_best, out_second, out_idx, out_margin);
+}
+
 // embed_tokens(ids) (utils/node_worker.py:215,302): row gather, 128-bit copies.
 __global__ void embed_any_kernel(const __nv_bfloat16* __restrict__ table, const int64_t* __restrict__ ids, int H, int V,
                                  void* __restrict__ out, int dtype) {

@@ -192,6 +192,39 @@ class Shard:
                                                    _lib.ptr(margin_out), self._stream()))
         return tok_out if self.has_lm_head else hidden_out
 
+    # ---- vocabulary-split tail (ring stages; include/b200shard.h)
+    def partial_msg_bytes(self, B: int) -> int:
+        return B * (self.hidden_size * 4 + 16)
+
+    def forward_partial(self, hidden: torch.Tensor, kv: "PagedKVCache", split: int, msg_out: torch.Tensor, slots=None,
+                        causal: bool = False) -> torch.Tensor:
+        """Tail shard: layers + lm_head rows [0, split); ``msg_out`` (uint8, >= partial_msg_bytes(B)) receives the message for
+        the stage that holds the other rows.  Pass the same persistent buffers every step (S == 1 replays a CUDA graph)."""
+        hidden = self._check_hidden(hidden)
+        B, S, _ = hidden.shape
+        if msg_out.numel() * msg_out.element_size() < self.partial_msg_bytes(B):
+            raise ValueError("[ERROR] message buffer too small")
+        _lib.check(self.lib.b200_shard_forward_partial(self.handle, kv.handle, self._slots(slots, B), hidden.data_ptr(), B, S,
+                                                       int(causal), int(split), msg_out.data_ptr(), self._stream()))
+        return msg_out
+
+    def set_vocab_tail(self, lm_head_rows: torch.Tensor, final_norm: torch.Tensor | None, split: int) -> None:
+        """The stage after the tail: rows [split, V) of lm_head ([V - split, H]) and the final norm weight."""
+        w = lm_head_rows.to(self.device).contiguous()
+        n = None if final_norm is None else final_norm.to(device=self.device, dtype=w.dtype).contiguous()
+        if w.dtype not in _lib.TORCH_TO_DT:
+            raise ValueError(f"[ERROR] unsupported weight dtype {w.dtype}")
+        _lib.check(self.lib.b200_shard_set_vocab_tail(self.handle, w.data_ptr(), _lib.ptr(n), int(split), _lib.TORCH_TO_DT[w.dtype],
+                                                      self._stream()))
+
+    def token_from_partial(self, msg: torch.Tensor, B: int, tok_out: torch.Tensor | None = None, want_margin: bool = False):
+        if tok_out is None:
+            tok_out = torch.empty(B, dtype=torch.int64, device=self.device)
+        margin = torch.empty(B, dtype=torch.float32, device=self.device) if want_margin else None
+        _lib.check(self.lib.b200_shard_token_from_partial(self.handle, msg.data_ptr(), B, tok_out.data_ptr(), _lib.ptr(margin),
+                                                          self._stream()))
+        return (tok_out, margin) if want_margin else tok_out
+
     def run_kernel(self, kv: "PagedKVCache", kind: int, layer: int, rows: int = 1) -> None:
         _lib.check(self.lib.b200_shard_run_kernel(self.handle, kv.handle, kind, layer, rows, self._stream()))
 
