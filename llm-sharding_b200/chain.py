@@ -11,6 +11,7 @@ from __future__ import annotations
 
 import collections
 import ctypes as C
+import os
 
 import torch
 import zmq
@@ -239,7 +240,7 @@ class ChainStage:
     ncclSend / ncclRecv through torch.distributed (the A/B alternative)."""
 
     def __init__(self, worker, rank: int, world: int, n_streams: int, max_prompt: int, ctrl_group=None,
-                 transport: str = "p2p", max_wait_us: int = 20_000_000, rows: int = 1):
+                 transport: str = "p2p", max_wait_us: int = 20_000_000, rows: int = 1, split_tail: bool | None = None):
         import torch.distributed as dist
 
         self.w, self.rank, self.world, self.n_streams = worker, rank, world, n_streams
@@ -256,7 +257,27 @@ class ChainStage:
         self.dist = dist
         self.nxt, self.prv = (rank + 1) % world, (rank - 1) % world
         self.rows = rows  # batch rows of one stream (micro-batch); stream i owns KV slots [i*rows, (i+1)*rows)
-        self.slot_bytes = max(rows * max_prompt * self.H * 2, 4096)
+        # Vocabulary-split tail: the reference's last worker carries final norm + lm_head + argmax for every stream
+        # (utils/node_worker.py:155-164,260-264) and so bounds the ring; here the tail scores the lower half of lm_head and the
+        # head — which receives the token anyway — the upper half, from the fp32 residual row the tail sends along
+        # (include/b200shard.h: bit-identical tokens).  Every stage derives the same decision from the same inputs.
+        if split_tail is None:
+            split_tail = os.environ.get("B200SHARD_SPLIT_TAIL", "1") != "0"
+        self.split = 0
+        if split_tail and world >= 2 and transport == "p2p" and rows <= 3:
+            self.split = int(worker.config["vocab_size"]) // 2
+        self.msg_bytes = rows * (self.H * 4 + 16)
+        self.slot_bytes = max(rows * max_prompt * self.H * 2, 4096, self.msg_bytes if self.split else 0)
+        if self.split and self.sched.is_head:
+            load = worker.state_provider or (lambda f: torch.load(os.path.join(worker.shards_path, f), map_location="cpu"))
+            lm = load("lm_head.pth")["weight"]
+            try:
+                fn = load("final_norm.pth")["weight"]
+            except FileNotFoundError:
+                fn = None
+            self.eng.set_vocab_tail(lm[self.split:], fn, self.split)
+            del lm
+            self._tok_buf = [torch.zeros(rows, dtype=torch.int64, device=self.device) for _ in range(n_streams)]
         if transport == "p2p":
             self.hop = P2PHop(self.device, n_streams, self.slot_bytes)
             mine = (self.hop.export(), self.hop.dev_index)
@@ -325,6 +346,22 @@ class ChainStage:
             if len(self._pending) > 4 * self.n_streams:
                 self._pending = [w for w in self._pending if not w.is_completed()]
 
+    def _token_ptr(self, item) -> int:
+        """Head: device address of the token ids that the message just waited for carries — the mailbox slot itself, or, with
+        the vocabulary-split tail, this stream's token buffer after the head scored its half of lm_head."""
+        if not self.split:
+            return self._in_ptr(item)
+        buf = self._tok_buf[item["stream"]]
+        _lib.check(self.lib.b200_shard_token_from_partial(self.eng.handle, self._in_ptr(item), self.rows, buf.data_ptr(), None, self._st()))
+        return buf.data_ptr()
+
+    def _token_view(self, item, tok_ptr: int) -> torch.Tensor:
+        if self.split:
+            return self._tok_buf[item["stream"]]
+        if self.hop is not None:
+            return tensor_view(tok_ptr, 8 * self.rows, self.device)
+        return self.inbuf[item["wait"][1]][:8 * self.rows]
+
     def _run(self, item, S: int, tok_in_ptr: int | None, record: bool, via_host: bool = False) -> None:
         import ctypes as C
         B = self.rows
@@ -332,6 +369,8 @@ class ChainStage:
         sch = self.sched
         hid_bytes, tok_bytes = B * S * self.H * 2, 8 * B
         in_bytes = tok_bytes if (sch.is_head and item["kind"] == "decode") else hid_bytes
+        if self.split:
+            tok_bytes = self.msg_bytes
         out_bytes = tok_bytes if sch.is_tail else hid_bytes
         self._wait(item, in_bytes)
         out_ptr = self._out_ptr(item)
@@ -341,11 +380,11 @@ class ChainStage:
             self.inbound.append((item["stream"], S, src.view(torch.bfloat16).view(B, S, self.H).clone()))
         if sch.is_head:
             if tok_in_ptr is None:
-                tok_in_ptr = self._in_ptr(item)
+                tok_in_ptr = self._token_ptr(item)
                 if via_host:
                     # end-to-end mode: the id leaves the GPU (D2H, the host blocks until the ring delivered it), is seen
                     # by the host loop (the reference decodes / prints it there) and comes back from pinned memory (H2D)
-                    src = (tensor_view(tok_in_ptr, 8 * B, self.device) if self.hop is not None else self.inbuf[item["wait"][1]][:8 * B])
+                    src = self._token_view(item, tok_in_ptr)
                     if not hasattr(self, "_host_tok"):
                         self._host_tok = torch.empty(B, dtype=torch.int64).pin_memory()
                         self._dev_tok = [torch.empty(B, dtype=torch.int64, device=self.device) for _ in range(self.n_streams)]
@@ -354,14 +393,16 @@ class ChainStage:
                     self._dev_tok[item["stream"]].copy_(self._host_tok, non_blocking=True)
                     tok_in_ptr = self._dev_tok[item["stream"]].data_ptr()
                 elif record:
-                    self.tokens.append(tensor_view(tok_in_ptr, 8 * B, self.device).view(torch.int64).clone()
-                                       if self.hop is not None else self.inbuf[item["wait"][1]][:8 * B].view(torch.int64).clone())
+                    self.tokens.append(self._token_view(item, tok_in_ptr).view(torch.int64).clone())
             if sch.is_tail:  # single-stage ring: token in, token out
                 _lib.check(self.lib.b200_shard_step_tokens(self.eng.handle, self.kv.handle, slots, tok_in_ptr, B, S, self.causal,
                                                            None, out_ptr, None, self._st()))
             else:
                 _lib.check(self.lib.b200_shard_step_tokens(self.eng.handle, self.kv.handle, slots, tok_in_ptr, B, S, self.causal,
                                                            out_ptr, None, None, self._st()))
+        elif sch.is_tail and self.split:
+            _lib.check(self.lib.b200_shard_forward_partial(self.eng.handle, self.kv.handle, slots, self._in_ptr(item), B, S,
+                                                           self.causal, self.split, out_ptr, self._st()))
         elif sch.is_tail:
             _lib.check(self.lib.b200_shard_forward_argmax(self.eng.handle, self.kv.handle, slots, self._in_ptr(item), B, S,
                                                           self.causal, None, out_ptr, None, self._st()))
@@ -393,11 +434,9 @@ class ChainStage:
         item = self.sched.finish(stream)
         B = self.rows
         if item["wait"] is not None:
-            self._wait(item, 8 * B)
+            self._wait(item, self.msg_bytes if self.split else 8 * B)
             if record:
-                src = (tensor_view(self._in_ptr(item), 8 * B, self.device) if self.hop is not None
-                       else self.inbuf[item["wait"][1]][:8 * B])
-                self.tokens.append(src.view(torch.int64).clone())
+                self.tokens.append(self._token_view(item, self._token_ptr(item)).view(torch.int64).clone())
         for slot in range(stream * B, stream * B + B):
             self.kv.reset(slot)
 
