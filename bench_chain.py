@@ -398,7 +398,10 @@ def run_chain(args, config, metric, ClockSampler, peaks):
             "metric": metric, "value": value, "unit": "tok/s", "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms_per_step,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
             "config": dict(config, transport=transport, layers_this_rank=[start, end], streams=n_streams, rows_per_stream=rows,
-                           batch_in_flight=n_streams * rows),
+                           batch_in_flight=n_streams * rows,
+                           lm_head_placement=("vocabulary-split tail: lm_head rows [0, V/2) scored on the tail stage, [V/2, V) on the head "
+                                              "stage from the tail's fp32 residual row; tokens bit-identical to the unsplit tail"
+                                              if stage.split else "all of lm_head on the tail stage")),
             "clocks": clk.summary(),
             "e2e": {"value": e2e_val, "unit": "tok/s", "h2d_bytes_per_step": 8 * n_streams * rows, "d2h_bytes_per_step": 8 * n_streams * rows,
                     "api": "ChainStage.decode(via_host=True): every token id D2H to the head's pinned host memory and H2D back"},
