@@ -203,6 +203,7 @@ def run_chain(args, config, metric, ClockSampler, peaks):
             stage = ChainStage(worker, rank, world, n_streams, PROMPT_LEN, ctrl_group=ctrl, transport="nccl", rows=rows)
         else:
             raise
+    split_on = bool(stage.split)
     eng = worker.shard.engine
     g = torch.Generator().manual_seed(1234)
     prompts = [torch.randint(3, cfg["vocab_size"], (rows * PROMPT_LEN,), generator=g, dtype=torch.int64) for _ in range(n_streams)]
@@ -401,7 +402,7 @@ def run_chain(args, config, metric, ClockSampler, peaks):
                            batch_in_flight=n_streams * rows,
                            lm_head_placement=("vocabulary-split tail: lm_head rows [0, V/2) scored on the tail stage, [V/2, V) on the head "
                                               "stage from the tail's fp32 residual row; tokens bit-identical to the unsplit tail"
-                                              if stage.split else "all of lm_head on the tail stage")),
+                                              if split_on else "all of lm_head on the tail stage")),
             "clocks": clk.summary(),
             "e2e": {"value": e2e_val, "unit": "tok/s", "h2d_bytes_per_step": 8 * n_streams * rows, "d2h_bytes_per_step": 8 * n_streams * rows,
                     "api": "ChainStage.decode(via_host=True): every token id D2H to the head's pinned host memory and H2D back"},

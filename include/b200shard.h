@@ -141,7 +141,9 @@ B200_API int b200_shard_step_tokens(b200_shard_t* s, b200_kv_t* kv, const int32_
  *   b200_shard_forward_partial   (tail)  forward over the shard's layers, then d_msg_out receives
  *        float x[B][H]        the last fp32 residual row of every batch row (before the final norm)
  *        float best[B], second[B]; int64 idx[B]   best / second-best score and best row over lm_head rows [0, split)
- *        = B200_PARTIAL_MSG_BYTES(B, H) bytes; at most 3 rows per call.
+ *        = B200_PARTIAL_MSG_BYTES(B, H) bytes.  Up to three rows per call both halves run the fused-norm GEMV of the unsplit
+ *        tail (bit-identical tokens and margins); more rows: both halves normalise into fp16 and use the streaming
+ *        tensor-core GEMM (scores comparable across the halves to the last bit, equal to the unsplit call's within fp16 rounding).
  *   b200_shard_set_vocab_tail    (next stage)  rows [split, V) of lm_head ([V - split, H], row-major) and the final norm
  *        weight (NULL: the model has none), device pointers of element type `dtype`; the split of a shard is fixed.
  *   b200_shard_token_from_partial (next stage)  scores its rows against x (same fused final norm), merges with the

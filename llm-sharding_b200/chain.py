@@ -264,7 +264,7 @@ class ChainStage:
         if split_tail is None:
             split_tail = os.environ.get("B200SHARD_SPLIT_TAIL", "1") != "0"
         self.split = 0
-        if split_tail and world >= 2 and transport == "p2p" and rows <= 3:
+        if split_tail and world >= 2 and transport == "p2p" and rows <= 32:
             self.split = int(worker.config["vocab_size"]) // 2
         self.msg_bytes = rows * (self.H * 4 + 16)
         self.slot_bytes = max(rows * max_prompt * self.H * 2, 4096, self.msg_bytes if self.split else 0)

@@ -711,23 +711,51 @@ static int enqueue_tail(b200_shard_t* s, int B, int S, bool from_residual, int64
 // Vocabulary-split tail, first half (the tail shard): the message for the next stage = the last fp32 residual row of every
 // batch row, then best / second-best score and best index over lm_head rows [0, split).  Same GEMV, same fused final norm as
 // enqueue_tail, so every logit has the bits it would have in the unsplit call.
+// Scores of lm_head rows W [n_rows, H] for B token rows -> s->logits [B][n_rows].  Up to the GEMV row limit: the GEMV with the
+// final norm fused (x: fp32 rows, x_stride apart), the very kernel of the unsplit tail.  More rows: normalise into fp16 and run
+// the streaming tensor-core GEMM (x must then be contiguous [B][H]); both halves of a split vocabulary take the same route, so
+// their scores are comparable to the last bit.
+static int score_rows(b200_shard_t* s, const __nv_bfloat16* W, int n_rows, const __nv_bfloat16* norm_w, const float* x, int64_t x_stride,
+                      int B, cudaStream_t st) {
+    const b200_shard_config_t& c = s->cfg;
+    const int H = c.hidden_size;
+    if (B <= gemv_row_limit(s)) {
+        GemvParams g{};
+        g.W = W; g.N = n_rows; g.K = H; g.out = s->logits; g.x = x; g.x_stride = x_stride; g.norm_w = norm_w; g.eps = c.rms_eps;
+        launch_gemv(g, B, EPI_STORE, norm_w != nullptr, s->num_sms, st);
+        s->n_launch += 1;
+        return 0;
+    }
+    if (x_stride != H) return fail(B200_EINVAL, "[ERROR] batched scoring needs contiguous rows");
+    launch_rmsnorm_bf16(x, norm_w, c.rms_eps, B, H, s->lastrow_b, st, B200_DT_F16);
+    if (B <= kMaxStreamRows && stream_gemm_enabled() && H % 64 == 0) {
+        StreamGemmParams g{};
+        g.W = W; g.X = s->lastrow_b; g.M = B; g.N = n_rows; g.K = H; g.out = s->logits; g.ws = s->sk_ws; g.ws_flags = s->sk_flags;
+        if (launch_gemm_stream(g, EPI_STORE, s->num_sms, st) != 0) return fail(B200_ECUDA, "[ERROR] %s", gemm_stream_last_error());
+    } else {
+        GemmParams g{};
+        g.A = s->lastrow_b; g.W = W; g.M = B; g.N = n_rows; g.K = H; g.out = s->logits; g.epi = GEMM_STORE_F32; g.ab_f16 = 1;
+        if (launch_gemm(g, st) != 0) return fail(B200_ECUDA, "[ERROR] %s", gemm_error());
+    }
+    s->n_launch += 2;
+    return 0;
+}
+
 static int enqueue_tail_partial(b200_shard_t* s, int B, int S, int split, void* msg, cudaStream_t st) {
     const b200_shard_config_t& c = s->cfg;
     const int H = c.hidden_size;
-    if (B > gemv_row_limit(s)) return fail(B200_EINVAL, "[ERROR] the vocabulary-split tail serves at most %d rows per call", gemv_row_limit(s));
+    if (B > c.max_batch) return fail(B200_EINVAL, "[ERROR] more rows than max_batch");
     if (split < 1 || split >= c.vocab_size) return fail(B200_EINVAL, "[ERROR] split must lie inside the vocabulary");
     float* mx = reinterpret_cast<float*>(msg);
     float* best = mx + (size_t)B * H;
     float* second = best + B;
     int64_t* idx = reinterpret_cast<int64_t*>(second + B);
     launch_lastrow_norm_f32(s->x, nullptr, 0.f, B, S, H, mx, st);
-    GemvParams g{};
-    g.W = s->lm_head; g.N = split; g.K = H; g.out = s->logits;
-    g.x = s->x + (size_t)(S - 1) * H; g.x_stride = (int64_t)S * H;
-    g.norm_w = c.has_final_norm ? s->final_norm : nullptr; g.eps = c.rms_eps;
-    launch_gemv(g, B, EPI_STORE, c.has_final_norm != 0, s->num_sms, st);
+    const __nv_bfloat16* nw = c.has_final_norm ? s->final_norm : nullptr;
+    if (B <= gemv_row_limit(s)) { TRY(score_rows(s, s->lm_head, split, nw, s->x + (size_t)(S - 1) * H, (int64_t)S * H, B, st)); }
+    else { TRY(score_rows(s, s->lm_head, split, nw, mx, H, B, st)); }
     launch_argmax_range(s->logits, B, split, 0, nullptr, nullptr, nullptr, best, second, idx, nullptr, st);
-    s->n_launch += 3;
+    s->n_launch += 2;
     return 0;
 }
 
@@ -888,7 +916,7 @@ extern "C" B200_API int b200_shard_token_from_partial(b200_shard_t* s, const voi
                                                       void* stream) {
     if (s == nullptr || msg_in == nullptr || tok_out == nullptr) return fail(B200_EINVAL, "[ERROR] null argument");
     if (s->aux_lm_head == nullptr) return fail(B200_ESTATE, "[ERROR] this shard holds no vocabulary tail (b200_shard_set_vocab_tail)");
-    if (B < 1 || B > gemv_row_limit(s) || B > s->cfg.max_batch) return fail(B200_EINVAL, "[ERROR] bad row count %d", B);
+    if (B < 1 || B > s->cfg.max_batch) return fail(B200_EINVAL, "[ERROR] bad row count %d", B);
     CU_TRY(cudaSetDevice(s->device));
     cudaStream_t st = (cudaStream_t)stream;
     const int H = s->cfg.hidden_size, rows = s->cfg.vocab_size - s->aux_split;
@@ -896,12 +924,9 @@ extern "C" B200_API int b200_shard_token_from_partial(b200_shard_t* s, const voi
     const float* best = mx + (size_t)B * H;
     const float* second = best + B;
     const int64_t* idx = reinterpret_cast<const int64_t*>(second + B);
-    GemvParams g{};
-    g.W = s->aux_lm_head; g.N = rows; g.K = H; g.out = s->logits; g.x = mx; g.x_stride = H;
-    g.norm_w = s->aux_final_norm; g.eps = s->cfg.rms_eps;
-    launch_gemv(g, B, EPI_STORE, s->aux_final_norm != nullptr, s->num_sms, st);
+    TRY(score_rows(s, s->aux_lm_head, rows, s->aux_final_norm, mx, H, B, st));
     launch_argmax_range(s->logits, B, rows, s->aux_split, best, second, idx, nullptr, nullptr, tok_out, margin_out, st);
-    s->n_launch += 2;
+    s->n_launch += 1;
     s->n_bytes += (uint64_t)rows * H * 2;
     s->n_flops += 2ull * rows * H * B;
     CU_TRY(cudaGetLastError());
